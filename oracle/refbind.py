@@ -1,0 +1,244 @@
+"""ctypes binding of oracle/_ref/libsdmm_ref.so -- the REFERENCE's own sdmm headers compiled
+behind oracle/ref_driver.cpp.  TEST INFRASTRUCTURE ONLY: importable from tests/,
+__graft_entry__.smoke() and bench.py's CPU-baseline legs, never from the product package.
+
+Flat layouts are documented at the top of oracle/ref_driver.cpp (and include/sdmm_b200.h).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libsdmm_ref.so")
+
+JOINT_PLANES = 32
+EM_PLANES = 81
+SCALAR_WORDS = 8
+
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError("oracle/_ref/libsdmm_ref.so missing: run `make -C oracle ref` where "
+                               "/root/reference is mounted")
+        L = C.CDLL(LIB_PATH)
+        fp = C.POINTER(C.c_float)
+        up = C.POINTER(C.c_uint32)
+        bp = C.POINTER(C.c_uint8)
+        vpp = C.POINTER(C.c_void_p)
+        L.sdmm_ref_cell_create.restype = C.c_void_p
+        L.sdmm_ref_cell_create.argtypes = [C.c_int]
+        L.sdmm_ref_cell_destroy.argtypes = [C.c_void_p]
+        L.sdmm_ref_cell_set.argtypes = [C.c_void_p, fp, fp, up]
+        L.sdmm_ref_cell_get.argtypes = [C.c_void_p, fp, fp, up]
+        L.sdmm_ref_cell_get_derived.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_em_step.argtypes = [C.c_void_p, C.c_int, fp, C.c_long, fp, C.c_int, fp]
+        L.sdmm_ref_em_batch.restype = C.c_double
+        L.sdmm_ref_em_batch.argtypes = [vpp, C.c_int, up, fp, C.c_long, fp, C.c_int, C.c_int, C.c_int]
+        L.sdmm_ref_prepare_conditioner.argtypes = [C.c_void_p]
+        L.sdmm_ref_get_conditioner.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_sample_pdf.restype = C.c_double
+        L.sdmm_ref_sample_pdf.argtypes = [vpp, C.c_long, up, fp, fp, fp, fp, fp, up, bp, C.c_int]
+        L.sdmm_ref_pdf.restype = C.c_double
+        L.sdmm_ref_pdf.argtypes = [vpp, C.c_long, up, fp, fp, fp, bp, fp, fp, C.c_int]
+        L.sdmm_ref_kat_pdf_scalar.restype = C.c_float
+        L.sdmm_ref_kat_pdf_dynamic.argtypes = [fp]
+        L.sdmm_ref_kat_conditioner.argtypes = [fp]
+        L.sdmm_ref_kat_cholesky3.argtypes = [fp, fp]
+        L.sdmm_ref_kat_categorical.argtypes = [C.c_int, fp, fp, fp]
+        L.sdmm_ref_kat_frame.argtypes = [fp, fp]
+        L.sdmm_ref_joint_to.argtypes = [fp, fp, fp, fp]
+        _lib = L
+    return _lib
+
+
+def _f(a):
+    assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def _u(a):
+    assert a.dtype == np.uint32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(C.c_uint32))
+
+
+def _b(a):
+    assert a.dtype == np.uint8 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+def _off(a, n):
+    assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+    return C.cast(a.ctypes.data + 4 * n, C.POINTER(C.c_float))
+
+
+class RefCells:
+    """A batch of reference cells (one JointSDMM + EM + Conditioner each)."""
+
+    def __init__(self, n_cells, K):
+        self.C, self.K = n_cells, K
+        L = lib()
+        self.handles = (C.c_void_p * n_cells)(*[L.sdmm_ref_cell_create(K) for _ in range(n_cells)])
+
+    def __del__(self):
+        try:
+            L = lib()
+            for h in self.handles:
+                L.sdmm_ref_cell_destroy(h)
+        except Exception:
+            pass
+
+    def set(self, joint, em=None, scal=None):
+        """joint [C,32,K] f32; em [C,81,K] f32; scal [C,8] u32 words.  Returns per-cell bool."""
+        L = lib()
+        ok = np.zeros(self.C, dtype=bool)
+        for c in range(self.C):
+            ok[c] = bool(L.sdmm_ref_cell_set(
+                self.handles[c], _f(joint[c]),
+                _f(em[c]) if em is not None else None,
+                _u(scal[c]) if scal is not None else None))
+        return ok
+
+    def get(self):
+        L = lib()
+        joint = np.zeros((self.C, JOINT_PLANES, self.K), np.float32)
+        em = np.zeros((self.C, EM_PLANES, self.K), np.float32)
+        scal = np.zeros((self.C, SCALAR_WORDS), np.uint32)
+        for c in range(self.C):
+            L.sdmm_ref_cell_get(self.handles[c], _f(joint[c]), _f(em[c]), _u(scal[c]))
+        return joint, em, scal
+
+    def derived(self):
+        L = lib()
+        out = np.zeros((self.C, 38, self.K), np.float32)
+        for c in range(self.C):
+            L.sdmm_ref_cell_get_derived(self.handles[c], _f(out[c]))
+        return out
+
+    def em_step(self, offsets, point6, weight, n_iters, want_loglik=False):
+        """point6 [6,Ntot] f32, weight [Ntot], offsets [C+1] u32.  Serial, per cell."""
+        L = lib()
+        ntot = point6.shape[1]
+        ll = None
+        if want_loglik:
+            ll = [None] * self.C
+        for c in range(self.C):
+            b, e = int(offsets[c]), int(offsets[c + 1])
+            out = np.zeros((n_iters, e - b), np.float32) if want_loglik else None
+            L.sdmm_ref_em_step(self.handles[c], e - b, _off(point6, b), ntot, _off(weight, b),
+                               n_iters, _f(out) if want_loglik else None)
+            if want_loglik:
+                ll[c] = out
+        return ll
+
+    def em_batch(self, offsets, point6, weight, n_iters, with_prepare=True, n_threads=0):
+        """OpenMP over cells; returns seconds inside the em_step(+prepare) loop."""
+        L = lib()
+        return L.sdmm_ref_em_batch(C.cast(self.handles, C.POINTER(C.c_void_p)), self.C, _u(offsets),
+                                   _f(point6), point6.shape[1], _f(weight), n_iters,
+                                   1 if with_prepare else 0, n_threads)
+
+    def prepare_conditioner(self):
+        L = lib()
+        for h in self.handles:
+            L.sdmm_ref_prepare_conditioner(h)
+
+    def conditioner(self):
+        L = lib()
+        out = np.zeros((self.C, 38, self.K), np.float32)
+        for c in range(self.C):
+            L.sdmm_ref_get_conditioner(self.handles[c], _f(out[c]))
+        return out
+
+    def sample_pdf(self, cell_idx, pos3, u3, n_threads=0):
+        """pos3, u3: [3,n] f32 (u by role: select, radius, angle).  Returns dict + seconds."""
+        L = lib()
+        n = pos3.shape[1]
+        out_dir = np.zeros((3, n), np.float32)
+        out_pdf = np.zeros(n, np.float32)
+        out_ij = np.zeros(n, np.float32)
+        out_comp = np.zeros(n, np.uint32)
+        out_valid = np.zeros(n, np.uint8)
+        secs = L.sdmm_ref_sample_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx),
+                                     _f(pos3), _f(u3), _f(out_dir), _f(out_pdf), _f(out_ij),
+                                     _u(out_comp), _b(out_valid), n_threads)
+        return dict(dir=out_dir, pdf=out_pdf, inv_jac=out_ij, comp=out_comp, valid=out_valid), secs
+
+    def pdf(self, cell_idx, pos3, dir3, n_threads=0):
+        L = lib()
+        n = pos3.shape[1]
+        out_pdf = np.zeros(n, np.float32)
+        out_valid = np.zeros(n, np.uint8)
+        secs = L.sdmm_ref_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx), _f(pos3),
+                              _f(dir3), _f(out_pdf), _b(out_valid), None, None, n_threads)
+        return out_pdf, out_valid, secs
+
+    def conditional_weights(self, cell, x):
+        """Normalised conditional pmf/cdf at one vertex (for tie analysis)."""
+        L = lib()
+        pos = np.asarray(x, np.float32).reshape(3, 1).copy()
+        d = np.zeros((3, 1), np.float32)
+        d[2] = 1
+        pmf = np.zeros(self.K, np.float32)
+        cdf = np.zeros(self.K, np.float32)
+        pdf = np.zeros(1, np.float32)
+        valid = np.zeros(1, np.uint8)
+        idx = np.array([cell], np.uint32)
+        L.sdmm_ref_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), 1, _u(idx), _f(pos), _f(d),
+                       _f(pdf), _b(valid), _f(pmf), _f(cdf), 1)
+        return pmf, cdf, bool(valid[0])
+
+
+def kat_pdf_scalar():
+    return float(lib().sdmm_ref_kat_pdf_scalar())
+
+
+def kat_pdf_dynamic():
+    out = np.zeros(6, np.float32)
+    lib().sdmm_ref_kat_pdf_dynamic(_f(out))
+    return out
+
+
+def kat_conditioner():
+    out = np.zeros(12, np.float32)
+    lib().sdmm_ref_kat_conditioner(_f(out))
+    return out
+
+
+def kat_cholesky3(m):
+    m = np.ascontiguousarray(m, np.float32)
+    out = np.zeros((3, 3), np.float32)
+    psd = lib().sdmm_ref_kat_cholesky3(_f(m), _f(out))
+    return out, bool(psd)
+
+
+def kat_categorical(pmf):
+    pmf = np.ascontiguousarray(pmf, np.float32)
+    p = np.zeros_like(pmf)
+    c = np.zeros_like(pmf)
+    ok = lib().sdmm_ref_kat_categorical(len(pmf), _f(pmf), _f(p), _f(c))
+    return p, c, bool(ok)
+
+
+def kat_frame(n):
+    n = np.ascontiguousarray(n, np.float32)
+    out = np.zeros((3, 3), np.float32)
+    lib().sdmm_ref_kat_frame(_f(n), _f(out))
+    return out
+
+
+def joint_to(mean6, point6):
+    mean6 = np.ascontiguousarray(mean6, np.float32)
+    point6 = np.ascontiguousarray(point6, np.float32)
+    t = np.zeros(5, np.float32)
+    ij = np.zeros(1, np.float32)
+    lib().sdmm_ref_joint_to(_f(mean6), _f(point6), _f(t), _f(ij))
+    return t, float(ij[0])
