@@ -1,0 +1,166 @@
+/* include/sdmm_b200.h -- the drop-in boundary of sdmm-b200: a thin C ABI over hand-written
+ * sm_100a CUDA kernels for the data-parallel hot path of SDMM path guiding.
+ *
+ * The reference (anadodik/sdmm-mitsuba) has NO FFI for this path: it is a header-only C++17
+ * template library (sdmm/include/sdmm) called directly from the Mitsuba `sdmm` integrator plugin.
+ * Each entry point below therefore names the reference C++ interface it replaces; the C++ shim
+ * with the reference's own signatures (sdmm_mitsuba_b200/csrc/host_shim.hpp) and the plugin-side
+ * call sites are shown in INTEGRATION.md.  All paths are relative to /root/reference.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative SDMMB_E_* code on failure, never throws;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous
+ *     on that stream unless they take/return HOST data, in which case they synchronise it;
+ *   - pointers named h_* are host pointers, d_* device pointers on the context's device;
+ *   - there is NO CPU fallback: every entry point needs a CUDA device.
+ *
+ * Flat layouts (float32, identical to oracle/ref_driver.cpp so parity tests move the same bytes)
+ *   joint : [cell][32][K]  plane 0 = weight.pmf, 1..6 = tangent_space.mean (x,y,z,dx,dy,dz),
+ *                          7+5r+c = cov(r,c)                       (sdmm/distributions/sdmm.h:118-124)
+ *   em    : [cell][81][K]  plane 0 = stats.weight, 1..5 = stats.mean, 6+5r+c = stats.cov,
+ *                          31+5r+c = cov_prior, 56+5r+c = depth_prior     (sdmm/opt/em.h:124-142)
+ *   scal  : [cell][8] 32-bit words: f32 total_weight, i32 iterations_run, i32 samples_seen,
+ *                          f32 weight_prior, f32 cov_prior_strength, f32 learning_rate, f32 alpha,
+ *                          u32 status (SDMMB_ST_* bits, written by the library)
+ *   samples: point6 = 6 planes (x,y,z,dx,dy,dz) of n_total floats with a common plane stride,
+ *            weight = n_total floats, cell_offsets = n_cells+1 u32 (CSR over cells)
+ *                                                                  (sdmm/opt/data.h:25-57)
+ *   queries: cell_idx[n] u32, pos3 = 3 planes of n, u3 = 3 planes of n with u BY ROLE
+ *            (plane 0: component select, plane 1: Box-Muller radius, plane 2: Box-Muller angle;
+ *            sdmm/distributions/sdmm.h:220, 239-240 leave the order of the two Box-Muller draws
+ *            to the compiler), dir3 = 3 planes of n.
+ */
+#ifndef SDMM_B200_H
+#define SDMM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDMMB_JOINT_PLANES 32
+#define SDMMB_EM_PLANES 81
+#define SDMMB_SCALAR_WORDS 8
+#define SDMMB_QUERY_RECORD_FLOATS 32 /* per component, 30 used */
+#define SDMMB_ESTEP_RECORD_PLANES 28 /* per component planes of the E-step record */
+#define SDMMB_MAX_K 128
+
+/* error codes */
+#define SDMMB_OK 0
+#define SDMMB_E_INVALID (-1)   /* bad argument */
+#define SDMMB_E_CUDA (-2)      /* CUDA runtime error (see sdmmb_last_cuda_error) */
+#define SDMMB_E_NOMEM (-3)     /* device allocation failed */
+#define SDMMB_E_RANGE (-4)     /* cell range / sample count outside the context's capacity */
+#define SDMMB_E_STATE (-5)     /* call order: e.g. em_step before set_samples */
+#define SDMMB_E_NCCL (-6)      /* NCCL missing or returned an error */
+#define SDMMB_E_DATA_FULL (-7) /* as Data::push_back's "Data full." (sdmm/opt/data.h:80) */
+
+/* per-cell status bits (scal word 7); a failed step leaves the model untouched like
+ * sdmm/opt/em.h:237-240 */
+#define SDMMB_ST_STEP_ABORTED 1u  /* normalize_stats returned false (total_weight 0/non-finite) */
+#define SDMMB_ST_CDF_INVALID 2u   /* Categorical::prepare: sum(pmf) <= 1e-20 (categorical.h:97-101) */
+#define SDMMB_ST_NON_PSD 4u       /* some component failed the Cholesky PSD mask (cholesky.h:33) */
+#define SDMMB_ST_COND_INVALID 8u  /* marginal weights invalid after conditioner prepare */
+
+typedef struct sdmmb_ctx sdmmb_ctx;
+
+/* Owns all device memory for `max_cells` cells of K components (K <= 128; internally padded to
+ * 16/32/64/128 with zero-weight components).  Replaces the per-cell SDMMContext bundle
+ * (sdmm/distributions/sdmm_context.h:11-45) owned by the STree. */
+int sdmmb_create(sdmmb_ctx** out, int device, int max_cells, int K);
+int sdmmb_destroy(sdmmb_ctx* ctx);
+const char* sdmmb_get_error_string(int code);
+const char* sdmmb_last_cuda_error(sdmmb_ctx* ctx);
+int sdmmb_num_components(sdmmb_ctx* ctx);
+int sdmmb_max_cells(sdmmb_ctx* ctx);
+
+/* Install mixtures + EM state for cells [first_cell, first_cell+n_cells): what the integrator does
+ * after sdmm::initialize / from_json (sdmm/distributions/sdmm.h:157-160): set_mean (frame) +
+ * prepare_vectorized (Cholesky with +1e-5 pivots, CDF, pmf normalisation; sdmm.h:163-173).
+ * h_em / h_scal may be NULL (zero statistics, learning_rate 0.2, alpha 0.5). */
+int sdmmb_upload_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* h_joint,
+                       const float* h_em, const uint32_t* h_scal, void* stream);
+int sdmmb_download_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_joint, float* h_em,
+                         uint32_t* h_scal, void* stream);
+/* Derived per-component state for parity checks, [cell][38][K] planes exactly as
+ * sdmm_ref_cell_get_derived in oracle/ref_driver.cpp: 0..8 frame.to, 9..33 cov_sqrt, 34 inv_det,
+ * 35 cdf, 36 pmf, 37 psd. */
+int sdmmb_download_derived(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, void* stream);
+
+/* Bind the training samples of cells [first_cell, first_cell+n_cells): replaces Data::push_back /
+ * the data <-> training_data swap (sdmm/opt/data.h:59-102; volpath_sdmm.cpp:290).  The device
+ * variant reads SoA planes already resident in HBM; the host variant copies them first (that copy
+ * is what bench.py's e2e number includes).  Samples are re-laid out on the device into the
+ * kernel's packed 32-byte records by a pack kernel.  h_cell_offsets is always a HOST array of
+ * n_cells+1 entries, relative to the first sample passed. */
+int sdmmb_set_samples(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d_point6,
+                      size_t plane_stride, const float* d_weight, const uint32_t* h_cell_offsets,
+                      void* stream);
+int sdmmb_set_samples_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* h_point6,
+                           size_t plane_stride, const float* h_weight,
+                           const uint32_t* h_cell_offsets, void* stream);
+
+/* n_iters x sdmm::em_step (sdmm/opt/em.h:218-253) on every bound cell of the range, i.e. the body
+ * of the ThreadPool::parallelFor in SDMMVolumetricPathTracer::optimize (volpath_sdmm.cpp:287-311):
+ * E-step + sufficient statistics (em.h:255-314), stepwise blend (:316-328), normalise (:330-351),
+ * update_model (:353-488), prepare_vectorized (sdmm.h:163-173).  If with_conditioner != 0 the
+ * last iteration also runs sdmm::prepare(conditioner, sdmm) (sdmm_conditioner.h:89-100).
+ * d_out_loglik (nullable): [n_iters][n_total] log sum_k pi_k p_k(x_n) under the model ENTERING
+ * each iteration, indexed like the bound samples. */
+int sdmmb_em_step(sdmmb_ctx* ctx, int first_cell, int n_cells, int n_iters, int with_conditioner,
+                  float* d_out_loglik, void* stream);
+
+/* sdmm::prepare(conditioner, joint) alone (sdmm_conditioner.h:89-100, 170-212). */
+int sdmmb_prepare_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, void* stream);
+/* Conditioner internals for parity checks, [cell][38][K] planes exactly as
+ * sdmm_ref_get_conditioner in oracle/ref_driver.cpp. */
+int sdmmb_download_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out,
+                               void* stream);
+
+/* Fused guided query, one per path vertex, as SDMMRenderer::sampleSurface does it
+ * (mitsuba/src/integrators/sdmm/sdmm_proc.cpp:361-372, 419-421, 491-501 -> 539-545):
+ * create_conditional(x) (sdmm_conditioner.h:102-115, 232-248) -> SDMM::sample (sdmm.h:209-273)
+ * -> posterior + hsum (sdmm.h:331-339).  out_valid[i] = 0 when create_conditional failed (all
+ * outputs zero); out_inv_jac[i] == 0 marks a rejected sample (sdmm_proc.cpp:436-439).
+ * `binned` != 0 promises cell_idx is sorted (vertices pre-binned by cell): records are then staged
+ * through shared memory per cell run; otherwise they are gathered through L2. */
+int sdmmb_sample_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+                     const float* d_u3, float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
+                     uint32_t* d_out_comp, uint8_t* d_out_valid, int binned, void* stream);
+/* pdfSurface for a caller-supplied direction (sdmm_proc.cpp:510-590). */
+int sdmmb_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+              const float* d_dir3, float* d_out_pdf, uint8_t* d_out_valid, int binned, void* stream);
+/* Host-buffer variants (H2D of inputs, kernel, D2H of outputs inside the call). */
+int sdmmb_sample_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
+                          const float* h_u3, float* h_out_dir3, float* h_out_pdf,
+                          float* h_out_inv_jac, uint32_t* h_out_comp, uint8_t* h_out_valid,
+                          int binned, void* stream);
+int sdmmb_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
+                   const float* h_dir3, float* h_out_pdf, uint8_t* h_out_valid, int binned,
+                   void* stream);
+
+/* Multi-GPU: cells are partitioned across ranks; after a training iteration every rank needs every
+ * cell's query records.  The context can hold records for a GLOBAL cell range while fitting only
+ * its own slice: records live in one device array of max_cells * K * 32 floats. */
+int sdmmb_query_records(sdmmb_ctx* ctx, float** d_records, size_t* floats_per_cell);
+/* ncclAllGather of the records of equal contiguous slices (cells_per_rank each; rank r owns
+ * cells [r*cells_per_rank, (r+1)*cells_per_rank)).  nccl_comm is an ncclComm_t; libnccl is
+ * resolved at run time (dlopen), so the library has no link-time NCCL dependency. */
+int sdmmb_allgather_records(sdmmb_ctx* ctx, void* nccl_comm, int cells_per_rank, void* stream);
+
+/* Introspection used by bench.py */
+int sdmmb_launch_count(sdmmb_ctx* ctx, uint64_t* out);           /* kernels launched by this ctx */
+int sdmmb_last_estep_ms(sdmmb_ctx* ctx, float* total_ms, int* n_launches); /* CUDA-event time of
+                                                                    the E-step launches of the last
+                                                                    sdmmb_em_step (syncs stream) */
+/* On-device micro-benchmarks that define the FP32 / SFU roofline denominators on THIS GPU:
+ * out[0] = scalar FFMA TFLOP/s, out[1] = packed FFMA2 (fma.rn.f32x2) TFLOP/s,
+ * out[2] = MUFU.EX2 Gop/s, out[3] = SM clock estimate in MHz during the FFMA2 run. */
+int sdmmb_measure_peaks(int device, float* out4);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDMM_B200_H */

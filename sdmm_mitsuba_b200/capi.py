@@ -1,0 +1,96 @@
+"""ctypes binding of the C ABI in include/sdmm_b200.h (libsdmm_b200.so).
+
+This is the ONLY route from Python to the product: there is no CPU or PyTorch fallback.  If the
+library has not been built (`python __graft_entry__.py` / `sdmm_mitsuba_b200._build.build()`),
+loading fails loudly.
+"""
+import ctypes as C
+import os
+
+from . import _build
+
+LIB_PATH = _build.LIB_PATH
+
+JOINT_PLANES = 32
+EM_PLANES = 81
+SCALAR_WORDS = 8
+QUERY_RECORD_FLOATS = 32
+
+ST_STEP_ABORTED, ST_CDF_INVALID, ST_NON_PSD, ST_COND_INVALID = 1, 2, 4, 8
+
+# every symbol include/sdmm_b200.h declares (tests check the library exports exactly these)
+SYMBOLS = [
+    "sdmmb_create", "sdmmb_destroy", "sdmmb_get_error_string", "sdmmb_last_cuda_error",
+    "sdmmb_num_components", "sdmmb_max_cells", "sdmmb_upload_cells", "sdmmb_download_cells",
+    "sdmmb_download_derived", "sdmmb_set_samples", "sdmmb_set_samples_host", "sdmmb_em_step",
+    "sdmmb_prepare_conditioner", "sdmmb_download_conditioner", "sdmmb_sample_pdf", "sdmmb_pdf",
+    "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_query_records", "sdmmb_allgather_records",
+    "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks",
+]
+
+_lib = None
+
+
+class SdmmError(RuntimeError):
+    def __init__(self, code, what, detail=""):
+        self.code = code
+        super().__init__("%s failed: %s (%d)%s" % (what, _errstr(code), code, (": " + detail) if detail else ""))
+
+
+def _errstr(code):
+    try:
+        return lib().sdmmb_get_error_string(code).decode()
+    except Exception:
+        return "?"
+
+
+def lib():
+    """Load libsdmm_b200.so; raises if the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "sdmm_mitsuba_b200: %s is missing -- build the CUDA extension first "
+            "(python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, fp, up, bp = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p  # raw addresses (host or device)
+    i, sz = C.c_int, C.c_size_t
+    L.sdmmb_create.argtypes = [C.POINTER(vp), i, i, i]
+    L.sdmmb_destroy.argtypes = [vp]
+    L.sdmmb_get_error_string.argtypes = [i]
+    L.sdmmb_get_error_string.restype = C.c_char_p
+    L.sdmmb_last_cuda_error.argtypes = [vp]
+    L.sdmmb_last_cuda_error.restype = C.c_char_p
+    L.sdmmb_num_components.argtypes = [vp]
+    L.sdmmb_max_cells.argtypes = [vp]
+    L.sdmmb_upload_cells.argtypes = [vp, i, i, fp, fp, up, vp]
+    L.sdmmb_download_cells.argtypes = [vp, i, i, fp, fp, up, vp]
+    L.sdmmb_download_derived.argtypes = [vp, i, i, fp, vp]
+    L.sdmmb_set_samples.argtypes = [vp, i, i, fp, sz, fp, up, vp]
+    L.sdmmb_set_samples_host.argtypes = [vp, i, i, fp, sz, fp, up, vp]
+    L.sdmmb_em_step.argtypes = [vp, i, i, i, i, fp, vp]
+    L.sdmmb_prepare_conditioner.argtypes = [vp, i, i, vp]
+    L.sdmmb_download_conditioner.argtypes = [vp, i, i, fp, vp]
+    L.sdmmb_sample_pdf.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]
+    L.sdmmb_pdf.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
+    L.sdmmb_sample_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]
+    L.sdmmb_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
+    L.sdmmb_query_records.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
+    L.sdmmb_allgather_records.argtypes = [vp, vp, i, vp]
+    L.sdmmb_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
+    L.sdmmb_last_estep_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i)]
+    L.sdmmb_measure_peaks.argtypes = [i, C.POINTER(C.c_float)]
+    for name in SYMBOLS:
+        if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):
+            getattr(L, name).restype = i
+    _lib = L
+    return L
+
+
+def check(rc, what, ctx=None):
+    if rc != 0:
+        detail = ""
+        if ctx is not None and rc in (-2, -3):
+            detail = lib().sdmmb_last_cuda_error(ctx).decode()
+        raise SdmmError(rc, what, detail)

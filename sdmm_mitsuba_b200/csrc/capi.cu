@@ -1,0 +1,309 @@
+// capi.cu -- the C ABI of include/sdmm_b200.h: context (device memory owner), marshalling between
+// the flat host layouts and the device layouts, work-item construction, kernel launches.
+// No CPU fallback anywhere: every entry point drives the CUDA kernels of this library.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/sdmm_b200.h"
+#include "kernels.h"
+
+using namespace sdmmb;
+
+struct sdmmb_ctx {
+    int device = 0;
+    int max_cells = 0;
+    int K_user = 0;  // components as the caller sees them
+    int K = 0;       // padded to 16 / 32 / 64 / 128 with zero-weight components
+    // model state
+    float* d_joint = nullptr;    // [max_cells][32][K]
+    float* d_em = nullptr;       // [max_cells][81][K]
+    uint32_t* d_scal = nullptr;  // [max_cells][8]
+    float* d_cdf = nullptr;      // [max_cells][K]
+    float* d_erec = nullptr;     // [max_cells][28][K]
+    float* d_qrec = nullptr;     // [max_cells][K][32]
+    // bound samples
+    float4* d_samples = nullptr;
+    size_t samples_cap = 0, n_samples = 0;
+    int bound_first = 0, bound_cells = 0;
+    std::vector<uint32_t> h_item_begin;  // [bound_cells+1] item index per bound cell
+    EItem* d_items = nullptr;
+    uint32_t* d_cell_item_begin = nullptr;
+    uint32_t* d_cell_sample_count = nullptr;
+    float* d_partials = nullptr;
+    float* d_item_scal = nullptr;
+    size_t items_cap = 0, cells_cap = 0, n_items = 0;
+    // staging (grow-only)
+    void* d_stage = nullptr;
+    size_t stage_cap = 0;
+    void* d_stage2 = nullptr;
+    size_t stage2_cap = 0;
+    // bookkeeping
+    uint64_t launches = 0;
+    std::string last_cuda_error;
+    std::vector<cudaEvent_t> ev;  // pairs around the E-step launches of the last em_step
+    int ev_used = 0;
+    uint32_t item_samples = 1024;
+    // nccl (resolved lazily)
+    void* nccl_handle = nullptr;
+    int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*nccl_user_rank)(void*, int*) = nullptr;
+};
+
+namespace {
+
+int pad_k(int k) {
+    if (k <= 16) return 16;
+    if (k <= 32) return 32;
+    if (k <= 64) return 64;
+    return 128;
+}
+
+int cuda_fail(sdmmb_ctx* c, cudaError_t e) {
+    if (c) c->last_cuda_error = cudaGetErrorString(e);
+    return (e == cudaErrorMemoryAllocation) ? SDMMB_E_NOMEM : SDMMB_E_CUDA;
+}
+
+#define CK(call)                                          \
+    do {                                                  \
+        cudaError_t _e = (call);                          \
+        if (_e != cudaSuccess) return cuda_fail(ctx, _e); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+int ensure(sdmmb_ctx* ctx, void** p, size_t* cap, size_t bytes) {
+    if (bytes <= *cap) return SDMMB_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    size_t want = bytes + bytes / 8;
+    CK(cudaMalloc(p, want));
+    *cap = want;
+    return SDMMB_OK;
+}
+
+bool range_ok(sdmmb_ctx* ctx, int first, int n) {
+    return first >= 0 && n >= 0 && (long long)first + n <= ctx->max_cells;
+}
+
+MStepArgs base_mstep_args(sdmmb_ctx* ctx, int first_cell, int n_cells, int mode) {
+    MStepArgs a{};
+    a.K = ctx->K;
+    a.first_cell = first_cell;
+    a.n_cells = n_cells;
+    a.mode = mode;
+    a.joint = ctx->d_joint;
+    a.em = ctx->d_em;
+    a.scal = ctx->d_scal;
+    a.cdf = ctx->d_cdf;
+    a.erec = ctx->d_erec;
+    a.qrec = ctx->d_qrec;
+    return a;
+}
+
+// host [cell][planes][K_user] -> padded [cell][planes][K]; `fill` per plane for the padding lanes
+void pad_planes(const float* src, float* dst, int n_cells, int planes, int Ku, int K,
+                const float* plane_fill) {
+    for (int c = 0; c < n_cells; ++c)
+        for (int p = 0; p < planes; ++p) {
+            float* d = dst + ((size_t)c * planes + p) * K;
+            if (src) std::memcpy(d, src + ((size_t)c * planes + p) * Ku, sizeof(float) * Ku);
+            else for (int k = 0; k < Ku; ++k) d[k] = 0.f;
+            for (int k = Ku; k < K; ++k) d[k] = plane_fill ? plane_fill[p] : 0.f;
+        }
+}
+
+void strip_planes(const float* src, float* dst, int n_cells, int planes, int Ku, int K) {
+    for (int c = 0; c < n_cells; ++c)
+        for (int p = 0; p < planes; ++p)
+            std::memcpy(dst + ((size_t)c * planes + p) * Ku, src + ((size_t)c * planes + p) * K,
+                        sizeof(float) * Ku);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* sdmmb_get_error_string(int code) {
+    switch (code) {
+        case SDMMB_OK: return "ok";
+        case SDMMB_E_INVALID: return "invalid argument";
+        case SDMMB_E_CUDA: return "CUDA runtime error";
+        case SDMMB_E_NOMEM: return "device allocation failed";
+        case SDMMB_E_RANGE: return "cell range or sample count outside the context's capacity";
+        case SDMMB_E_STATE: return "call order: samples not bound for this cell range";
+        case SDMMB_E_NCCL: return "NCCL missing or returned an error";
+        case SDMMB_E_DATA_FULL: return "Data full.";
+        default: return "unknown error";
+    }
+}
+
+const char* sdmmb_last_cuda_error(sdmmb_ctx* ctx) { return ctx ? ctx->last_cuda_error.c_str() : ""; }
+int sdmmb_num_components(sdmmb_ctx* ctx) { return ctx ? ctx->K_user : SDMMB_E_INVALID; }
+int sdmmb_max_cells(sdmmb_ctx* ctx) { return ctx ? ctx->max_cells : SDMMB_E_INVALID; }
+
+int sdmmb_create(sdmmb_ctx** out, int device, int max_cells, int K) {
+    if (!out || max_cells <= 0 || K <= 0 || K > SDMMB_MAX_K) return SDMMB_E_INVALID;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return SDMMB_E_CUDA;
+    sdmmb_ctx* ctx = new (std::nothrow) sdmmb_ctx();
+    if (!ctx) return SDMMB_E_NOMEM;
+    ctx->device = device;
+    ctx->max_cells = max_cells;
+    ctx->K_user = K;
+    ctx->K = pad_k(K);
+    if (const char* s = std::getenv("SDMMB_ITEM_SAMPLES")) {
+        long v = std::atol(s);
+        if (v >= 32) ctx->item_samples = (uint32_t)v;
+    }
+    DeviceGuard g(device);
+    const size_t ck = (size_t)max_cells * ctx->K;
+    cudaError_t e;
+    if ((e = cudaMalloc(&ctx->d_joint, ck * JOINT_PLANES * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_em, ck * EM_PLANES * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_scal, (size_t)max_cells * SCALAR_WORDS * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_cdf, ck * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_erec, ck * EREC_PLANES * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_qrec, ck * QREC_FLOATS * 4)) != cudaSuccess) {
+        int rc = cuda_fail(nullptr, e);
+        sdmmb_destroy(ctx);
+        return rc;
+    }
+    cudaMemset(ctx->d_joint, 0, ck * JOINT_PLANES * 4);
+    cudaMemset(ctx->d_em, 0, ck * EM_PLANES * 4);
+    cudaMemset(ctx->d_scal, 0, (size_t)max_cells * SCALAR_WORDS * 4);
+    cudaMemset(ctx->d_cdf, 0, ck * 4);
+    cudaMemset(ctx->d_erec, 0, ck * EREC_PLANES * 4);
+    cudaMemset(ctx->d_qrec, 0, ck * QREC_FLOATS * 4);
+    *out = ctx;
+    return SDMMB_OK;
+}
+
+int sdmmb_destroy(sdmmb_ctx* ctx) {
+    if (!ctx) return SDMMB_OK;
+    DeviceGuard g(ctx->device);
+    cudaFree(ctx->d_joint); cudaFree(ctx->d_em); cudaFree(ctx->d_scal); cudaFree(ctx->d_cdf);
+    cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
+    cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
+    cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2);
+    for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
+    delete ctx;
+    return SDMMB_OK;
+}
+
+int sdmmb_upload_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* h_joint,
+                       const float* h_em, const uint32_t* h_scal, void* stream) {
+    if (!ctx || !h_joint) return SDMMB_E_INVALID;
+    if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
+    if (n_cells == 0) return SDMMB_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int K = ctx->K, Ku = ctx->K_user;
+    // padding components: zero weight, direction +z, identity covariance (Cholesky stays finite)
+    float jfill[JOINT_PLANES] = {0};
+    jfill[6] = 1.f;
+    for (int i = 0; i < 5; ++i) jfill[7 + 6 * i] = 1.f;
+    std::vector<float> hj((size_t)n_cells * JOINT_PLANES * K), he((size_t)n_cells * EM_PLANES * K);
+    pad_planes(h_joint, hj.data(), n_cells, JOINT_PLANES, Ku, K, jfill);
+    pad_planes(h_em, he.data(), n_cells, EM_PLANES, Ku, K, nullptr);
+    std::vector<uint32_t> hs((size_t)n_cells * SCALAR_WORDS, 0u);
+    for (int c = 0; c < n_cells; ++c) {
+        uint32_t* s = hs.data() + (size_t)c * SCALAR_WORDS;
+        if (h_scal) std::memcpy(s, h_scal + (size_t)c * SCALAR_WORDS, SCALAR_WORDS * 4);
+        else {
+            float lr = 0.2f, al = 0.5f;  // R: sdmm/opt/em.h:137-138
+            std::memcpy(&s[5], &lr, 4);
+            std::memcpy(&s[6], &al, 4);
+        }
+        s[7] = 0;
+    }
+    CK(cudaMemcpyAsync(ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K, hj.data(), hj.size() * 4,
+                       cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_em + (size_t)first_cell * EM_PLANES * K, he.data(), he.size() * 4,
+                       cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_scal + (size_t)first_cell * SCALAR_WORDS, hs.data(), hs.size() * 4,
+                       cudaMemcpyHostToDevice, st));
+    MStepArgs a = base_mstep_args(ctx, first_cell, n_cells, 4);
+    CK(launch_mstep(a, st));
+    ctx->launches += 1;
+    CK(cudaStreamSynchronize(st));  // the pageable staging vectors die at return
+    return SDMMB_OK;
+}
+
+int sdmmb_download_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_joint, float* h_em,
+                         uint32_t* h_scal, void* stream) {
+    if (!ctx) return SDMMB_E_INVALID;
+    if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
+    if (n_cells == 0) return SDMMB_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int K = ctx->K, Ku = ctx->K_user;
+    std::vector<float> tmp;
+    if (h_joint) {
+        tmp.resize((size_t)n_cells * JOINT_PLANES * K);
+        CK(cudaMemcpyAsync(tmp.data(), ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K, tmp.size() * 4,
+                           cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        strip_planes(tmp.data(), h_joint, n_cells, JOINT_PLANES, Ku, K);
+    }
+    if (h_em) {
+        tmp.resize((size_t)n_cells * EM_PLANES * K);
+        CK(cudaMemcpyAsync(tmp.data(), ctx->d_em + (size_t)first_cell * EM_PLANES * K, tmp.size() * 4,
+                           cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        strip_planes(tmp.data(), h_em, n_cells, EM_PLANES, Ku, K);
+    }
+    if (h_scal) {
+        CK(cudaMemcpyAsync(h_scal, ctx->d_scal + (size_t)first_cell * SCALAR_WORDS,
+                           (size_t)n_cells * SCALAR_WORDS * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    return SDMMB_OK;
+}
+
+static int readout38(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, void* stream, bool cond) {
+    if (!ctx || !h_out) return SDMMB_E_INVALID;
+    if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
+    if (n_cells == 0) return SDMMB_OK;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int K = ctx->K, Ku = ctx->K_user;
+    const size_t bytes = (size_t)n_cells * 38 * K * 4;
+    int rc = ensure(ctx, &ctx->d_stage, &ctx->stage_cap, bytes);
+    if (rc) return rc;
+    if (cond) CK(launch_conditioner_readout(ctx->d_joint, ctx->d_qrec, first_cell, n_cells, K, (float*)ctx->d_stage, st));
+    else CK(launch_derived_readout(ctx->d_joint, ctx->d_cdf, first_cell, n_cells, K, (float*)ctx->d_stage, st));
+    ctx->launches += 1;
+    std::vector<float> tmp((size_t)n_cells * 38 * K);
+    CK(cudaMemcpyAsync(tmp.data(), ctx->d_stage, bytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    strip_planes(tmp.data(), h_out, n_cells, 38, Ku, K);
+    return SDMMB_OK;
+}
+
+int sdmmb_download_derived(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, void* stream) {
+    return readout38(ctx, first_cell, n_cells, h_out, stream, false);
+}
+int sdmmb_download_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, void* stream) {
+    return readout38(ctx, first_cell, n_cells, h_out, stream, true);
+}
+
+}  // extern "C"
+
+#include "capi_part2.inc"

@@ -1,0 +1,104 @@
+// kernels.h -- device data layouts and launcher declarations shared by the kernel translation
+// units and the C ABI (capi.cu).  Internal; the public boundary is include/sdmm_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace sdmmb {
+
+constexpr int JOINT_PLANES = 32;
+constexpr int EM_PLANES = 81;
+constexpr int SCALAR_WORDS = 8;
+
+// E-step record: 28 planes of K floats per cell ([cell][plane][K], lanes read consecutive k)
+constexpr int EREC_NMU = 0;   // 3: -mean position
+constexpr int EREC_R = 3;     // 9: frame.to, row-major
+constexpr int EREC_W = 12;    // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major
+constexpr int EREC_NLC = 27;  // 1: -log2(pmf * inv_cov_sqrt_det * (2 pi)^-5/2)
+constexpr int EREC_PLANES = 28;
+
+// E-step partial statistics per item: 21 planes of K floats
+//   0 = sum g, 1..5 = sum g t_i, 6 + i(i+1)/2 + j = sum g t_i t_j (i >= j)
+constexpr int ESTAT_PLANES = 21;
+
+// Query record: 32 floats per component, [cell][k][32] (one 128-byte line per component)
+constexpr int QREC_MU = 0;     // 3: marginal mean
+constexpr int QREC_WA = 3;     // 6: sqrt(log2(e)/2) * L_aa^-1 lower triangle (00,10,11,20,21,22)
+constexpr int QREC_NLCA = 9;   // 1: -log2(pmf_marginal * inv_det_aa * (2 pi)^-3/2)
+constexpr int QREC_M = 10;     // 6: mean_transform 2x3 row-major
+constexpr int QREC_R = 16;     // 9: conditional frame.to row-major (from = transpose)
+constexpr int QREC_LC = 25;    // 3: conditional cov_sqrt (00,10,11)
+constexpr int QREC_WC = 28;    // 3: sqrt(log2(e)/2) * L_c^-1 (00,10,11)
+constexpr int QREC_NLCC = 31;  // 1: -log2(inv_det_c * (2 pi)^-1)
+constexpr int QREC_FLOATS = 32;
+
+constexpr uint32_t ST_STEP_ABORTED = 1u, ST_CDF_INVALID = 2u, ST_NON_PSD = 4u, ST_COND_INVALID = 8u;
+
+constexpr int MSTEP_THREADS = 128;
+
+// One E-step work item = a contiguous run of one cell's samples, processed by one CTA.
+struct EItem {
+    uint32_t cell;   // absolute cell index (into erec)
+    uint32_t begin;  // absolute sample index range in the packed sample array
+    uint32_t end;
+    uint32_t pad;
+};
+
+struct EStepLaunch {
+    int K;
+    int n_items;
+    const float4* samples;  // packed records, 2 float4 per sample
+    const EItem* items;
+    const float* erec;
+    float* partials;   // [n_items][21][K]
+    float* item_scal;  // [n_items][2]: sum of weights, skipped-sample count (int bits)
+    float* out_loglik; // nullable, indexed by absolute sample index
+};
+
+struct MStepArgs {
+    int K;
+    int first_cell, n_cells;
+    int mode;  // bit0 EM update, bit1 conditioner records, bit2 normalise pmf (upload)
+    float* joint;
+    float* em;
+    uint32_t* scal;
+    float* cdf;
+    float* erec;
+    float* qrec;
+    const float* partials;
+    const float* item_scal;
+    const uint32_t* cell_item_begin;    // [n_cells+1] absolute item indices, entry 0 = this launch's first cell
+    uint32_t item_base;                 // item index that `partials` / `item_scal` start at
+    const uint32_t* cell_sample_count;  // [n_cells]
+};
+
+struct QueryLaunch {
+    int K;
+    size_t n;
+    const float* qrec;
+    const uint32_t* cell_idx;
+    const float* pos3;   // 3 planes of n
+    const float* u3;     // 3 planes of n (sample mode) or nullptr
+    const float* dir3;   // 3 planes of n (pdf-only mode) or nullptr
+    float* out_dir3;
+    float* out_pdf;
+    float* out_inv_jac;
+    uint32_t* out_comp;
+    uint8_t* out_valid;
+    int binned;
+    int max_cells;
+};
+
+cudaError_t launch_pack(const float* point6, size_t stride, const float* weight, float4* rec, size_t n,
+                        cudaStream_t st);
+cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st);
+cudaError_t launch_mstep(const MStepArgs& a, cudaStream_t st);
+cudaError_t launch_derived_readout(const float* joint, const float* cdf, int first_cell, int n_cells, int K,
+                                   float* out, cudaStream_t st);
+cudaError_t launch_conditioner_readout(const float* joint, const float* qrec, int first_cell, int n_cells,
+                                       int K, float* out, cudaStream_t st);
+cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st);
+cudaError_t measure_peaks(float* out4);
+
+}  // namespace sdmmb

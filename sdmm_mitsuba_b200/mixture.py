@@ -1,0 +1,249 @@
+"""Host-side mirror of the reference's sdmm EM / mixture interface for the hot path, batched over
+spatial cells and backed ONLY by the CUDA library (capi.py -> libsdmm_b200.so).
+
+Reference interface mirrored (paths relative to /root/reference):
+  SDMMContext bundle per cell            sdmm/include/sdmm/distributions/sdmm_context.h:11-45
+  Data::push_back / clear                sdmm/include/sdmm/opt/data.h:59-102           -> set_samples
+  sdmm::em_step                          sdmm/include/sdmm/opt/em.h:218-253            -> em_step
+  sdmm::prepare(conditioner, joint)      sdmm/include/sdmm/distributions/sdmm_conditioner.h:89-100 -> prepare
+  sdmm::create_conditional + SDMM::sample + SDMM::posterior (per vertex, sdmm_proc.cpp:361-372,
+  419-421, 539-545)                                                                    -> sample_pdf / pdf
+
+NumPy arrays take the host-buffer entry points (copies inside the call); torch CUDA tensors take the
+device-pointer entry points on torch's current stream.  PyTorch is only used for device memory,
+streams and torch.distributed plumbing.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import EM_PLANES, JOINT_PLANES, QUERY_RECORD_FLOATS, SCALAR_WORDS, check
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _np(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+def _hp(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def _stream(device):
+    import torch
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class SDMMCells:
+    """A batch of per-cell SDMM contexts (joint mixture + EM state + conditioner) resident on one GPU."""
+
+    def __init__(self, max_cells, K, device=0):
+        self._L = capi.lib()
+        self.max_cells, self.K, self.device = int(max_cells), int(K), int(device)
+        h = C.c_void_p()
+        check(self._L.sdmmb_create(C.byref(h), self.device, self.max_cells, self.K), "sdmmb_create")
+        self._h = h
+        self.n_samples = 0
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.sdmmb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- model state -----------------------------------------------------------------------
+    def upload(self, joint, em=None, scal=None, first_cell=0):
+        """joint [C,32,K] f32, em [C,81,K] f32 or None, scal [C,8] u32 words or None.
+        Runs set_mean + prepare_vectorized (sdmm.h:157-173) on the device."""
+        joint = _np(joint, np.float32)
+        n = joint.shape[0]
+        assert joint.shape == (n, JOINT_PLANES, self.K), joint.shape
+        em = _np(em, np.float32) if em is not None else None
+        scal = _np(scal, np.uint32) if scal is not None else None
+        if em is not None:
+            assert em.shape == (n, EM_PLANES, self.K), em.shape
+        if scal is not None:
+            assert scal.shape == (n, SCALAR_WORDS), scal.shape
+        check(self._L.sdmmb_upload_cells(self._h, first_cell, n, _hp(joint), _hp(em), _hp(scal), None),
+              "sdmmb_upload_cells", self._h)
+
+    def download(self, first_cell=0, n_cells=None):
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        joint = np.zeros((n, JOINT_PLANES, self.K), np.float32)
+        em = np.zeros((n, EM_PLANES, self.K), np.float32)
+        scal = np.zeros((n, SCALAR_WORDS), np.uint32)
+        check(self._L.sdmmb_download_cells(self._h, first_cell, n, _hp(joint), _hp(em), _hp(scal), None),
+              "sdmmb_download_cells", self._h)
+        return joint, em, scal
+
+    def status(self, first_cell=0, n_cells=None):
+        return self.download(first_cell, n_cells)[2][:, 7].copy()
+
+    def derived(self, first_cell=0, n_cells=None):
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        out = np.zeros((n, 38, self.K), np.float32)
+        check(self._L.sdmmb_download_derived(self._h, first_cell, n, _hp(out), None), "sdmmb_download_derived", self._h)
+        return out
+
+    def conditioner(self, first_cell=0, n_cells=None):
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        out = np.zeros((n, 38, self.K), np.float32)
+        check(self._L.sdmmb_download_conditioner(self._h, first_cell, n, _hp(out), None),
+              "sdmmb_download_conditioner", self._h)
+        return out
+
+    # ---- training ---------------------------------------------------------------------------
+    def set_samples(self, point6, weight, cell_offsets, first_cell=0):
+        """point6 [6,N] (x,y,z,dx,dy,dz planes), weight [N], cell_offsets [C+1] (host, u32)."""
+        off = _np(np.asarray(cell_offsets), np.uint32)
+        n_cells = off.shape[0] - 1
+        if _is_torch(point6):
+            assert point6.is_cuda and weight.is_cuda and point6.dtype.is_floating_point
+            assert point6.is_contiguous() and weight.is_contiguous() and point6.shape[0] == 6
+            self._keep = (point6, weight)
+            check(self._L.sdmmb_set_samples(self._h, first_cell, n_cells, C.c_void_p(point6.data_ptr()),
+                                            point6.shape[1], C.c_void_p(weight.data_ptr()), _hp(off),
+                                            _stream(self.device)), "sdmmb_set_samples", self._h)
+        else:
+            point6 = _np(point6, np.float32)
+            weight = _np(weight, np.float32)
+            assert point6.shape[0] == 6 and weight.shape[0] == point6.shape[1]
+            check(self._L.sdmmb_set_samples_host(self._h, first_cell, n_cells, _hp(point6), point6.shape[1],
+                                                 _hp(weight), _hp(off), None), "sdmmb_set_samples_host", self._h)
+        self.n_samples = int(off[-1] - off[0])
+        self._bound = (first_cell, n_cells)
+
+    def em_step(self, n_iters=1, first_cell=None, n_cells=None, with_conditioner=True, want_loglik=False):
+        """n_iters x sdmm::em_step on every bound cell (+ sdmm::prepare of the conditioner after the
+        last one).  want_loglik -> torch tensor [n_iters, N] of per-sample log-likelihoods."""
+        if first_cell is None:
+            first_cell, n_cells = self._bound
+        ll = None
+        ptr = None
+        st = None
+        if want_loglik:
+            import torch
+            ll = torch.empty((n_iters, self.n_samples), dtype=torch.float32, device="cuda:%d" % self.device)
+            ptr = C.c_void_p(ll.data_ptr())
+            st = _stream(self.device)
+        else:
+            try:
+                st = _stream(self.device)
+            except Exception:
+                st = None
+        check(self._L.sdmmb_em_step(self._h, first_cell, n_cells, n_iters, 1 if with_conditioner else 0, ptr, st),
+              "sdmmb_em_step", self._h)
+        return ll
+
+    def prepare(self, first_cell=0, n_cells=None):
+        """sdmm::prepare(conditioner, sdmm) for a cell range."""
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, None), "sdmmb_prepare_conditioner", self._h)
+
+    # ---- queries ------------------------------------------------------------------------------
+    def sample_pdf(self, cell_idx, pos3, u3, binned=False):
+        """Per vertex: create_conditional(x) -> sample(u) -> posterior(omega) summed.
+        u3 planes by role: select, Box-Muller radius, Box-Muller angle."""
+        if _is_torch(pos3):
+            import torch
+            n = pos3.shape[1]
+            dev = pos3.device
+            out = dict(dir=torch.empty((3, n), dtype=torch.float32, device=dev),
+                       pdf=torch.empty(n, dtype=torch.float32, device=dev),
+                       inv_jac=torch.empty(n, dtype=torch.float32, device=dev),
+                       comp=torch.empty(n, dtype=torch.int32, device=dev),
+                       valid=torch.empty(n, dtype=torch.uint8, device=dev))
+            check(self._L.sdmmb_sample_pdf(self._h, n, C.c_void_p(cell_idx.data_ptr()), C.c_void_p(pos3.data_ptr()),
+                                           C.c_void_p(u3.data_ptr()), C.c_void_p(out["dir"].data_ptr()),
+                                           C.c_void_p(out["pdf"].data_ptr()), C.c_void_p(out["inv_jac"].data_ptr()),
+                                           C.c_void_p(out["comp"].data_ptr()), C.c_void_p(out["valid"].data_ptr()),
+                                           1 if binned else 0, _stream(self.device)), "sdmmb_sample_pdf", self._h)
+            return out
+        cell_idx = _np(cell_idx, np.uint32)
+        pos3 = _np(pos3, np.float32)
+        u3 = _np(u3, np.float32)
+        n = pos3.shape[1]
+        out = dict(dir=np.zeros((3, n), np.float32), pdf=np.zeros(n, np.float32), inv_jac=np.zeros(n, np.float32),
+                   comp=np.zeros(n, np.uint32), valid=np.zeros(n, np.uint8))
+        check(self._L.sdmmb_sample_pdf_host(self._h, n, _hp(cell_idx), _hp(pos3), _hp(u3), _hp(out["dir"]),
+                                            _hp(out["pdf"]), _hp(out["inv_jac"]), _hp(out["comp"]),
+                                            _hp(out["valid"]), 1 if binned else 0, None),
+              "sdmmb_sample_pdf_host", self._h)
+        return out
+
+    def pdf(self, cell_idx, pos3, dir3, binned=False):
+        """pdfSurface's mixture term for caller-supplied directions."""
+        cell_idx = _np(cell_idx, np.uint32)
+        pos3 = _np(pos3, np.float32)
+        dir3 = _np(dir3, np.float32)
+        n = pos3.shape[1]
+        out_pdf = np.zeros(n, np.float32)
+        out_valid = np.zeros(n, np.uint8)
+        check(self._L.sdmmb_pdf_host(self._h, n, _hp(cell_idx), _hp(pos3), _hp(dir3), _hp(out_pdf), _hp(out_valid),
+                                     1 if binned else 0, None), "sdmmb_pdf_host", self._h)
+        return out_pdf, out_valid
+
+    # ---- multi-GPU / introspection --------------------------------------------------------------
+    def query_records(self):
+        """Zero-copy torch view [max_cells, K_padded, 32] of the device-resident query records."""
+        import torch
+        p, n = C.c_void_p(), C.c_size_t()
+        check(self._L.sdmmb_query_records(self._h, C.byref(p), C.byref(n)), "sdmmb_query_records")
+        kp = n.value // QUERY_RECORD_FLOATS
+
+        class _Ext:
+            pass
+
+        ext = _Ext()
+        ext.__cuda_array_interface__ = dict(shape=(self.max_cells, kp, QUERY_RECORD_FLOATS), typestr="<f4",
+                                            data=(p.value, False), version=2)
+        self._ext = ext
+        return torch.as_tensor(ext, device="cuda:%d" % self.device)
+
+    def allgather_records(self, cells_per_rank, group=None):
+        """After a training iteration: every rank contributes the records of its contiguous slice
+        (rank r owns cells [r*cells_per_rank, (r+1)*cells_per_rank)).  NCCL all-gather, in place."""
+        import torch.distributed as dist
+        rec = self.query_records()
+        world = dist.get_world_size(group)
+        flat = rec[: world * cells_per_rank].reshape(-1)
+        rank = dist.get_rank(group)
+        per = flat.numel() // world
+        dist.all_gather_into_tensor(flat, flat[rank * per:(rank + 1) * per], group=group)
+
+    def launch_count(self):
+        v = C.c_uint64()
+        check(self._L.sdmmb_launch_count(self._h, C.byref(v)), "sdmmb_launch_count")
+        return int(v.value)
+
+    def last_estep_ms(self):
+        ms, n = C.c_float(), C.c_int()
+        check(self._L.sdmmb_last_estep_ms(self._h, C.byref(ms), C.byref(n)), "sdmmb_last_estep_ms", self._h)
+        return float(ms.value), int(n.value)
+
+
+def measure_peaks(device=0):
+    """FP32 scalar / packed TFLOP/s, MUFU Gop/s and SM MHz measured by on-device micro-benchmarks."""
+    out = (C.c_float * 4)()
+    check(capi.lib().sdmmb_measure_peaks(device, out), "sdmmb_measure_peaks")
+    return dict(fp32_ffma_tflops=out[0], fp32_ffma2_tflops=out[1], mufu_gops=out[2], sm_mhz=out[3])
+
+
+# reference-named free functions (sdmm::em_step / sdmm::prepare)
+def em_step(cells, n_iters=1, **kw):
+    return cells.em_step(n_iters=n_iters, **kw)
+
+
+def prepare(cells, first_cell=0, n_cells=None):
+    return cells.prepare(first_cell, n_cells)

@@ -1,0 +1,174 @@
+"""GPU parity of the query path (conditioner prepare + fused guided sample/pdf kernel) against the
+oracle(s).  Component selection must be identical for identical uniforms away from CDF ties."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+PDF_RTOL = 1e-3      # conditional pdf: a sum of K exp() terms of fitted parameters
+TIE_DELTA = 2e-5     # |u0 - cdf[k]| below this counts as a tie (K * 2^-22 relative)
+
+
+def _oracles():
+    from oracle import portbind, refbind
+    out = [("port", portbind.PortCells)]
+    if refbind.available():
+        out.append(("ref", refbind.RefCells))
+    return out
+
+
+def _fitted(C, K, N=1024, iters=3, seed=0):
+    """Fit with the ORACLE port so GPU and oracle query the very same mixtures."""
+    from oracle import portbind
+    from sdmm_mitsuba_b200 import synth
+    point6, weight, off = synth.make_samples(C, N, seed=seed)
+    joint, em, scal = synth.make_initial_model(C, K, seed=seed + 1)
+    o = portbind.PortCells(C, K)
+    o.set(joint, em, scal)
+    o.em_step(off, point6, weight, iters)
+    return o.get()
+
+
+@pytest.mark.parametrize("K", [16, 64, 128])
+def test_conditioner_prepare_parity(K):
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C = 3
+    joint, em, scal = _fitted(C, K, seed=K)
+    cells = SDMMCells(C, K)
+    cells.upload(joint, em, scal)
+    cells.prepare()
+    g = cells.conditioner()
+    for name, cls in _oracles():
+        o = cls(C, K)
+        o.set(joint, em, scal)
+        o.prepare_conditioner()
+        r = o.conditioner()
+        np.testing.assert_allclose(g[:, 0:3], r[:, 0:3], atol=1e-6, err_msg=name + " marginal mean")
+        np.testing.assert_allclose(g[:, 3:12], r[:, 3:12], rtol=1e-4, atol=1e-6, err_msg=name + " L_aa")
+        np.testing.assert_allclose(g[:, 12], r[:, 12], rtol=1e-4, err_msg=name + " inv_det_a")
+        np.testing.assert_allclose(g[:, 13], r[:, 13], rtol=1e-4, atol=1e-8, err_msg=name + " marginal pmf")
+        scale = np.abs(r[:, 14:20]).max(axis=1, keepdims=True)
+        assert (np.abs(g[:, 14:20] - r[:, 14:20]) / scale).max() < 1e-3, name + " mean_transform"
+        np.testing.assert_allclose(g[:, 20:29], r[:, 20:29], atol=2e-6, err_msg=name + " frame")
+        cs = np.abs(r[:, 34:38]).max(axis=1, keepdims=True)
+        assert (np.abs(g[:, 34:38] - r[:, 34:38]) / cs).max() < 1e-3, name + " cond cov"
+        ls = np.abs(r[:, 29:33]).max(axis=1, keepdims=True)
+        assert (np.abs(g[:, 29:33] - r[:, 29:33]) / ls).max() < 1e-3, name + " cond L"
+        np.testing.assert_allclose(g[:, 33], r[:, 33], rtol=1e-3, err_msg=name + " inv_det_c")
+
+
+def _compare_queries(name, g, r, o, cell, pos3, u3, K):
+    np.testing.assert_array_equal(g["valid"], r["valid"], err_msg=name)
+    v = r["valid"].astype(bool)
+    diff = np.nonzero((g["comp"] != r["comp"]) & v)[0]
+    # every disagreement must sit on a CDF tie
+    for i in diff[:200]:
+        pmf, cdf, ok = o.conditional_weights(int(cell[i]), pos3[:, i])
+        assert ok
+        assert np.abs(cdf - u3[0, i]).min() < TIE_DELTA, (name, i, u3[0, i], cdf[max(0, g["comp"][i] - 1):g["comp"][i] + 2])
+    same = v & (g["comp"] == r["comp"])
+    assert same.sum() >= 0.999 * v.sum(), (name, same.sum(), v.sum())
+    ang = np.arccos(np.clip((g["dir"][:, same] * r["dir"][:, same]).sum(axis=0), -1, 1))
+    assert ang.max() < 2e-3, (name, "direction", ang.max())
+    np.testing.assert_allclose(g["inv_jac"][same], r["inv_jac"][same], rtol=1e-4, atol=1e-6, err_msg=name)
+    # the pdf is evaluated at slightly different directions; compare where it is not negligible
+    big = same & (r["pdf"] > 1e-6)
+    rel = np.abs(g["pdf"][big] - r["pdf"][big]) / r["pdf"][big]
+    assert np.quantile(rel, 0.999) < 5e-3 and np.median(rel) < 1e-4, (name, np.quantile(rel, [0.5, 0.99, 0.999, 1.0]))
+    return len(diff) / max(1, v.sum())
+
+
+@pytest.mark.parametrize("K,binned", [(16, True), (64, True), (64, False), (128, True)])
+def test_sample_pdf_parity(K, binned):
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, n = 6, 20000
+    joint, em, scal = _fitted(C, K, seed=10 + K)
+    cells = SDMMCells(C, K)
+    cells.upload(joint, em, scal)
+    cells.prepare()
+    cell, pos3, u3 = synth.make_queries(n, C, seed=4, binned=binned)
+    g = cells.sample_pdf(cell, pos3, u3, binned=binned)
+    for name, cls in _oracles():
+        o = cls(C, K)
+        o.set(joint, em, scal)
+        o.prepare_conditioner()
+        r, _ = o.sample_pdf(cell, pos3, u3)
+        _compare_queries(name, g, r, o, cell, pos3, u3, K)
+
+
+def test_pdf_only_parity_and_binned_equals_gather():
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, K, n = 5, 64, 8000
+    joint, em, scal = _fitted(C, K, seed=31)
+    cells = SDMMCells(C, K)
+    cells.upload(joint, em, scal)
+    cells.prepare()
+    cell, pos3, _ = synth.make_queries(n, C, seed=6, binned=True)
+    rng = np.random.default_rng(8)
+    d = rng.normal(size=(3, n)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=0, keepdims=True)
+    p_b, v_b = cells.pdf(cell, pos3, d, binned=True)
+    p_g, v_g = cells.pdf(cell, pos3, d, binned=False)
+    np.testing.assert_array_equal(p_b, p_g)
+    np.testing.assert_array_equal(v_b, v_g)
+    for name, cls in _oracles():
+        o = cls(C, K)
+        o.set(joint, em, scal)
+        o.prepare_conditioner()
+        p, v, _ = o.pdf(cell, pos3, d)
+        np.testing.assert_array_equal(v_b, v)
+        big = p > 1e-6
+        rel = np.abs(p_b[big] - p[big]) / p[big]
+        assert rel.max() < PDF_RTOL, (name, rel.max())
+
+
+def test_query_edge_cases():
+    """Far-away vertex -> invalid conditional (all outputs zero, valid = 0); out-of-range cell
+    index -> invalid; empty batch is a no-op; a single run shorter than a warp."""
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, K = 2, 16
+    joint, em, scal = _fitted(C, K, seed=3)
+    cells = SDMMCells(C, K)
+    cells.upload(joint, em, scal)
+    cells.prepare()
+    cell = np.array([0, 0, 1, 7], np.uint32)
+    pos3 = np.array([[0.5, 1e6, 0.5, 0.5], [0.5, 1e6, 0.5, 0.5], [0.5, 1e6, 0.5, 0.5]], np.float32)
+    u3 = np.full((3, 4), 0.5, np.float32)
+    for binned in (True, False):
+        g = cells.sample_pdf(cell, pos3, u3, binned=binned)
+        assert list(g["valid"]) == [1, 0, 1, 0]
+        assert g["pdf"][1] == 0 and g["inv_jac"][1] == 0 and (g["dir"][:, 1] == 0).all()
+        assert g["pdf"][3] == 0 and g["comp"][3] == 0
+        np.testing.assert_allclose(np.linalg.norm(g["dir"][:, [0, 2]], axis=0), 1.0, atol=1e-5)
+    e = cells.sample_pdf(np.zeros(0, np.uint32), np.zeros((3, 0), np.float32), np.zeros((3, 0), np.float32))
+    assert e["pdf"].shape == (0,)
+
+
+def test_full_size_query_properties():
+    """1M vertices over 256 fitted cells (BASELINE config-3 shape at reduced count): directions are
+    unit vectors, pdfs finite and non-negative, and E[1/pdf] over sampled directions integrates
+    to the covered solid angle (<= 4 pi): a sampling/pdf consistency check that needs no oracle."""
+    import torch
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, K, n = 256, 64, 1 << 20
+    point6, weight, off = synth.make_samples(C, 512, seed=5)
+    joint, em, scal = synth.make_initial_model(C, K, seed=6)
+    cells = SDMMCells(C, K)
+    cells.upload(joint, em, scal)
+    cells.set_samples(point6, weight, off)
+    cells.em_step(3)
+    cell, pos3, u3 = synth.make_queries(n, C, seed=7, binned=True)
+    g = cells.sample_pdf(torch.from_numpy(cell.view(np.int32)).cuda(), torch.from_numpy(pos3).cuda(),
+                         torch.from_numpy(u3).cuda(), binned=True)
+    torch.cuda.synchronize()
+    valid = g["valid"].bool() & (g["inv_jac"] > 0)
+    assert valid.float().mean() > 0.9
+    nrm = g["dir"][:, valid].norm(dim=0)
+    assert (nrm - 1).abs().max() < 1e-4
+    pdf = g["pdf"][valid]
+    assert torch.isfinite(pdf).all() and (pdf > 0).all()
+    est = (1.0 / pdf.double()).mean().item()
+    assert 0.5 < est < 4 * np.pi * 1.05, est
