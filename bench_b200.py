@@ -1,0 +1,212 @@
+"""Second half of bench.py: the B200 arm (one process per GPU; torchrun provides RANK/WORLD_SIZE)."""
+import json
+import os
+import time
+
+import numpy as np
+
+
+def _maxreduce(torch, dist, world, v, device):
+    if world == 1:
+        return v
+    t = torch.tensor([v], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_baseline, FLOP_PER_UPDATE,
+             SFU_PER_UPDATE):
+    import torch
+    import torch.distributed as dist
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells, measure_peaks
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path "
+                         "(use --impl reference for the CPU reference arm)")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    K, N, iters = cfg["K"], cfg["N"], cfg["iters"]
+    strong = args.config == "cfg5"
+    C_local = cfg["cells"] // world if strong else cfg["cells"]
+    C_total = C_local * world
+    first = rank * C_local
+
+    peaks = measure_peaks(local)
+
+    cells = SDMMCells(C_total, K, device=local)
+    joint, em, scal = synth.make_initial_model(C_local, K, seed=1000 + rank)
+    cells.upload(joint, em, scal, first_cell=first)
+    chunks = []
+    step_c = 1024
+    for c0 in range(0, C_local, step_c):
+        chunks.append(make_device_samples(torch, min(step_c, C_local - c0), N, 77 + 1000 * rank + c0, device))
+    point6 = torch.cat([c[0] for c in chunks], dim=1).contiguous()
+    weight = torch.cat([c[1] for c in chunks]).contiguous()
+    del chunks
+    n_local = point6.shape[1]
+    off = (np.arange(C_local + 1, dtype=np.uint64) * N).astype(np.uint32)
+    torch.cuda.synchronize()
+
+    def step():
+        cells.set_samples(point6, weight, off, first_cell=first)
+        cells.em_step(iters, with_conditioner=True)
+        if world > 1:
+            cells.allgather_records(C_local)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = cells.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms_local = e0.elapsed_time(e1)
+    estep_ms, estep_n = cells.last_estep_ms()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = cells.launch_count() - l0
+    ms_total = _maxreduce(torch, dist, world, ms_local, device)
+    ms_per_step = ms_total / args.steps
+    updates_per_step = float(C_total) * K * N * iters
+    value = updates_per_step / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (K1, E-step + statistics), rank 0's launches ----------
+    est_ms = estep_ms / max(1, estep_n)
+    upd_per_launch = float(C_local) * K * N
+    achieved_tf = FLOP_PER_UPDATE * upd_per_launch / (est_ms * 1e-3) / 1e12
+    peak_tf = max(peaks["fp32_ffma2_tflops"], peaks["fp32_ffma_tflops"])
+    hbm_peak = None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+            hbm_peak = json.load(f).get("hbm_gbs")
+    except Exception:
+        pass
+    hbm_src = "MEASURED_PEAKS.json" if hbm_peak else "fallback (B200_PROFILING.md)"
+    hbm_peak = hbm_peak or 6650.0
+    hbm_gbs = 32.0 * C_local * N / (est_ms * 1e-3) / 1e9
+    roofline = dict(
+        bound="fp32", kernel="em_estep_kernel", achieved=achieved_tf, peak=peak_tf, unit="TFLOP/s",
+        frac=achieved_tf / peak_tf, traffic=None,
+        peak_source="FFMA2 micro-benchmark run by this process on this GPU (sdmmb_measure_peaks); "
+                    "MEASURED_PEAKS.json carries no FP32 figure",
+        flop_per_update=FLOP_PER_UPDATE, updates_per_launch=upd_per_launch, ms_per_launch=est_ms,
+        share_of_step=estep_ms / ms_per_step if world == 1 else None,
+        sfu=dict(achieved_gops=SFU_PER_UPDATE * upd_per_launch / (est_ms * 1e-3) / 1e9, peak_gops=peaks["mufu_gops"]),
+        hbm=dict(achieved=hbm_gbs, peak=hbm_peak, unit="GB/s", frac=hbm_gbs / hbm_peak, peak_source=hbm_src,
+                 algorithmic_bytes_per_sample=32),
+        measured_peaks=peaks,
+        note="no tensor cores: the contraction is 5-D; flop-based fraction is capped at ~71% by the "
+             "instruction mix (72 FP32-pipe lane-ops per 102 algorithmic flop)")
+
+    # ---- guided queries (second half of the metric), all ranks as replicas ----------------------
+    queries = None
+    nq = args.queries if args.queries else (1 << 24)
+    if nq > 0:
+        cell_q, pos_q, u_q = synth.make_queries(nq, C_total, seed=5 + rank, binned=True)
+        d_cell = torch.from_numpy(cell_q.view(np.int32)).to(device)
+        d_pos = torch.from_numpy(pos_q).to(device)
+        d_u = torch.from_numpy(u_q).to(device)
+        perm = torch.randperm(nq, device=device)
+        r_cell, r_pos, r_u = d_cell[perm].contiguous(), d_pos[:, perm].contiguous(), d_u[:, perm].contiguous()
+        res = {}
+        for name, (cc, pp, uu, binned) in dict(binned=(d_cell, d_pos, d_u, True),
+                                               random=(r_cell, r_pos, r_u, False)).items():
+            for _ in range(2):
+                out = cells.sample_pdf(cc, pp, uu, binned=binned)
+            torch.cuda.synchronize()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record()
+            for _ in range(3):
+                out = cells.sample_pdf(cc, pp, uu, binned=binned)
+            q1.record()
+            torch.cuda.synchronize()
+            qms = _maxreduce(torch, dist, world, q0.elapsed_time(q1) / 3, device)
+            res[name] = dict(value=world * nq / (qms * 1e-3), unit="queries/s", ms=qms)
+            valid_frac = float(out["valid"].float().mean().item())
+        flop_q = 80.0 * K + 120.0
+        queries = dict(metric="guided sample+pdf queries/s", n=nq * world, K=K, binned=res["binned"],
+                       random_order=res["random"], valid_fraction=valid_frac,
+                       roofline=dict(bound="fp32", achieved=flop_q * res["binned"]["value"] / world / 1e12,
+                                     peak=peaks["fp32_ffma_tflops"], unit="TFLOP/s",
+                                     frac=flop_q * res["binned"]["value"] / world / 1e12 / peaks["fp32_ffma_tflops"],
+                                     flop_per_query=flop_q))
+        del d_cell, d_pos, d_u, r_cell, r_pos, r_u, out
+
+    # ---- end to end through the host-buffer API --------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        h_point6 = torch.empty((6, n_local), dtype=torch.float32, pin_memory=True)
+        h_weight = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
+        h_point6.copy_(point6)
+        h_weight.copy_(weight)
+        h_joint = torch.empty((C_local, 32, K), dtype=torch.float32, pin_memory=True)
+        h_scal = torch.empty((C_local, 8), dtype=torch.int32, pin_memory=True)
+        np_p6, np_w = h_point6.numpy(), h_weight.numpy()
+        np_joint, np_scal = h_joint.numpy(), h_scal.numpy().view(np.uint32)
+        torch.cuda.synchronize()
+
+        def e2e_step():
+            cells.set_samples(np_p6, np_w, off, first_cell=first)        # H2D + pack
+            cells.em_step(iters, with_conditioner=True)
+            if world > 1:
+                cells.allgather_records(C_local)
+            cells.download(first, C_local, out=(np_joint, None, np_scal))    # D2H of the fitted mixtures
+
+        e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        n_e2e = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        e_ms = _maxreduce(torch, dist, world, (t1 - t0) * 1e3 / n_e2e, device)
+        assert np.isfinite(np_joint).all()
+        e2e = dict(value=updates_per_step / (e_ms * 1e-3), unit="updates/s", ms_per_step=e_ms, steps=n_e2e,
+                   h2d_bytes_per_step=int(28 * n_local), d2h_bytes_per_step=int(np_joint.nbytes + np_scal.nbytes),
+                   api="SDMMCells.set_samples(host) -> em_step -> download (sdmmb_set_samples_host / "
+                       "sdmmb_em_step / sdmmb_download_cells), pinned host buffers")
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb, _ = cpu_baseline(K, N, iters)
+
+    if rank == 0:
+        line = dict(
+            metric="EM sample-component updates/s", value=value, unit="updates/s", n_gpus=world,
+            steps=args.steps, warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=True,
+            scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32", data="synthetic",
+            config=dict(workload="%s: batched StepwiseTangentEM (sdmm::em_step), %d cells x %d components x %d "
+                                 "5-D samples/cell, %d EM iterations per step%s" %
+                                 (args.config, C_total, K, N, iters,
+                                  (" (%d cells per GPU, cell-sharded, NCCL all-gather of query records per step)"
+                                   % C_local) if world > 1 else ""),
+                        cells=C_total, components=K, samples_per_cell=N, em_iterations=iters,
+                        parallelism="cells sharded over %d GPU(s)" % world,
+                        l2_policy="inputs larger than L2 (%.0f MB of packed samples per GPU per iteration)"
+                                  % (32.0 * n_local / 1e6),
+                        model_state="EM state carries over between steps (same work per step)"),
+            clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cb,
+            queries=queries)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()

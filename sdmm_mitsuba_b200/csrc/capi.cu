@@ -219,9 +219,19 @@ int sdmmb_upload_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, const float*
     float jfill[JOINT_PLANES] = {0};
     jfill[6] = 1.f;
     for (int i = 0; i < 5; ++i) jfill[7 + 6 * i] = 1.f;
-    std::vector<float> hj((size_t)n_cells * JOINT_PLANES * K), he((size_t)n_cells * EM_PLANES * K);
-    pad_planes(h_joint, hj.data(), n_cells, JOINT_PLANES, Ku, K, jfill);
-    pad_planes(h_em, he.data(), n_cells, EM_PLANES, Ku, K, nullptr);
+    // no padding needed (K already 16/32/64/128): copy straight from the caller's buffers
+    const bool direct = (Ku == K);
+    std::vector<float> hj, he;
+    if (!direct) {
+        hj.resize((size_t)n_cells * JOINT_PLANES * K);
+        pad_planes(h_joint, hj.data(), n_cells, JOINT_PLANES, Ku, K, jfill);
+    }
+    if (!direct || !h_em) {
+        he.resize((size_t)n_cells * EM_PLANES * K);
+        pad_planes(h_em, he.data(), n_cells, EM_PLANES, Ku, K, nullptr);
+    }
+    const float* src_j = direct ? h_joint : hj.data();
+    const float* src_e = (direct && h_em) ? h_em : he.data();
     std::vector<uint32_t> hs((size_t)n_cells * SCALAR_WORDS, 0u);
     for (int c = 0; c < n_cells; ++c) {
         uint32_t* s = hs.data() + (size_t)c * SCALAR_WORDS;
@@ -233,10 +243,10 @@ int sdmmb_upload_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, const float*
         }
         s[7] = 0;
     }
-    CK(cudaMemcpyAsync(ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K, hj.data(), hj.size() * 4,
-                       cudaMemcpyHostToDevice, st));
-    CK(cudaMemcpyAsync(ctx->d_em + (size_t)first_cell * EM_PLANES * K, he.data(), he.size() * 4,
-                       cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K, src_j,
+                       (size_t)n_cells * JOINT_PLANES * K * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(ctx->d_em + (size_t)first_cell * EM_PLANES * K, src_e,
+                       (size_t)n_cells * EM_PLANES * K * 4, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(ctx->d_scal + (size_t)first_cell * SCALAR_WORDS, hs.data(), hs.size() * 4,
                        cudaMemcpyHostToDevice, st));
     MStepArgs a = base_mstep_args(ctx, first_cell, n_cells, 4);
@@ -255,6 +265,19 @@ int sdmmb_download_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_j
     cudaStream_t st = (cudaStream_t)stream;
     const int K = ctx->K, Ku = ctx->K_user;
     std::vector<float> tmp;
+    if (Ku == K) {
+        if (h_joint)
+            CK(cudaMemcpyAsync(h_joint, ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K,
+                               (size_t)n_cells * JOINT_PLANES * K * 4, cudaMemcpyDeviceToHost, st));
+        if (h_em)
+            CK(cudaMemcpyAsync(h_em, ctx->d_em + (size_t)first_cell * EM_PLANES * K,
+                               (size_t)n_cells * EM_PLANES * K * 4, cudaMemcpyDeviceToHost, st));
+        if (h_scal)
+            CK(cudaMemcpyAsync(h_scal, ctx->d_scal + (size_t)first_cell * SCALAR_WORDS,
+                               (size_t)n_cells * SCALAR_WORDS * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return SDMMB_OK;
+    }
     if (h_joint) {
         tmp.resize((size_t)n_cells * JOINT_PLANES * K);
         CK(cudaMemcpyAsync(tmp.data(), ctx->d_joint + (size_t)first_cell * JOINT_PLANES * K, tmp.size() * 4,

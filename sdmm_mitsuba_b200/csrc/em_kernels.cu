@@ -46,7 +46,7 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// K0: SoA planes -> packed records.  rec[2n] = (x, y, z, w), rec[2n+1] = (dx, dy, dz, 0).
+// K0: SoA planes -> packed records.  rec[2n] = (x, y, z, w), rec[2n+1] = (dx, dy, dz, w_eff).
 // HBM-bound: 28 B read + 32 B written per sample, fully coalesced.
 // ------------------------------------------------------------------------------------------------
 __global__ void pack_samples_kernel(const float* __restrict__ point6, size_t stride,
@@ -56,8 +56,11 @@ __global__ void pack_samples_kernel(const float* __restrict__ point6, size_t str
     size_t step = (size_t)gridDim.x * blockDim.x;
     for (; i < n; i += step) {
         float4 a = make_float4(point6[i], point6[stride + i], point6[2 * stride + i], weight[i]);
+        // b.w = effective weight: 0 for samples the EM loop skips (R: opt/data.h:20-23, em.h:267-269)
+        const float w = a.w;
+        const float w_eff = (w >= 1e-8f && w <= 3.402823466e+38f) ? w : 0.f;
         float4 b = make_float4(point6[3 * stride + i], point6[4 * stride + i],
-                               point6[5 * stride + i], 0.f);
+                               point6[5 * stride + i], w_eff);
         rec[2 * i] = a;
         rec[2 * i + 1] = b;
     }
@@ -165,13 +168,37 @@ __device__ __forceinline__ void accumulate_pair(PairAcc& acc, const PairOut& o, 
         }
 }
 
-template <int NP, int LPS, int WARPS, int MINB>
+// One sample-step of a lane: E-step of all its NP component pairs for the sample at smem slot `si`,
+// plus the lane-local part of the mixture normaliser.
+template <int NP>
+struct StepOut {
+    PairOut o[NP];
+    float sum;
+};
+
+template <int NP>
+__device__ __forceinline__ StepOut<NP> estep_sample(const float2 (&prm)[NP][EREC_PLANES],
+                                                    const float4* __restrict__ wbuf, int si) {
+    StepOut<NP> r;
+    const float4 A = wbuf[si * 4 + 0], B = wbuf[si * 4 + 1], C = wbuf[si * 4 + 2];
+    r.sum = 0.f;
+#pragma unroll
+    for (int q = 0; q < NP; ++q) {
+        r.o[q] = estep_pair(prm[q], make_float2(A.x, A.y), make_float2(A.z, A.w), make_float2(B.x, B.y),
+                            make_float2(B.z, B.w), make_float2(C.x, C.y), make_float2(C.z, C.w));
+        r.sum += r.o[q].p.x + r.o[q].p.y;
+    }
+    return r;
+}
+
+template <int NP, int LPS, int WARPS, int MINB, bool LL>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
 em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ items,
                 const float* __restrict__ erec, float* __restrict__ partials,
                 float* __restrict__ item_scal, float* __restrict__ out_loglik) {
     constexpr int K = 2 * NP * LPS;
-    constexpr int SPW = 32 / LPS;  // samples a warp processes per step
+    constexpr int SPW = 32 / LPS;      // samples a warp processes per step
+    constexpr int STEPS = 32 / SPW;    // steps per 32-sample chunk
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* sbuf = reinterpret_cast<float4*>(smem_raw);                     // [WARPS][32][4] float4
     float* red = reinterpret_cast<float*>(smem_raw + WARPS * 32 * 64);      // [WARPS][21][K]
@@ -203,73 +230,82 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
 #pragma unroll
         for (int i = 0; i < 15; ++i) acc[q].s2[i] = splat(0.f);
     }
-    float wsum = 0.f;
-    int nskip = 0;
+    // per-lane bookkeeping of the lane's OWN sample of each chunk (reduced once at the end)
+    float wsum = 0.f;   // sum of all stored weights                      R: opt/data.h:104-113
+    int n_wvalid = 0;   // samples with a valid weight                    R: opt/data.h:20-23
+    int n_ok = 0;       // samples that contributed (valid weight, finite non-zero normaliser)
 
     float4* wbuf = sbuf + warp * 32 * 4;
     const uint32_t n_chunks = (item.end - item.begin + 31u) / 32u;
-    // register prefetch of this lane's sample of the warp's first chunk
+    // CTA-uniform trip count (every warp runs the same number of rounds; a warp whose chunk lies
+    // beyond the item processes 32 zero-weight padding samples).  Keeping the loop bound free of
+    // the warp index lets the compiler prove the warp converged at the shuffles below, so the
+    // whole round stays one basic block that the scheduler can interleave.
+    const uint32_t n_rounds = (n_chunks + WARPS - 1) / WARPS;
+    // register prefetch of this lane's sample of the warp's first chunk; rb.w = effective weight
     float4 ra = make_float4(0.f, 0.f, 0.f, 0.f), rb = make_float4(0.f, 0.f, 1.f, 0.f);
     {
         uint32_t idx = item.begin + warp * 32u + lane;
-        if ((uint32_t)warp < n_chunks && idx < item.end) {
+        if (idx < item.end) {
             ra = samples[2 * (size_t)idx];
             rb = samples[2 * (size_t)idx + 1];
         }
     }
-    for (uint32_t chunk = warp; chunk < n_chunks; chunk += WARPS) {
-        const uint32_t cbase = item.begin + chunk * 32u;
+    for (uint32_t round = 0; round < n_rounds; ++round) {
+        const uint32_t cbase = item.begin + (round * WARPS + warp) * 32u;
         __syncwarp();
-        // duplicated-pair layout: (x,x,y,y) (z,z,dx,dx) (dy,dy,dz,dz) (w,-,-,-)
+        // duplicated-pair layout: (x,x,y,y) (z,z,dx,dx) (dy,dy,dz,dz) (w_eff,-,-,-)
         wbuf[lane * 4 + 0] = make_float4(ra.x, ra.x, ra.y, ra.y);
         wbuf[lane * 4 + 1] = make_float4(ra.z, ra.z, rb.x, rb.x);
         wbuf[lane * 4 + 2] = make_float4(rb.y, rb.y, rb.z, rb.z);
-        wbuf[lane * 4 + 3] = make_float4(ra.w, 0.f, 0.f, 0.f);
+        wbuf[lane * 4 + 3] = make_float4(rb.w, 0.f, 0.f, 0.f);
+        wsum += ra.w;
+        n_wvalid += (rb.w > 0.f) ? 1 : 0;
         __syncwarp();
         {   // prefetch the next chunk while this one is processed
             uint32_t nidx = cbase + WARPS * 32u + lane;
             ra = make_float4(0.f, 0.f, 0.f, 0.f);
             rb = make_float4(0.f, 0.f, 1.f, 0.f);
-            if (chunk + WARPS < n_chunks && nidx < item.end) {
+            if (nidx < item.end) {
                 ra = samples[2 * (size_t)nidx];
                 rb = samples[2 * (size_t)nidx + 1];
             }
         }
+        // software pipeline over the chunk's steps: the E-step of step s+1 is independent of the
+        // shuffle butterfly + accumulation of step s, so both sit in one basic block and overlap.
+        StepOut<NP> cur = estep_sample<NP>(prm, wbuf, grp);
 #pragma unroll 2
-        for (int s = 0; s < 32; s += SPW) {
-            const int si = s + grp;
-            const float4 A = wbuf[si * 4 + 0], B = wbuf[si * 4 + 1], C = wbuf[si * 4 + 2];
-            const float w = reinterpret_cast<const float*>(wbuf + si * 4 + 3)[0];
-            PairOut o[NP];
-            float sum = 0.f;
-#pragma unroll
-            for (int q = 0; q < NP; ++q) {
-                o[q] = estep_pair(prm[q], make_float2(A.x, A.y), make_float2(A.z, A.w),
-                                  make_float2(B.x, B.y), make_float2(B.z, B.w),
-                                  make_float2(C.x, C.y), make_float2(C.z, C.w));
-                sum += o[q].p.x + o[q].p.y;
-            }
+        for (int s = 0; s < STEPS; ++s) {
+            const int si = s * SPW + grp;
+            // the pipeline tail recomputes the last sample (result unused) to stay branch-free
+            const int sn = (s + 1 < STEPS) ? si + SPW : si;
+            StepOut<NP> nxt = estep_sample<NP>(prm, wbuf, sn);
+            float sum = cur.sum;
 #pragma unroll
             for (int off = LPS / 2; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-            // hsum; skip if 0 / non-finite                            R: opt/em.h:288-293
-            const bool wvalid = (w >= 1e-8f) && (w <= 3.402823466e+38f);   // R: opt/data.h:20-23
+            const float w = reinterpret_cast<const float*>(wbuf + si * 4 + 3)[0];
+            // hsum; skip if 0 / non-finite                           R: opt/em.h:288-293
             const float rs = rcp_approx(sum);
-            const bool ok = wvalid && (sum > 0.f) && (sum <= 3.402823466e+38f) && (rs <= 3.402823466e+38f);
-            const float sc = ok ? w * rs : 0.f;                          // w_n / sum  R: em.h:295-298, 309
-            wsum += w;                                                    // R: opt/data.h:104-113
-            nskip += (wvalid && !ok) ? 1 : 0;
-            if (!(sum <= 3.402823466e+38f)) {                             // NaN/inf: keep 0 * p finite
-#pragma unroll
-                for (int q = 0; q < NP; ++q) o[q].p = splat(0.f);
+            const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);   // sum finite, > 0, 1/sum finite
+            const float sc = ok ? w * rs : 0.f;                       // w_n / sum   R: em.h:295-298, 309
+            n_ok += (sc > 0.f) ? 1 : 0;
+            if (LL) {
+                if (l == 0 && cbase + si < item.end) out_loglik[cbase + si] = logf(sum);
             }
-            if (out_loglik != nullptr && l == 0 && cbase + si < item.end)
-                out_loglik[cbase + si] = logf(sum);
             const float2 ss = splat(sc);
 #pragma unroll
-            for (int q = 0; q < NP; ++q) accumulate_pair(acc[q], o[q], ss);
+            for (int q = 0; q < NP; ++q) {
+                // a NaN/inf normaliser must not leak 0 * inf into the statistics
+                PairOut o = cur.o[q];
+                o.p.x = ok ? o.p.x : 0.f;
+                o.p.y = ok ? o.p.y : 0.f;
+                accumulate_pair(acc[q], o, ss);
+            }
+            cur = nxt;
         }
     }
-
+    // n_ok was counted by every lane of a sample's group (identical values): keep lane l == 0's
+    int nskip = 0;
     // ---- reduce: sample groups within the warp, then warps within the CTA (fixed order) --------
     if (SPW > 1) {
 #pragma unroll
@@ -281,10 +317,12 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
                 for (int off = LPS; off < 32; off <<= 1) f[i] += __shfl_xor_sync(0xffffffffu, f[i], off);
         }
     }
-    // wsum / nskip are identical across the lanes of a group: take lane l == 0 of each group
+    // wsum / n_wvalid are per-lane partials over the lane's own samples; n_ok is replicated across the
+    // lanes of a sample group, so only lane l == 0 of each group contributes it
     {
-        float ws = (l == 0) ? wsum : 0.f;
-        int ns = (l == 0) ? nskip : 0;
+        float ws = wsum;
+        int ns = n_wvalid - ((l == 0) ? n_ok : 0);
+        (void)nskip;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
             ws += __shfl_xor_sync(0xffffffffu, ws, off);
@@ -722,11 +760,11 @@ __global__ void conditioner_readout_kernel(const float* __restrict__ joint_all, 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
 // ------------------------------------------------------------------------------------------------
-template <int NP, int LPS, int WARPS, int MINB>
-static cudaError_t launch_estep_t(const EStepLaunch& L, cudaStream_t st) {
+template <int NP, int LPS, int WARPS, int MINB, bool LL>
+static cudaError_t launch_estep_tl(const EStepLaunch& L, cudaStream_t st) {
     constexpr int K = 2 * NP * LPS;
     const size_t smem = (size_t)WARPS * 32 * 64 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
-    auto kern = em_estep_kernel<NP, LPS, WARPS, MINB>;
+    auto kern = em_estep_kernel<NP, LPS, WARPS, MINB, LL>;
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -735,6 +773,12 @@ static cudaError_t launch_estep_t(const EStepLaunch& L, cudaStream_t st) {
     }
     kern<<<L.n_items, WARPS * 32, smem, st>>>(L.samples, L.items, L.erec, L.partials, L.item_scal, L.out_loglik);
     return cudaGetLastError();
+}
+
+template <int NP, int LPS, int WARPS, int MINB>
+static cudaError_t launch_estep_t(const EStepLaunch& L, cudaStream_t st) {
+    return L.out_loglik ? launch_estep_tl<NP, LPS, WARPS, MINB, true>(L, st)
+                        : launch_estep_tl<NP, LPS, WARPS, MINB, false>(L, st);
 }
 
 cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st) {

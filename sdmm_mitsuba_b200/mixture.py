@@ -78,11 +78,16 @@ class SDMMCells:
         check(self._L.sdmmb_upload_cells(self._h, first_cell, n, _hp(joint), _hp(em), _hp(scal), None),
               "sdmmb_upload_cells", self._h)
 
-    def download(self, first_cell=0, n_cells=None):
+    def download(self, first_cell=0, n_cells=None, out=None, want_em=True):
+        """Returns (joint, em, scal).  `out` = optional (joint, em-or-None, scal) NumPy buffers to fill
+        (e.g. views of pinned memory); want_em=False skips the EM statistics (em is None)."""
         n = self.max_cells - first_cell if n_cells is None else n_cells
-        joint = np.zeros((n, JOINT_PLANES, self.K), np.float32)
-        em = np.zeros((n, EM_PLANES, self.K), np.float32)
-        scal = np.zeros((n, SCALAR_WORDS), np.uint32)
+        if out is not None:
+            joint, em, scal = out
+        else:
+            joint = np.zeros((n, JOINT_PLANES, self.K), np.float32)
+            em = np.zeros((n, EM_PLANES, self.K), np.float32) if want_em else None
+            scal = np.zeros((n, SCALAR_WORDS), np.uint32)
         check(self._L.sdmmb_download_cells(self._h, first_cell, n, _hp(joint), _hp(em), _hp(scal), None),
               "sdmmb_download_cells", self._h)
         return joint, em, scal
