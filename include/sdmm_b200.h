@@ -44,7 +44,7 @@ extern "C" {
 #define SDMMB_EM_PLANES 81
 #define SDMMB_SCALAR_WORDS 8
 #define SDMMB_QUERY_RECORD_FLOATS 32 /* per component, 30 used */
-#define SDMMB_ESTEP_RECORD_PLANES 28 /* per component planes of the E-step record */
+#define SDMMB_ESTEP_RECORD_PLANES 25 /* per component planes of the E-step record */
 #define SDMMB_MAX_K 128
 
 /* error codes */

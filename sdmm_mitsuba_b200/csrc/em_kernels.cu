@@ -96,14 +96,25 @@ struct PairOut {
     float2 t[5];  // tangent coordinates
 };
 
-// prm: 28 packed parameter pairs (kernels.h: EREC_*).
+// prm: 25 packed parameter pairs (kernels.h: EREC_*).  `ndz` is MINUS the sample's direction z.
+//
+// d_loc = R_to d without the 3x3 matrix.  The frame is always the Duff et al. basis of the unit mean
+// direction n (R: linalg/coordinate_system.h:21-38): rows of R_to are
+//   s = (1 + sign a nx^2, sign b, -sign nx),  t = (b, sign + a ny^2, -ny),  n,   b = nx ny a,
+// so with q = nx dx + ny dy and h = a q - dz:
+//   s.d = dx + sign nx h,   t.d = sign (dy + sign ny h),   n.d = q + nz dz.
+// 6 FMA-pipe ops instead of 9 and 6 parameter registers instead of 9.  The kernel carries
+// ly' = sign * (t.d); the factor is folded into W(4,4) for the Mahalanobis form and undone on the
+// five t_4-odd statistics when the M-step reduces the partials.
 __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, float2 xx, float2 yy,
-                                              float2 zz, float2 dx, float2 dy, float2 dz) {
+                                              float2 zz, float2 dx, float2 dy, float2 ndz) {
     PairOut o;
-    // d_loc = R_to d                                      R: spaces/spatio_directional.h:89-91
-    float2 lx = fma2(prm[EREC_R + 2], dz, fma2(prm[EREC_R + 1], dy, mul2(prm[EREC_R + 0], dx)));
-    float2 ly = fma2(prm[EREC_R + 5], dz, fma2(prm[EREC_R + 4], dy, mul2(prm[EREC_R + 3], dx)));
-    float2 lz = fma2(prm[EREC_R + 8], dz, fma2(prm[EREC_R + 7], dy, mul2(prm[EREC_R + 6], dx)));
+    const float2* F = prm + EREC_ROT;  // nx, ny, -nz, a, sign nx, sign ny
+    float2 q = fma2(F[1], dy, mul2(F[0], dx));
+    float2 lz = fma2(F[2], ndz, q);
+    float2 h = fma2(F[3], q, ndz);
+    float2 lx = fma2(F[4], h, dx);
+    float2 ly = fma2(F[5], h, dy);
     float2 a = make_float2(fminf(fabsf(lz.x), SDMMB_ONE_MINUS), fminf(fabsf(lz.y), SDMMB_ONE_MINUS));
     float2 P = fma2(a, kC2[6], kC2[5]);
     P = fma2(P, a, kC2[4]);
@@ -140,6 +151,87 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
     float2 ex = make_float2(ex2_approx(-e.x), ex2_approx(-e.y));
     o.p = mul2(r, ex);
     return o;
+}
+
+// The same E-step for S samples in lockstep, written operation by operation across the samples so
+// that consecutive instructions share their per-component parameter operand: the register file
+// delivers one 64-bit operand per cycle (profiles/ubench_r1.txt), an operand repeated in the same
+// slot of the next instruction comes from the reuse cache for free.
+template <int S>
+__device__ __forceinline__ void estep_pair_multi(const float2* __restrict__ prm, const float4 (&A)[S],
+                                                 const float4 (&B)[S], PairOut (&o)[S]) {
+    const float2* F = prm + EREC_ROT;
+    const float2* W = prm + EREC_W;
+    float2 q[S], lz[S], h[S], lx[S], ly[S], a[S], P[S], opa[S], oma[S], u[S], v[S], r[S];
+#define SDMMB_EACH for (int s = 0; s < S; ++s)
+#pragma unroll
+    SDMMB_EACH q[s] = mul2(F[0], splat(A[s].w));
+#pragma unroll
+    SDMMB_EACH q[s] = fma2(F[1], splat(B[s].x), q[s]);
+#pragma unroll
+    SDMMB_EACH lz[s] = fma2(F[2], splat(B[s].y), q[s]);
+#pragma unroll
+    SDMMB_EACH h[s] = fma2(F[3], q[s], splat(B[s].y));
+#pragma unroll
+    SDMMB_EACH lx[s] = fma2(F[4], h[s], splat(A[s].w));
+#pragma unroll
+    SDMMB_EACH ly[s] = fma2(F[5], h[s], splat(B[s].x));
+#pragma unroll
+    SDMMB_EACH a[s] = make_float2(fminf(fabsf(lz[s].x), SDMMB_ONE_MINUS), fminf(fabsf(lz[s].y), SDMMB_ONE_MINUS));
+#pragma unroll
+    SDMMB_EACH P[s] = fma2(a[s], kC2[6], kC2[5]);
+#pragma unroll
+    for (int c = 4; c >= 0; --c)
+#pragma unroll
+        SDMMB_EACH P[s] = fma2(P[s], a[s], kC2[c]);
+#pragma unroll
+    SDMMB_EACH {
+        opa[s] = add2(a[s], kC2[7]);
+        oma[s] = fma2(a[s], kC2[8], kC2[7]);
+        u[s] = make_float2(rsqrt_approx(opa[s].x), rsqrt_approx(opa[s].y));
+        v[s] = make_float2(rsqrt_approx(oma[s].x), rsqrt_approx(oma[s].y));
+    }
+#pragma unroll
+    SDMMB_EACH {
+        float2 alt = fma2(v[s], kC2[9], P[s]);
+        float2 sel = make_float2(lz[s].x >= 0.f ? P[s].x : -alt.x, lz[s].y >= 0.f ? P[s].y : -alt.y);
+        r[s] = mul2(sel, u[s]);
+    }
+#pragma unroll
+    SDMMB_EACH o[s].t[0] = add2(splat(A[s].x), prm[EREC_NMU + 0]);
+#pragma unroll
+    SDMMB_EACH o[s].t[1] = add2(splat(A[s].y), prm[EREC_NMU + 1]);
+#pragma unroll
+    SDMMB_EACH o[s].t[2] = add2(splat(A[s].z), prm[EREC_NMU + 2]);
+#pragma unroll
+    SDMMB_EACH o[s].t[3] = mul2(lx[s], r[s]);
+#pragma unroll
+    SDMMB_EACH o[s].t[4] = mul2(ly[s], r[s]);
+    // z = W t, row by row; within a row the W entry is the shared operand across the samples
+    float2 z[S][5];
+    int e = 0;
+#pragma unroll
+    for (int row = 0; row < 5; ++row) {
+#pragma unroll
+        for (int c = 0; c <= row; ++c) {
+#pragma unroll
+            SDMMB_EACH z[s][row] = (c == 0) ? mul2(W[e], o[s].t[0]) : fma2(W[e], o[s].t[c], z[s][row]);
+            ++e;
+        }
+    }
+    float2 ee[S];
+#pragma unroll
+    SDMMB_EACH ee[s] = fma2(z[s][0], z[s][0], prm[EREC_NLC]);
+#pragma unroll
+    for (int row = 1; row < 5; ++row)
+#pragma unroll
+        SDMMB_EACH ee[s] = fma2(z[s][row], z[s][row], ee[s]);
+#pragma unroll
+    SDMMB_EACH {
+        float2 ex = make_float2(ex2_approx(-ee[s].x), ex2_approx(-ee[s].y));
+        o[s].p = mul2(r[s], ex);
+    }
+#undef SDMMB_EACH
 }
 
 struct PairAcc {
@@ -180,18 +272,19 @@ template <int NP>
 __device__ __forceinline__ StepOut<NP> estep_sample(const float2 (&prm)[NP][EREC_PLANES],
                                                     const float4* __restrict__ wbuf, int si) {
     StepOut<NP> r;
-    const float4 A = wbuf[si * 4 + 0], B = wbuf[si * 4 + 1], C = wbuf[si * 4 + 2];
-    r.sum = 0.f;
+    // (x, y, z, dx) (dy, -dz, w_eff, -): scalars, splat into both halves of the packed operands so
+    // that the compiler can use the 32-bit broadcast operand form (half the register-file traffic)
+    const float4 A = wbuf[si * 2 + 0], B = wbuf[si * 2 + 1];
 #pragma unroll
     for (int q = 0; q < NP; ++q) {
-        r.o[q] = estep_pair(prm[q], make_float2(A.x, A.y), make_float2(A.z, A.w), make_float2(B.x, B.y),
-                            make_float2(B.z, B.w), make_float2(C.x, C.y), make_float2(C.z, C.w));
-        r.sum += r.o[q].p.x + r.o[q].p.y;
+        r.o[q] = estep_pair(prm[q], splat(A.x), splat(A.y), splat(A.z), splat(A.w), splat(B.x), splat(B.y));
+        const float pq = r.o[q].p.x + r.o[q].p.y;
+        r.sum = (q == 0) ? pq : r.sum + pq;
     }
     return r;
 }
 
-template <int NP, int LPS, int WARPS, int MINB, bool LL>
+template <int NP, int LPS, int WARPS, int MINB, bool LL, int MODE>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
 em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ items,
                 const float* __restrict__ erec, float* __restrict__ partials,
@@ -200,8 +293,8 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     constexpr int SPW = 32 / LPS;      // samples a warp processes per step
     constexpr int STEPS = 32 / SPW;    // steps per 32-sample chunk
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* sbuf = reinterpret_cast<float4*>(smem_raw);                     // [WARPS][32][4] float4
-    float* red = reinterpret_cast<float*>(smem_raw + WARPS * 32 * 64);      // [WARPS][21][K]
+    float4* sbuf = reinterpret_cast<float4*>(smem_raw);                     // [WARPS][32][2] float4
+    float* red = reinterpret_cast<float*>(smem_raw + WARPS * 32 * 32);      // [WARPS][21][K]
     __shared__ float s_wsum[WARPS];
     __shared__ int s_skip[WARPS];
 
@@ -235,7 +328,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     int n_wvalid = 0;   // samples with a valid weight                    R: opt/data.h:20-23
     int n_ok = 0;       // samples that contributed (valid weight, finite non-zero normaliser)
 
-    float4* wbuf = sbuf + warp * 32 * 4;
+    float4* wbuf = sbuf + warp * 32 * 2;
     const uint32_t n_chunks = (item.end - item.begin + 31u) / 32u;
     // CTA-uniform trip count (every warp runs the same number of rounds; a warp whose chunk lies
     // beyond the item processes 32 zero-weight padding samples).  Keeping the loop bound free of
@@ -254,11 +347,9 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     for (uint32_t round = 0; round < n_rounds; ++round) {
         const uint32_t cbase = item.begin + (round * WARPS + warp) * 32u;
         __syncwarp();
-        // duplicated-pair layout: (x,x,y,y) (z,z,dx,dx) (dy,dy,dz,dz) (w_eff,-,-,-)
-        wbuf[lane * 4 + 0] = make_float4(ra.x, ra.x, ra.y, ra.y);
-        wbuf[lane * 4 + 1] = make_float4(ra.z, ra.z, rb.x, rb.x);
-        wbuf[lane * 4 + 2] = make_float4(rb.y, rb.y, rb.z, rb.z);
-        wbuf[lane * 4 + 3] = make_float4(rb.w, 0.f, 0.f, 0.f);
+        // per-warp staging slot of a sample: (x, y, z, dx) (dy, -dz, w_eff, -)
+        wbuf[lane * 2 + 0] = make_float4(ra.x, ra.y, ra.z, rb.x);
+        wbuf[lane * 2 + 1] = make_float4(rb.y, -rb.z, rb.w, 0.f);
         wsum += ra.w;
         n_wvalid += (rb.w > 0.f) ? 1 : 0;
         __syncwarp();
@@ -271,6 +362,54 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
                 rb = samples[2 * (size_t)nidx + 1];
             }
         }
+        if constexpr (MODE == 1) {
+            // phased: E-step of two samples in lockstep (shared parameter operands), both normaliser
+            // butterflies, then both accumulations; latency is covered by the other resident warps
+#pragma unroll 1
+            for (int s = 0; s < STEPS; s += 2) {
+                const int si0 = s * SPW + grp;
+                float4 A[2], B[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    A[j] = wbuf[(si0 + j * SPW) * 2 + 0];
+                    B[j] = wbuf[(si0 + j * SPW) * 2 + 1];
+                }
+                PairOut o[NP][2];
+                float sum[2];
+#pragma unroll
+                for (int q = 0; q < NP; ++q) {
+                    estep_pair_multi<2>(prm[q], A, B, o[q]);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const float pq = o[q][j].p.x + o[q][j].p.y;
+                        sum[j] = (q == 0) ? pq : sum[j] + pq;
+                    }
+                }
+#pragma unroll
+                for (int off = LPS / 2; off > 0; off >>= 1)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) sum[j] += __shfl_xor_sync(0xffffffffu, sum[j], off);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int si = si0 + j * SPW;
+                    const float rs = rcp_approx(sum[j]);
+                    const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);
+                    const float sc = ok ? B[j].z * rs : 0.f;
+                    n_ok += (sc > 0.f) ? 1 : 0;
+                    if (LL) {
+                        if (l == 0 && cbase + si < item.end) out_loglik[cbase + si] = logf(sum[j]);
+                    }
+                    const float2 ss = splat(sc);
+#pragma unroll
+                    for (int q = 0; q < NP; ++q) {
+                        PairOut oo = o[q][j];
+                        oo.p.x = ok ? oo.p.x : 0.f;
+                        oo.p.y = ok ? oo.p.y : 0.f;
+                        accumulate_pair(acc[q], oo, ss);
+                    }
+                }
+            }
+        } else {
         // software pipeline over the chunk's steps: the E-step of step s+1 is independent of the
         // shuffle butterfly + accumulation of step s, so both sit in one basic block and overlap.
         StepOut<NP> cur = estep_sample<NP>(prm, wbuf, grp);
@@ -283,7 +422,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             float sum = cur.sum;
 #pragma unroll
             for (int off = LPS / 2; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-            const float w = reinterpret_cast<const float*>(wbuf + si * 4 + 3)[0];
+            const float w = reinterpret_cast<const float*>(wbuf + si * 2 + 1)[2];
             // hsum; skip if 0 / non-finite                           R: opt/em.h:288-293
             const float rs = rcp_approx(sum);
             const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);   // sum finite, > 0, 1/sum finite
@@ -303,6 +442,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             }
             cur = nxt;
         }
+            }
     }
     // n_ok was counted by every lane of a sample's group (identical values): keep lane l == 0's
     int nskip = 0;
@@ -394,13 +534,25 @@ __device__ inline void write_erec(float* __restrict__ erec_cell, int K, int k, f
     const float scale = 0.84932180028801904272f;  // sqrt(log2(e) / 2)
 #pragma unroll
     for (int d = 0; d < 3; ++d) erec_cell[(EREC_NMU + d) * K + k] = -mean[d];
+    {   // factored Duff frame of the unit mean direction (rows of cp.to are s, t, n)
+        const float nx = cp.to[6], ny = cp.to[7], nz = cp.to[8];
+        const float sign = copysignf(1.f, nz);
+        float* f = erec_cell + (size_t)EREC_ROT * K + k;
+        f[0 * K] = nx;
+        f[1 * K] = ny;
+        f[2 * K] = -nz;
+        f[3 * K] = -1.f / (sign + nz);
+        f[4 * K] = sign * nx;
+        f[5 * K] = sign * ny;
+        int e = 0;
 #pragma unroll
-    for (int i = 0; i < 9; ++i) erec_cell[(EREC_R + i) * K + k] = cp.to[i];
-    int e = 0;
+        for (int r = 0; r < 5; ++r)
 #pragma unroll
-    for (int r = 0; r < 5; ++r)
-#pragma unroll
-        for (int c = 0; c <= r; ++c) erec_cell[(EREC_W + e++) * K + k] = W[r * 5 + c] * scale;
+            for (int c = 0; c <= r; ++c) {
+                const float w = W[r * 5 + c] * scale;
+                erec_cell[(EREC_W + e++) * K + k] = (c == 4) ? sign * w : w;
+            }
+    }
     // -log2(pi_k * inv_det * (2 pi)^-5/2); +inf switches a zero-weight component off (2^-inf = 0)
     float coef = pmf * cp.inv_det * gaussian_normalization(5);
     erec_cell[EREC_NLC * K + k] = (coef > 0.f) ? -log2f(coef) : (coef == 0.f ? INFINITY : NAN);
@@ -549,6 +701,12 @@ em_mstep_kernel(MStepArgs a) {
             for (int i = 0; i < ESTAT_PLANES; ++i) bt[i] += p[i * K + k];
             weight_sum += a.item_scal[2 * (size_t)it];
             nskip += __float_as_int(a.item_scal[2 * (size_t)it + 1]);
+        }
+        {   // the E-step accumulated with sign * t_4 (see estep_pair): undo on the t_4-odd statistics
+            const float sgn = copysignf(1.f, mean[5]);
+            bt[5] *= sgn;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bt[16 + j] *= sgn;
         }
         const int n_samples = (int)(a.cell_sample_count[ci]);
         float total_weight = __uint_as_float(scal[0]);
@@ -760,11 +918,11 @@ __global__ void conditioner_readout_kernel(const float* __restrict__ joint_all, 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
 // ------------------------------------------------------------------------------------------------
-template <int NP, int LPS, int WARPS, int MINB, bool LL>
+template <int NP, int LPS, int WARPS, int MINB, bool LL, int MODE>
 static cudaError_t launch_estep_tl(const EStepLaunch& L, cudaStream_t st) {
     constexpr int K = 2 * NP * LPS;
-    const size_t smem = (size_t)WARPS * 32 * 64 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
-    auto kern = em_estep_kernel<NP, LPS, WARPS, MINB, LL>;
+    const size_t smem = (size_t)WARPS * 32 * 32 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
+    auto kern = em_estep_kernel<NP, LPS, WARPS, MINB, LL, MODE>;
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -775,10 +933,10 @@ static cudaError_t launch_estep_tl(const EStepLaunch& L, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-template <int NP, int LPS, int WARPS, int MINB>
+template <int NP, int LPS, int WARPS, int MINB, int MODE = 0>
 static cudaError_t launch_estep_t(const EStepLaunch& L, cudaStream_t st) {
-    return L.out_loglik ? launch_estep_tl<NP, LPS, WARPS, MINB, true>(L, st)
-                        : launch_estep_tl<NP, LPS, WARPS, MINB, false>(L, st);
+    return L.out_loglik ? launch_estep_tl<NP, LPS, WARPS, MINB, true, MODE>(L, st)
+                        : launch_estep_tl<NP, LPS, WARPS, MINB, false, MODE>(L, st);
 }
 
 cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st) {
@@ -786,7 +944,20 @@ cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st) {
     switch (L.K) {
         case 16: return launch_estep_t<1, 8, 4, 3>(L, st);
         case 32: return launch_estep_t<1, 16, 4, 3>(L, st);
-        case 64: return launch_estep_t<1, 32, 4, 3>(L, st);
+        case 64: {
+            // tuning hook (tools/estep_sweep.py): alternative lane/occupancy shapes of the same kernel
+            static const int variant = [] { const char* v = getenv("SDMMB_ESTEP_VARIANT"); return v ? atoi(v) : 0; }();
+            switch (variant) {
+                case 1: return launch_estep_t<2, 16, 4, 2>(L, st);
+                case 2: return launch_estep_t<1, 32, 4, 4>(L, st);
+                case 3: return launch_estep_t<1, 32, 8, 1>(L, st);
+                case 4: return launch_estep_t<2, 16, 8, 1>(L, st);
+                case 5: return launch_estep_t<1, 32, 2, 6>(L, st);
+                case 6: return launch_estep_t<1, 32, 4, 3, 1>(L, st);
+                case 7: return launch_estep_t<1, 32, 4, 4, 1>(L, st);
+                default: return launch_estep_t<1, 32, 4, 3>(L, st);
+            }
+        }
         case 128: return launch_estep_t<2, 32, 4, 2>(L, st);
         default: return cudaErrorInvalidValue;
     }

@@ -11,12 +11,14 @@ constexpr int JOINT_PLANES = 32;
 constexpr int EM_PLANES = 81;
 constexpr int SCALAR_WORDS = 8;
 
-// E-step record: 28 planes of K floats per cell ([cell][plane][K], lanes read consecutive k)
+// E-step record: 25 planes of K floats per cell ([cell][plane][K], lanes read consecutive k)
 constexpr int EREC_NMU = 0;   // 3: -mean position
-constexpr int EREC_R = 3;     // 9: frame.to, row-major
-constexpr int EREC_W = 12;    // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major
-constexpr int EREC_NLC = 27;  // 1: -log2(pmf * inv_cov_sqrt_det * (2 pi)^-5/2)
-constexpr int EREC_PLANES = 28;
+constexpr int EREC_ROT = 3;   // 6: the Duff frame in factored form: n.x, n.y, n.z, a = -1/(sign + n.z),
+                              //    sign * n.x, sign * n.y  (sign = copysign(1, n.z)); see estep_pair()
+constexpr int EREC_W = 9;     // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major; the (4,4) entry
+                              //    carries the factor `sign` because the kernel works with sign * t_4
+constexpr int EREC_NLC = 24;  // 1: -log2(pmf * inv_cov_sqrt_det * (2 pi)^-5/2)
+constexpr int EREC_PLANES = 25;
 
 // E-step partial statistics per item: 21 planes of K floats
 //   0 = sum g, 1..5 = sum g t_i, 6 + i(i+1)/2 + j = sum g t_i t_j (i >= j)

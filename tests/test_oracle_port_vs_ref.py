@@ -1,0 +1,81 @@
+"""The plain-C restatement (oracle/sdmm_oracle.c) against the reference's own headers compiled in
+place (oracle/_ref) on identical seeded streams -- run wherever oracle/_ref exists (it is built in
+the container that has /root/reference and travels to the GPU box as a prebuilt .so)."""
+import numpy as np
+import pytest
+
+from parity import LL_RTOL, PARAM_RTOL, assert_joint_close, loglik_err
+
+
+@pytest.mark.parametrize("K,N", [(16, 500), (64, 1000), (128, 700)])
+def test_port_vs_ref_em_per_iteration(oracle_port, oracle_ref, K, N):
+    from sdmm_mitsuba_b200 import synth
+    C, iters = 3, 4
+    point6, weight, off = synth.make_samples(C, N, seed=K + 1)
+    joint, em, scal = synth.make_initial_model(C, K, seed=K + 2)
+    r = oracle_ref.RefCells(C, K)
+    p = oracle_port.PortCells(C, K)
+    r.set(joint, em, scal)
+    for it in range(iters):
+        j0, e0, s0 = r.get()
+        p.set(j0, e0, s0)
+        ll_r = np.concatenate(r.em_step(off, point6, weight, 1, want_loglik=True), axis=1)
+        ll_p = np.concatenate(p.em_step(off, point6, weight, 1, want_loglik=True), axis=1)
+        err, mism = loglik_err(ll_p, ll_r)
+        assert mism == 0 and err <= LL_RTOL, (it, err)
+        jr, er, sr = r.get()
+        jp, ep, sp = p.get()
+        assert_joint_close(jp, jr, PARAM_RTOL, "it %d" % it)
+        assert (sp[:, 1:3] == sr[:, 1:3]).all()
+
+
+@pytest.mark.parametrize("K", [16, 64])
+def test_port_vs_ref_queries(oracle_port, oracle_ref, K):
+    from sdmm_mitsuba_b200 import synth
+    C, N, n = 4, 800, 5000
+    point6, weight, off = synth.make_samples(C, N, seed=K + 11)
+    joint, em, scal = synth.make_initial_model(C, K, seed=K + 12)
+    r = oracle_ref.RefCells(C, K)
+    r.set(joint, em, scal)
+    r.em_step(off, point6, weight, 3)
+    j, e, s = r.get()
+    p = oracle_port.PortCells(C, K)
+    p.set(j, e, s)
+    r.prepare_conditioner()
+    p.prepare_conditioner()
+    cell, pos3, u3 = synth.make_queries(n, C, seed=K + 13, binned=True)
+    qr, _ = r.sample_pdf(cell, pos3, u3)
+    qp, _ = p.sample_pdf(cell, pos3, u3)
+    np.testing.assert_array_equal(qr["valid"], qp["valid"])
+    v = qr["valid"].astype(bool)
+    same = v & (qr["comp"] == qp["comp"])
+    assert same.sum() >= 0.999 * v.sum()
+    for i in np.nonzero(v & ~same)[0]:
+        _, cdf, ok = r.conditional_weights(int(cell[i]), pos3[:, i])
+        assert ok and np.abs(cdf - u3[0, i]).min() < 2e-5
+    ang = np.arccos(np.clip((qr["dir"][:, same] * qp["dir"][:, same]).sum(axis=0), -1, 1))
+    assert ang.max() < 2e-3
+    big = same & (qr["pdf"] > 1e-6)
+    rel = np.abs(qp["pdf"][big] - qr["pdf"][big]) / qr["pdf"][big]
+    assert np.median(rel) < 1e-4 and np.quantile(rel, 0.999) < 5e-3
+
+
+def test_port_vs_ref_tangent_map(oracle_port, oracle_ref):
+    """SpatioDirectionalTangentSpace::to on single points, incl. the antipode and the pole."""
+    rng = np.random.default_rng(0)
+    for i in range(200):
+        m = rng.normal(size=6).astype(np.float32)
+        m[3:] /= np.linalg.norm(m[3:])
+        x = rng.normal(size=6).astype(np.float32)
+        x[3:] /= np.linalg.norm(x[3:])
+        if i == 0:
+            x[3:] = m[3:]
+        if i == 1:
+            x[3:] = -m[3:]
+        tr, ijr = oracle_ref.joint_to(m, x)
+        tp, ijp = oracle_port.joint_to(m, x)
+        # within ~4 degrees of the antipode theta/sin(theta) is ill-conditioned (d/dcos ~ 1/sin^3) and
+        # both sides are only as good as their float32 cos: the density there is negligible
+        near_antipode = float(np.dot(m[3:], x[3:])) < -0.9975
+        np.testing.assert_allclose(tp, tr, rtol=5e-3 if near_antipode else 2e-5, atol=2e-6)
+        assert abs(ijp - ijr) <= (5e-3 if near_antipode else 2e-5) * max(1.0, abs(ijr))

@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz by running the REFERENCE ITSELF (its sdmm headers compiled in place
+from /root/reference as oracle/_ref/libsdmm_ref.so) on small seeded inputs.  The fixtures travel to
+the GPU box (where /root/reference does not exist) and pin both the plain-C oracle restatement and
+the CUDA path.  Run in the build container:  python tools/make_golden.py
+
+Each fixture holds: the inputs (samples, initial joint/em/scal), and for every one of `iters`
+stepwise iterations the reference's per-sample log-likelihood and its state AFTER sdmm::em_step;
+then the conditioner internals after sdmm::prepare and the results of create_conditional + sample +
+posterior for seeded queries."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import refbind  # noqa: E402
+from sdmm_mitsuba_b200 import synth  # noqa: E402
+
+CASES = {
+    # name: (cells, K, samples per cell, EM iterations, queries)
+    "em_k16": (2, 16, 300, 4, 2000),
+    "em_k64": (1, 64, 640, 4, 2000),
+    "em_k128": (1, 128, 512, 2, 1000),
+}
+
+
+def make(name, C, K, N, iters, nq):
+    point6, weight, off = synth.make_samples(C, N, seed=1000 + K)
+    # a few samples the EM loop must skip (sdmm/opt/data.h:20-23, em.h:267-269)
+    weight[3] = 0.0
+    weight[N // 2] = 1e-9
+    joint, em, scal = synth.make_initial_model(C, K, seed=2000 + K)
+    o = refbind.RefCells(C, K)
+    assert o.set(joint, em, scal).all()
+    out = dict(point6=point6, weight=weight, offsets=off, joint0=joint, em0=em, scal0=scal)
+    out["derived0"] = o.derived()
+    for it in range(iters):
+        ll = np.concatenate(o.em_step(off, point6, weight, 1, want_loglik=True), axis=1)[0]
+        j, e, s = o.get()
+        out["loglik%d" % it] = ll
+        out["joint%d" % (it + 1)] = j
+        out["em%d" % (it + 1)] = e
+        out["scal%d" % (it + 1)] = s
+    out["derived_final"] = o.derived()
+    o.prepare_conditioner()
+    out["conditioner"] = o.conditioner()
+    cell, pos3, u3 = synth.make_queries(nq, C, seed=3000 + K, binned=True)
+    r, _ = o.sample_pdf(cell, pos3, u3)
+    out.update(q_cell=cell, q_pos3=pos3, q_u3=u3, q_dir=r["dir"], q_pdf=r["pdf"], q_inv_jac=r["inv_jac"],
+               q_comp=r["comp"], q_valid=r["valid"])
+    # distance of u0 to the nearest conditional-CDF entry: the tie margin of each query
+    margin = np.zeros(nq, np.float32)
+    for i in range(nq):
+        pmf, cdf, ok = o.conditional_weights(int(cell[i]), pos3[:, i])
+        margin[i] = np.abs(cdf - u3[0, i]).min() if ok else 0.0
+    out["q_tie_margin"] = margin
+    rng = np.random.default_rng(4000 + K)
+    d = rng.normal(size=(3, nq)).astype(np.float32)
+    d /= np.sqrt((d * d).sum(axis=0, keepdims=True, dtype=np.float32))
+    p, v, _ = o.pdf(cell, pos3, d)
+    out.update(p_dir=d, p_pdf=p, p_valid=v)
+    out["meta"] = np.array([C, K, N, iters, nq], np.int64)
+    path = os.path.join(ROOT, "tests", "golden", name + ".npz")
+    np.savez_compressed(path, **out)
+    print(path, "%.0f KB" % (os.path.getsize(path) / 1e3))
+
+
+if __name__ == "__main__":
+    assert refbind.available(), "build oracle/_ref first (make -C oracle ref)"
+    for name, cfg in CASES.items():
+        make(name, *cfg)
