@@ -49,7 +49,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -92,7 +92,7 @@ class ClockSampler:
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
@@ -176,7 +176,7 @@ def run_reference(args, cfg, rank, world):
     K, N, iters = cfg["K"], cfg["N"], cfg["iters"]
     vals = []
     for i in range(args.warmup + args.steps):
-        cb, secs = cpu_baseline(K, N, iters, seconds_target=6.0)
+        cb, secs = cpu_baseline(K, N, iters, seconds_target=3.0)
         if i >= args.warmup:
             vals.append((cb, secs))
     v = float(np.mean([c["value"] for c, _ in vals]))

@@ -112,6 +112,17 @@ int sdmmb_set_samples_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const fl
 int sdmmb_em_step(sdmmb_ctx* ctx, int first_cell, int n_cells, int n_iters, int with_conditioner,
                   float* d_out_loglik, void* stream);
 
+/* The per-iteration training call of the integrator for a whole batch of cells in ONE entry point
+ * with HOST buffers: the body of optimize()'s parallelFor (volpath_sdmm.cpp:287-311) = bind the cells'
+ * samples, n_iters x sdmm::em_step, sdmm::prepare(conditioner, sdmm), read the fitted mixtures back.
+ * Internally pipelined over chunks of cells (H2D of chunk c+1 and D2H of chunk c-1 overlap the fit of
+ * chunk c on separate streams), which needs PINNED host buffers to take effect; pageable buffers work
+ * but serialise.  h_out_* are nullable, laid out like sdmmb_download_cells.  Synchronous. */
+int sdmmb_optimize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* h_point6,
+                        size_t plane_stride, const float* h_weight, const uint32_t* h_cell_offsets,
+                        int n_iters, int with_conditioner, float* h_out_joint, float* h_out_em,
+                        uint32_t* h_out_scal, void* stream);
+
 /* sdmm::prepare(conditioner, joint) alone (sdmm_conditioner.h:89-100, 170-212). */
 int sdmmb_prepare_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, void* stream);
 /* Conditioner internals for parity checks, [cell][38][K] planes exactly as

@@ -23,7 +23,7 @@ SYMBOLS = [
     "sdmmb_create", "sdmmb_destroy", "sdmmb_get_error_string", "sdmmb_last_cuda_error",
     "sdmmb_num_components", "sdmmb_max_cells", "sdmmb_upload_cells", "sdmmb_download_cells",
     "sdmmb_download_derived", "sdmmb_set_samples", "sdmmb_set_samples_host", "sdmmb_em_step",
-    "sdmmb_prepare_conditioner", "sdmmb_download_conditioner", "sdmmb_sample_pdf", "sdmmb_pdf",
+    "sdmmb_optimize_host", "sdmmb_prepare_conditioner", "sdmmb_download_conditioner", "sdmmb_sample_pdf", "sdmmb_pdf",
     "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks",
 ]
@@ -70,6 +70,7 @@ def lib():
     L.sdmmb_set_samples.argtypes = [vp, i, i, fp, sz, fp, up, vp]
     L.sdmmb_set_samples_host.argtypes = [vp, i, i, fp, sz, fp, up, vp]
     L.sdmmb_em_step.argtypes = [vp, i, i, i, i, fp, vp]
+    L.sdmmb_optimize_host.argtypes = [vp, i, i, fp, sz, fp, up, i, i, fp, fp, up, vp]
     L.sdmmb_prepare_conditioner.argtypes = [vp, i, i, vp]
     L.sdmmb_download_conditioner.argtypes = [vp, i, i, fp, vp]
     L.sdmmb_sample_pdf.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]

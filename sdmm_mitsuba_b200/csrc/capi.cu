@@ -49,6 +49,11 @@ struct sdmmb_ctx {
     std::vector<cudaEvent_t> ev;  // pairs around the E-step launches of the last em_step
     int ev_used = 0;
     uint32_t item_samples = 1024;
+    // sdmmb_optimize_host pipeline: H2D copy stream, D2H stream, events
+    // [0,1] chunk copied, [2,3] chunk packed (staging buffer reusable), [4] entry fence, [5] chunk fitted
+    cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
+    cudaEvent_t pipe_ev[6] = {};
+    size_t pipe_chunk_samples = 2u << 20;
     // nccl (resolved lazily)
     void* nccl_handle = nullptr;
     int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
@@ -172,6 +177,10 @@ int sdmmb_create(sdmmb_ctx** out, int device, int max_cells, int K) {
         long v = std::atol(s);
         if (v >= 32) ctx->item_samples = (uint32_t)v;
     }
+    if (const char* s = std::getenv("SDMMB_PIPE_CHUNK_SAMPLES")) {
+        long v = std::atol(s);
+        if (v >= 1024) ctx->pipe_chunk_samples = (size_t)v;
+    }
     DeviceGuard g(device);
     const size_t ck = (size_t)max_cells * ctx->K;
     cudaError_t e;
@@ -203,6 +212,11 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2);
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
+    if (ctx->copy_stream) {
+        cudaStreamDestroy(ctx->copy_stream);
+        cudaStreamDestroy(ctx->d2h_stream);
+        for (cudaEvent_t e : ctx->pipe_ev) cudaEventDestroy(e);
+    }
     delete ctx;
     return SDMMB_OK;
 }

@@ -30,17 +30,20 @@ __global__ void __launch_bounds__(PK_THREADS) peak_ffma2_kernel(float* out, floa
     const float2 aa = make_float2(a, a), bb = make_float2(b, b);
 #pragma unroll
     for (int i = 0; i < 8; ++i) x[i] = make_float2((float)(threadIdx.x + i), (float)i);
+    unsigned long long g0, g1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
     long long t0 = clock64();
     for (int it = 0; it < PK_ITERS; ++it) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] = __ffma2_rn(x[i], aa, bb);
     }
     long long t1 = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) s += x[i].x + x[i].y;
     if (s == 123.456f) out[0] = s;
-    if (blockIdx.x == 0 && threadIdx.x == 0) clk[0] = t1 - t0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { clk[0] = t1 - t0; clk[1] = (long long)(g1 - g0); }
 }
 
 __global__ void __launch_bounds__(PK_THREADS) peak_mufu_kernel(float* out, float a) {
@@ -89,7 +92,7 @@ cudaError_t measure_peaks(float* out4) {
     long long* d_clk;
     cudaError_t err = cudaMalloc(&d_out, 16);
     if (err != cudaSuccess) return err;
-    cudaMalloc(&d_clk, 8);
+    cudaMalloc(&d_clk, 16);
     const double lane_ops = (double)grid * PK_THREADS * PK_ITERS * 8.0;
     float ms;
     err = time_best([&] { peak_ffma_kernel<<<grid, PK_THREADS>>>(d_out, 0.999f, 0.001f); }, &ms);
@@ -98,13 +101,10 @@ cudaError_t measure_peaks(float* out4) {
     err = time_best([&] { peak_ffma2_kernel<<<grid, PK_THREADS>>>(d_out, 0.999f, 0.001f, d_clk); }, &ms);
     if (err != cudaSuccess) return err;
     out4[1] = (float)(lane_ops * 4.0 / (ms * 1e-3) / 1e12);
-    // SM clock during the FFMA2 run: cycles one CTA's loop took / wall time is not available per
-    // CTA, so estimate from the whole-kernel time: every SM runs grid/sms CTAs of PK_THREADS/32
-    // warps; report the clock64 span of one CTA relative to kernel time as a utilisation-free MHz.
-    long long clk = 0;
-    cudaMemcpy(&clk, d_clk, 8, cudaMemcpyDeviceToHost);
-    // 8 CTAs are co-resident per SM and 4 such waves run back to back: kernel time ~= 4 * span
-    out4[3] = (float)((double)clk * 4.0 / (ms * 1e-3) / 1e6);
+    // SM clock during the FFMA2 run: SM cycles (clock64) over nanoseconds (%globaltimer) of one CTA's loop
+    long long clk[2] = {0, 0};
+    cudaMemcpy(clk, d_clk, 16, cudaMemcpyDeviceToHost);
+    out4[3] = clk[1] > 0 ? (float)((double)clk[0] / (double)clk[1] * 1e3) : 0.f;
     err = time_best([&] { peak_mufu_kernel<<<grid, PK_THREADS>>>(d_out, 1e-3f); }, &ms);
     if (err != cudaSuccess) return err;
     out4[2] = (float)(lane_ops / (ms * 1e-3) / 1e9);

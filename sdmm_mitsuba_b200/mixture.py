@@ -151,6 +151,27 @@ class SDMMCells:
               "sdmmb_em_step", self._h)
         return ll
 
+    def optimize_host(self, point6, weight, cell_offsets, n_iters, first_cell=0, with_conditioner=True, out=None):
+        """The integrator's per-iteration training call for a batch of cells, host buffers in and out
+        (volpath_sdmm.cpp:287-311): bind samples -> n_iters x em_step -> conditioner -> fitted mixtures.
+        `out` = (joint, em-or-None, scal) NumPy buffers (pinned memory overlaps the copies)."""
+        off = _np(np.asarray(cell_offsets), np.uint32)
+        n_cells = off.shape[0] - 1
+        point6 = _np(point6, np.float32)
+        weight = _np(weight, np.float32)
+        assert point6.shape[0] == 6 and weight.shape[0] == point6.shape[1]
+        if out is None:
+            out = (np.zeros((n_cells, JOINT_PLANES, self.K), np.float32),
+                   np.zeros((n_cells, EM_PLANES, self.K), np.float32),
+                   np.zeros((n_cells, SCALAR_WORDS), np.uint32))
+        joint, em, scal = out
+        check(self._L.sdmmb_optimize_host(self._h, first_cell, n_cells, _hp(point6), point6.shape[1], _hp(weight),
+                                          _hp(off), n_iters, 1 if with_conditioner else 0, _hp(joint), _hp(em),
+                                          _hp(scal), None), "sdmmb_optimize_host", self._h)
+        self.n_samples = int(off[-1] - off[0])
+        self._bound = (first_cell, n_cells)
+        return joint, em, scal
+
     def prepare(self, first_cell=0, n_cells=None):
         """sdmm::prepare(conditioner, sdmm) for a cell range."""
         n = self.max_cells - first_cell if n_cells is None else n_cells

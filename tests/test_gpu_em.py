@@ -203,3 +203,36 @@ def test_full_size_properties():
     w = weight.astype(np.float64)
     mean_ll = (ll.astype(np.float64) * w).sum(axis=1) / w.sum()
     assert mean_ll[3] > mean_ll[0] + 0.5, mean_ll
+
+
+@pytest.mark.parametrize("K", [64, 24])
+def test_optimize_host_pipeline_equals_stepwise_calls(K, monkeypatch):
+    """sdmmb_optimize_host (chunked copy/compute pipeline) gives bit-identical fits to
+    set_samples_host + em_step + download, also when the chunks are tiny and ragged."""
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    sizes = [700, 33, 0, 1500, 1025, 64, 900, 2000, 17]
+    C = len(sizes)
+    point6, weight, _ = synth.make_samples(1, sum(sizes), seed=13)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    joint, em, scal = synth.make_initial_model(C, K, seed=14)
+    a = SDMMCells(C, K)
+    a.upload(joint, em, scal)
+    a.set_samples(point6, weight, off)
+    a.em_step(3, with_conditioner=True)
+    ja, ea, sa = a.download()
+    qa = a.conditioner()
+    monkeypatch.setenv("SDMMB_PIPE_CHUNK_SAMPLES", "1500")
+    b = SDMMCells(C, K)
+    b.upload(joint, em, scal)
+    jb, eb, sb = b.optimize_host(point6, weight, off, 3)
+    np.testing.assert_array_equal(ja, jb)
+    np.testing.assert_array_equal(ea, eb)
+    np.testing.assert_array_equal(sa, sb)
+    np.testing.assert_array_equal(qa, b.conditioner())
+    # a second call on the same context (buffers reused) continues the stepwise EM identically
+    a.em_step(1, with_conditioner=True)
+    jb2, _, sb2 = b.optimize_host(point6, weight, off, 1)
+    ja2, _, sa2 = a.download()
+    np.testing.assert_array_equal(ja2, jb2)
+    np.testing.assert_array_equal(sa2, sb2)
