@@ -240,13 +240,8 @@ class SDMMCells:
     def allgather_records(self, cells_per_rank, group=None):
         """After a training iteration: every rank contributes the records of its contiguous slice
         (rank r owns cells [r*cells_per_rank, (r+1)*cells_per_rank)).  NCCL all-gather, in place."""
-        import torch.distributed as dist
-        rec = self.query_records()
-        world = dist.get_world_size(group)
-        flat = rec[: world * cells_per_rank].reshape(-1)
-        rank = dist.get_rank(group)
-        per = flat.numel() // world
-        dist.all_gather_into_tensor(flat, flat[rank * per:(rank + 1) * per], group=group)
+        from . import sharding
+        sharding.allgather_records(self.query_records(), cells_per_rank, group)
 
     def launch_count(self):
         v = C.c_uint64()
