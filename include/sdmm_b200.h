@@ -135,8 +135,9 @@ int sdmmb_download_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, floa
  * create_conditional(x) (sdmm_conditioner.h:102-115, 232-248) -> SDMM::sample (sdmm.h:209-273)
  * -> posterior + hsum (sdmm.h:331-339).  out_valid[i] = 0 when create_conditional failed (all
  * outputs zero); out_inv_jac[i] == 0 marks a rejected sample (sdmm_proc.cpp:436-439).
- * `binned` != 0 promises cell_idx is sorted (vertices pre-binned by cell): records are then staged
- * through shared memory per cell run; otherwise they are gathered through L2. */
+ * `binned` != 0 promises cell_idx is sorted (vertices pre-binned by cell).  Otherwise the library bins
+ * them on the device first (counting sort by cell, 3 small kernels) -- either way a CTA stages each
+ * cell's records in shared memory once per run of vertices and handles two vertices per thread. */
 int sdmmb_sample_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
                      const float* d_u3, float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
                      uint32_t* d_out_comp, uint8_t* d_out_valid, int binned, void* stream);

@@ -43,6 +43,8 @@ struct sdmmb_ctx {
     size_t stage_cap = 0;
     void* d_stage2 = nullptr;
     size_t stage2_cap = 0;
+    void* d_qscratch = nullptr;  // query binning scratch
+    size_t qscratch_cap = 0;
     // bookkeeping
     uint64_t launches = 0;
     std::string last_cuda_error;
@@ -210,7 +212,7 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_joint); cudaFree(ctx->d_em); cudaFree(ctx->d_scal); cudaFree(ctx->d_cdf);
     cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
-    cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2);
+    cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch);
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     if (ctx->copy_stream) {
         cudaStreamDestroy(ctx->copy_stream);

@@ -134,14 +134,25 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
     o.t[2] = add2(zz, prm[EREC_NMU + 2]);
     o.t[3] = mul2(lx, r);
     o.t[4] = mul2(ly, r);
-    // z = W t with W = sqrt(log2(e)/2) * L^-1 (replaces linalg::solve, R: linalg/cholesky.h:38-58)
+    // z = W t with W = sqrt(log2(e)/2) * L^-1 (replaces linalg::solve, R: linalg/cholesky.h:38-58),
+    // column by column: the five rows are independent chains and consecutive instructions share t_c
+    // (an operand repeated in the same slot comes from the reuse cache instead of the register file)
     const float2* W = prm + EREC_W;
     float2 z0 = mul2(W[0], o.t[0]);
-    float2 z1 = fma2(W[2], o.t[1], mul2(W[1], o.t[0]));
-    float2 z2 = fma2(W[5], o.t[2], fma2(W[4], o.t[1], mul2(W[3], o.t[0])));
-    float2 z3 = fma2(W[9], o.t[3], fma2(W[8], o.t[2], fma2(W[7], o.t[1], mul2(W[6], o.t[0]))));
-    float2 z4 = fma2(W[14], o.t[4],
-                     fma2(W[13], o.t[3], fma2(W[12], o.t[2], fma2(W[11], o.t[1], mul2(W[10], o.t[0])))));
+    float2 z1 = mul2(W[1], o.t[0]);
+    float2 z2 = mul2(W[3], o.t[0]);
+    float2 z3 = mul2(W[6], o.t[0]);
+    float2 z4 = mul2(W[10], o.t[0]);
+    z1 = fma2(W[2], o.t[1], z1);
+    z2 = fma2(W[4], o.t[1], z2);
+    z3 = fma2(W[7], o.t[1], z3);
+    z4 = fma2(W[11], o.t[1], z4);
+    z2 = fma2(W[5], o.t[2], z2);
+    z3 = fma2(W[8], o.t[2], z3);
+    z4 = fma2(W[12], o.t[2], z4);
+    z3 = fma2(W[9], o.t[3], z3);
+    z4 = fma2(W[13], o.t[3], z4);
+    z4 = fma2(W[14], o.t[4], z4);
     // e = |z|^2 - log2(pi_k inv_det (2 pi)^-5/2);  p = inv_jac * 2^-e       R: distributions/sdmm.h:292-294, 337
     float2 e = fma2(z0, z0, prm[EREC_NLC]);
     e = fma2(z1, z1, e);

@@ -6,13 +6,16 @@
 // as called from SDMMRenderer::sampleSurface / pdfSurface (mitsuba/src/integrators/sdmm/sdmm_proc.cpp:
 // 361-372, 419-421, 491-501, 539-545).
 //
-// Mapping: thread <-> vertex, sequential loop over the K components so that the conditional CDF is
-// the same left-to-right float32 prefix sum the reference builds (categorical.h:92-111) -- the
-// component chosen for a given uniform then only depends on the pmf bits.  The cell's query
-// records (K x 128 B) are staged in shared memory when the vertices are pre-binned by cell
-// (a CTA works on a run of vertices of ONE cell; all lanes read the same record -> broadcast LDS),
-// or gathered through L2 otherwise.  The K unnormalised conditional weights of a vertex live in a
-// per-thread shared-memory column (conflict-free) between the three passes.
+// Mapping: thread <-> a PAIR of vertices of the same cell (the two halves of the packed FP32
+// instructions), sequential loop over the K components so that the conditional CDF is the same
+// left-to-right float32 prefix sum the reference builds (categorical.h:92-111) -- the component chosen
+// for a given uniform then only depends on the pmf bits.  The cell's query records (K x 128 B) are
+// staged in shared memory once per run of vertices of that cell (all lanes read the same record ->
+// broadcast LDS); vertices that arrive unsorted are binned on the device first (counting sort).  The K
+// unnormalised conditional weights of a vertex pair live in a per-thread shared-memory column
+// (conflict-free) between the three passes.
+#include <algorithm>
+
 #include "kernels.h"
 #include "sdmm_math.cuh"
 
@@ -62,128 +65,214 @@ __device__ __forceinline__ QRec load_rec(const float4* __restrict__ base, int k)
     return r;
 }
 
-// marginal posterior pi_k N3(x; mu_a, Sigma_aa) and tangent_mean = M (x - mu_a)
-// R: sdmm_conditioner.h:242-244
-__device__ __forceinline__ float marginal_weight(const float4 r0, const float4 r1, const float4 r2,
-                                                 float x, float y, float z, float& d0, float& d1, float& d2) {
-    // r0 = (mu0, mu1, mu2, wa00), r1 = (wa10, wa11, wa20, wa21), r2 = (wa22, nlca, m00, m01)
-    d0 = x - r0.x; d1 = y - r0.y; d2 = z - r0.z;
-    float z0 = r0.w * d0;
-    float z1 = fmaf(r1.y, d1, r1.x * d0);
-    float z2 = fmaf(r2.x, d2, fmaf(r1.w, d1, r1.z * d0));
-    float e = fmaf(z0, z0, r2.y);
-    e = fmaf(z1, z1, e);
-    e = fmaf(z2, z2, e);
-    return q_ex2(-e);
-}
+// ------------------------------------------------------------------------------------------------
+// Two vertices of the same cell per thread, riding in the two halves of the packed FP32
+// instructions (FFMA2/FMUL2/FADD2); the cell's record values enter as 32-bit broadcast operands, so
+// one shared-memory read of a record serves both vertices.  Every half follows exactly the
+// reference's operation order (left-to-right CDF sums), so results do not depend on its partner.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 q_splat(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float2 q_fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 q_mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 q_add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 q_sub2(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }
 
-template <bool SMEM, bool SAMPLE>
-__device__ __forceinline__ void query_one(const float4* __restrict__ rec, int K, float* __restrict__ wcol,
-                                          int wstride, float x, float y, float z, float u0, float u1,
-                                          float u2, float& wx, float& wy, float& wz, float& out_pdf,
-                                          float& out_ij, uint32_t& out_comp, uint8_t& out_valid) {
-    // ---- pass 1: unnormalised conditional weights, sequential sum -------------------------------
-    float total = 0.f;
+struct PairIn {
+    float2 x, y, z;      // positions of the two vertices
+    float2 u0, u1, u2;   // uniforms (sample mode)
+    float2 wx, wy, wz;   // directions (pdf-only mode: input; sample mode: output)
+};
+struct PairRes {
+    float2 pdf, ij;
+    uint32_t comp[2];
+    uint8_t valid[2];
+};
+
+template <bool SAMPLE>
+__device__ __forceinline__ void query_pair(const float4* __restrict__ rec, int K, float2* __restrict__ wcol,
+                                           int wstride, PairIn& in, PairRes& out) {
+    // ---- pass 1: unnormalised conditional weights, sequential sums ------------------------------
+    float2 total = q_splat(0.f);
+#pragma unroll 2
     for (int k = 0; k < K; ++k) {
-        const float4 r0 = SMEM ? rec[k * 8 + 0] : __ldg(rec + k * 8 + 0);
-        const float4 r1 = SMEM ? rec[k * 8 + 1] : __ldg(rec + k * 8 + 1);
-        const float4 r2 = SMEM ? rec[k * 8 + 2] : __ldg(rec + k * 8 + 2);
-        float d0, d1, d2;
-        float w = marginal_weight(r0, r1, r2, x, y, z, d0, d1, d2);
+        const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
+        const float2 d0 = q_sub2(in.x, q_splat(r0.x)), d1 = q_sub2(in.y, q_splat(r0.y)), d2 = q_sub2(in.z, q_splat(r0.z));
+        const float2 z0 = q_mul2(q_splat(r0.w), d0);
+        const float2 z1 = q_fma2(q_splat(r1.y), d1, q_mul2(q_splat(r1.x), d0));
+        const float2 z2 = q_fma2(q_splat(r2.x), d2, q_fma2(q_splat(r1.w), d1, q_mul2(q_splat(r1.z), d0)));
+        float2 e = q_fma2(z0, z0, q_splat(r2.y));
+        e = q_fma2(z1, z1, e);
+        e = q_fma2(z2, z2, e);
+        const float2 w = make_float2(q_ex2(-e.x), q_ex2(-e.y));
         wcol[k * wstride] = w;
-        total = (k == 0) ? w : total + w;
+        total = (k == 0) ? w : q_add2(total, w);
     }
-    // Categorical::prepare: valid iff sum > 1e-20                    R: categorical.h:97-101
-    if (!(total > 1e-20f)) {
-        out_valid = 0; out_pdf = 0.f; out_ij = 0.f; out_comp = 0u;
-        if (SAMPLE) { wx = wy = wz = 0.f; }
-        return;
-    }
-    out_valid = 1;
-    const float inv = 1.f / total;
+    const bool v0 = total.x > 1e-20f, v1 = total.y > 1e-20f;      // R: categorical.h:97-101
+    out.valid[0] = v0 ? 1 : 0;
+    out.valid[1] = v1 ? 1 : 0;
+    const float2 inv = make_float2(1.f / total.x, 1.f / total.y);
+    out.comp[0] = out.comp[1] = 0u;
+    out.ij = q_splat(0.f);
     if (SAMPLE) {
-        // ---- pass 2: first k with cdf[k] * inv >= u0 (== enoki::binary_search on the monotone
-        // cdf, clamped to K-1), then back off over zero-pmf components   R: sdmm.h:220-233
-        int sel = K - 1;
-        float run = 0.f;
-        bool found = false;
+        // ---- pass 2: first k with cdf[k] * inv >= u0, then back off over zero-pmf components ------
+        int sel0 = K - 1, sel1 = K - 1;
+        bool f0 = false, f1 = false;
+        float2 run = q_splat(0.f);
+#pragma unroll 4
         for (int k = 0; k < K; ++k) {
-            float w = wcol[k * wstride];
-            run = (k == 0) ? w : run + w;
-            if (!found && !(run * inv < u0)) { sel = k; found = true; }
+            const float2 w = wcol[k * wstride];
+            run = (k == 0) ? w : q_add2(run, w);
+            const float2 c = q_mul2(run, inv);
+            if (!f0 && !(c.x < in.u0.x)) { sel0 = k; f0 = true; }
+            if (!f1 && !(c.y < in.u0.y)) { sel1 = k; f1 = true; }
         }
-        while (sel > 0 && wcol[sel * wstride] * inv == 0.f) --sel;
-        out_comp = (uint32_t)sel;
-        // Box-Muller                                                 R: sdmm.h:199-207, 239-245
-        float radius = sqrtf(-2.f * logf(1.f - u1));
-        float theta = 2.f * kPi * u2;
-        float sn, cs;
-        sincosf(theta, &sn, &cs);
-        float g0 = sn * radius, g1 = cs * radius;
-        const QRec r = load_rec<SMEM>(rec, sel);
-        float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
-        float tm0 = r.f(QREC_M + 0) * dx0 + r.f(QREC_M + 1) * dx1 + r.f(QREC_M + 2) * dx2;
-        float tm1 = r.f(QREC_M + 3) * dx0 + r.f(QREC_M + 4) * dx1 + r.f(QREC_M + 5) * dx2;
-        // tangent = cov_sqrt * z (lower triangular)                  R: sdmm.h:247-262
-        float t0 = r.f(QREC_LC + 0) * g0;
-        float t1 = r.f(QREC_LC + 1) * g0 + r.f(QREC_LC + 2) * g1;
-        // OffsetDirectionalTangentSpace::from                        R: offset_directional.h:62-82
-        const float max_length = kPi - 1e-1f;
-        float ox = t0 + tm0, oy = t1 + tm1;
-        float length = sqrtf(ox * ox + oy * oy);
-        float sl, cl;
-        sincosf(length, &sl, &cl);
-        float sinc = ((sl < 1e-2f) || length > max_length) ? 1.f : sl / length;
-        out_ij = (length > max_length) ? 0.f : sinc;
-        float l0 = ox * sinc, l1 = oy * sinc, l2 = cl;
-        // from = transpose(to)
-        wx = r.f(QREC_R + 0) * l0 + r.f(QREC_R + 3) * l1 + r.f(QREC_R + 6) * l2;
-        wy = r.f(QREC_R + 1) * l0 + r.f(QREC_R + 4) * l1 + r.f(QREC_R + 7) * l2;
-        wz = r.f(QREC_R + 2) * l0 + r.f(QREC_R + 5) * l1 + r.f(QREC_R + 8) * l2;
-    } else {
-        out_ij = 0.f;
-        out_comp = 0u;
+        while (sel0 > 0 && wcol[sel0 * wstride].x * inv.x == 0.f) --sel0;
+        while (sel1 > 0 && wcol[sel1 * wstride].y * inv.y == 0.f) --sel1;
+        out.comp[0] = (uint32_t)sel0;
+        out.comp[1] = (uint32_t)sel1;
+        // Box-Muller + exp map of the selected component, per vertex (scalar: once per vertex)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float x = h ? in.x.y : in.x.x, y = h ? in.y.y : in.y.x, z = h ? in.z.y : in.z.x;
+            const float u1 = h ? in.u1.y : in.u1.x, u2 = h ? in.u2.y : in.u2.x;
+            const int sel = h ? sel1 : sel0;
+            float radius = sqrtf(-2.f * logf(1.f - u1));
+            float theta = 2.f * kPi * u2;
+            float sn, cs;
+            sincosf(theta, &sn, &cs);
+            float g0 = sn * radius, g1 = cs * radius;
+            const QRec r = load_rec<true>(rec, sel);
+            float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
+            float tm0 = r.f(QREC_M + 0) * dx0 + r.f(QREC_M + 1) * dx1 + r.f(QREC_M + 2) * dx2;
+            float tm1 = r.f(QREC_M + 3) * dx0 + r.f(QREC_M + 4) * dx1 + r.f(QREC_M + 5) * dx2;
+            float t0 = r.f(QREC_LC + 0) * g0;
+            float t1 = r.f(QREC_LC + 1) * g0 + r.f(QREC_LC + 2) * g1;
+            const float max_length = kPi - 1e-1f;
+            float ox = t0 + tm0, oy = t1 + tm1;
+            float length = sqrtf(ox * ox + oy * oy);
+            float sl, cl;
+            sincosf(length, &sl, &cl);
+            float sinc = ((sl < 1e-2f) || length > max_length) ? 1.f : sl / length;
+            float ij = (length > max_length) ? 0.f : sinc;
+            float l0 = ox * sinc, l1 = oy * sinc, l2 = cl;
+            float wx = r.f(QREC_R + 0) * l0 + r.f(QREC_R + 3) * l1 + r.f(QREC_R + 6) * l2;
+            float wy = r.f(QREC_R + 1) * l0 + r.f(QREC_R + 4) * l1 + r.f(QREC_R + 7) * l2;
+            float wz = r.f(QREC_R + 2) * l0 + r.f(QREC_R + 5) * l1 + r.f(QREC_R + 8) * l2;
+            if (h) { in.wx.y = wx; in.wy.y = wy; in.wz.y = wz; out.ij.y = ij; }
+            else { in.wx.x = wx; in.wy.x = wy; in.wz.x = wz; out.ij.x = ij; }
+        }
     }
-    // ---- pass 3: conditional pdf at omega, summed over components     R: sdmm.h:331-339, 284-294
-    float pdf = 0.f;
+    // ---- pass 3: conditional pdf at omega, summed over components ---------------------------------
+    float2 pdf = q_splat(0.f);
+#pragma unroll 2
     for (int k = 0; k < K; ++k) {
-        const QRec r = load_rec<SMEM>(rec, k);
-        float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
-        float tm0 = fmaf(r.f(QREC_M + 2), dx2, fmaf(r.f(QREC_M + 1), dx1, r.f(QREC_M + 0) * dx0));
-        float tm1 = fmaf(r.f(QREC_M + 5), dx2, fmaf(r.f(QREC_M + 4), dx1, r.f(QREC_M + 3) * dx0));
-        // OffsetDirectionalTangentSpace::to                          R: offset_directional.h:39-60
-        float lx = fmaf(r.f(QREC_R + 2), wz, fmaf(r.f(QREC_R + 1), wy, r.f(QREC_R + 0) * wx));
-        float ly = fmaf(r.f(QREC_R + 5), wz, fmaf(r.f(QREC_R + 4), wy, r.f(QREC_R + 3) * wx));
-        float lz = fmaf(r.f(QREC_R + 8), wz, fmaf(r.f(QREC_R + 7), wy, r.f(QREC_R + 6) * wx));
-        float rs = rcp_sinc_from_cos(lz);
-        float ij = (lz < -0.98f) ? 0.f : rs;
-        float t0 = fmaf(lx, rs, -tm0), t1 = fmaf(ly, rs, -tm1);
-        float z0 = r.f(QREC_WC + 0) * t0;
-        float z1 = fmaf(r.f(QREC_WC + 2), t1, r.f(QREC_WC + 1) * t0);
-        float e = fmaf(z0, z0, r.f(QREC_NLCC));
-        e = fmaf(z1, z1, e);
-        float pk = ij * q_ex2(-e);
-        pdf = fmaf(pk, wcol[k * wstride] * inv, pdf);
+        const QRec r = load_rec<true>(rec, k);
+        const float2 dx0 = q_sub2(in.x, q_splat(r.f(QREC_MU + 0))), dx1 = q_sub2(in.y, q_splat(r.f(QREC_MU + 1))),
+                     dx2 = q_sub2(in.z, q_splat(r.f(QREC_MU + 2)));
+        const float2 tm0 = q_fma2(q_splat(r.f(QREC_M + 2)), dx2, q_fma2(q_splat(r.f(QREC_M + 1)), dx1, q_mul2(q_splat(r.f(QREC_M + 0)), dx0)));
+        const float2 tm1 = q_fma2(q_splat(r.f(QREC_M + 5)), dx2, q_fma2(q_splat(r.f(QREC_M + 4)), dx1, q_mul2(q_splat(r.f(QREC_M + 3)), dx0)));
+        const float2 lx = q_fma2(q_splat(r.f(QREC_R + 2)), in.wz, q_fma2(q_splat(r.f(QREC_R + 1)), in.wy, q_mul2(q_splat(r.f(QREC_R + 0)), in.wx)));
+        const float2 ly = q_fma2(q_splat(r.f(QREC_R + 5)), in.wz, q_fma2(q_splat(r.f(QREC_R + 4)), in.wy, q_mul2(q_splat(r.f(QREC_R + 3)), in.wx)));
+        const float2 lz = q_fma2(q_splat(r.f(QREC_R + 8)), in.wz, q_fma2(q_splat(r.f(QREC_R + 7)), in.wy, q_mul2(q_splat(r.f(QREC_R + 6)), in.wx)));
+        const float2 rs = make_float2(rcp_sinc_from_cos(lz.x), rcp_sinc_from_cos(lz.y));
+        const float2 ij = make_float2((lz.x < -0.98f) ? 0.f : rs.x, (lz.y < -0.98f) ? 0.f : rs.y);
+        const float2 t0 = q_fma2(lx, rs, make_float2(-tm0.x, -tm0.y)), t1 = q_fma2(ly, rs, make_float2(-tm1.x, -tm1.y));
+        const float2 z0 = q_mul2(q_splat(r.f(QREC_WC + 0)), t0);
+        const float2 z1 = q_fma2(q_splat(r.f(QREC_WC + 2)), t1, q_mul2(q_splat(r.f(QREC_WC + 1)), t0));
+        float2 e = q_fma2(z0, z0, q_splat(r.f(QREC_NLCC)));
+        e = q_fma2(z1, z1, e);
+        const float2 pk = q_mul2(ij, make_float2(q_ex2(-e.x), q_ex2(-e.y)));
+        pdf = q_fma2(pk, q_mul2(wcol[k * wstride], inv), pdf);
     }
-    out_pdf = pdf;
+    out.pdf = pdf;
+    if (!v0) { out.pdf.x = 0.f; out.ij.x = 0.f; out.comp[0] = 0u; if (SAMPLE) { in.wx.x = in.wy.x = in.wz.x = 0.f; } }
+    if (!v1) { out.pdf.y = 0.f; out.ij.y = 0.f; out.comp[1] = 0u; if (SAMPLE) { in.wx.y = in.wy.y = in.wz.y = 0.f; } }
 }
 
-// Binned path: vertices sorted by cell.  A CTA owns a contiguous tile of QTILE vertices; it walks
-// the cell runs inside the tile, staging each cell's records in shared memory once.
+// ------------------------------------------------------------------------------------------------
+// Binning on the device for vertices that arrive in arbitrary order (the renderer's case): counting
+// sort by cell -> perm[] (sorted position -> original index) and the sorted cell ids.  Cell indices
+// outside the context go to one extra trailing bucket.  The order inside a bucket is arbitrary
+// (atomic cursor); every vertex is independent, so results do not depend on it.
+// ------------------------------------------------------------------------------------------------
+__global__ void bin_count_kernel(const uint32_t* __restrict__ cell_idx, size_t n, uint32_t n_buckets,
+                                 uint32_t* __restrict__ count) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += step) {
+        uint32_t c = cell_idx[i];
+        atomicAdd(&count[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
+    }
+}
+
+// exclusive scan of count[0..n_buckets) into cursor[] by one CTA of 1024 threads
+__global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restrict__ count, uint32_t n_buckets,
+                                                        uint32_t* __restrict__ cursor) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_buckets; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < n_buckets ? count[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, x, off);
+            if ((threadIdx.x & 31) >= off) x += y;
+        }
+        if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = s_warp[threadIdx.x];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                uint32_t y = __shfl_up_sync(0xffffffffu, w, off);
+                if (threadIdx.x >= off) w += y;
+            }
+            s_warp[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t warp_excl = (threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0u;
+        const uint32_t carry = s_carry;
+        if (i < n_buckets) cursor[i] = carry + warp_excl + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + warp_excl + x;
+        __syncthreads();
+    }
+}
+
+__global__ void bin_scatter_kernel(const uint32_t* __restrict__ cell_idx, size_t n, uint32_t n_buckets,
+                                   uint32_t* __restrict__ cursor, uint32_t* __restrict__ perm,
+                                   uint32_t* __restrict__ sorted_cell) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += step) {
+        const uint32_t c = cell_idx[i];
+        const uint32_t pos = atomicAdd(&cursor[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
+        perm[pos] = (uint32_t)i;
+        sorted_cell[pos] = c;
+    }
+}
+
+// A CTA owns a contiguous tile of the cell-sorted vertex order; it walks the cell runs inside the
+// tile, staging each cell's records in shared memory once, and handles 2 * QTHREADS vertices of the run
+// per round (thread t: sorted positions pos + t and pos + QTHREADS + t).  `perm` (nullable) maps sorted
+// positions to the caller's indices.
 template <bool SAMPLE>
 __global__ void __launch_bounds__(QTHREADS)
-query_binned_kernel(QueryLaunch q, int tile) {
+query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint32_t* __restrict__ perm, int tile) {
     extern __shared__ __align__(16) unsigned char qsmem[];
     const int K = q.K;
-    float4* srec = reinterpret_cast<float4*>(qsmem);                                   // [K][8]
-    float* wcols = reinterpret_cast<float*>(qsmem + (size_t)K * QREC_FLOATS * 4);       // [K][QTHREADS]
+    float4* srec = reinterpret_cast<float4*>(qsmem);                                    // [K][8]
+    float2* wcols = reinterpret_cast<float2*>(qsmem + (size_t)K * QREC_FLOATS * 4);      // [K][QTHREADS]
     __shared__ uint32_t s_cell;
     const size_t tbegin = (size_t)blockIdx.x * tile;
     const size_t tend = (tbegin + tile < q.n) ? tbegin + tile : q.n;
     size_t pos = tbegin;
     while (pos < tend) {
         __syncthreads();
-        if (threadIdx.x == 0) s_cell = q.cell_idx[pos];
+        if (threadIdx.x == 0) s_cell = cells[pos];
         __syncthreads();
         const uint32_t cell = s_cell;
         const bool cell_ok = cell < (uint32_t)q.max_cells;
@@ -192,74 +281,57 @@ query_binned_kernel(QueryLaunch q, int tile) {
             for (int i = threadIdx.x; i < K * 8; i += QTHREADS) srec[i] = __ldg(g + i);
         }
         __syncthreads();
-        // process QTHREADS vertices at a time while they belong to `cell`
         bool run_over = false;
         while (!run_over && pos < tend) {
-            const size_t i = pos + threadIdx.x;
-            const bool mine = (i < tend) && (q.cell_idx[i] == cell);
-            if (mine) {
-                float wx = 0.f, wy = 0.f, wz = 0.f, pdf = 0.f, ij = 0.f;
-                uint32_t comp = 0;
-                uint8_t valid = 0;
+            const size_t p0 = pos + threadIdx.x, p1 = p0 + QTHREADS;
+            const bool m0 = (p0 < tend) && (cells[p0] == cell);
+            const bool m1 = (p1 < tend) && (cells[p1] == cell);
+            if (m0) {   // a sorted run is contiguous: m1 implies m0
+                const size_t i0 = perm ? perm[p0] : p0;
+                const size_t i1 = m1 ? (perm ? perm[p1] : p1) : i0;
+                PairIn in;
+                PairRes res;
+                res.pdf = res.ij = make_float2(0.f, 0.f);
+                res.comp[0] = res.comp[1] = 0u;
+                res.valid[0] = res.valid[1] = 0;
+                in.wx = in.wy = in.wz = make_float2(0.f, 0.f);
                 if (cell_ok) {
-                    const float x = q.pos3[i], y = q.pos3[q.n + i], z = q.pos3[2 * q.n + i];
+                    in.x = make_float2(q.pos3[i0], q.pos3[i1]);
+                    in.y = make_float2(q.pos3[q.n + i0], q.pos3[q.n + i1]);
+                    in.z = make_float2(q.pos3[2 * q.n + i0], q.pos3[2 * q.n + i1]);
                     if (SAMPLE) {
-                        query_one<true, true>(srec, K, wcols + threadIdx.x, QTHREADS, x, y, z, q.u3[i],
-                                              q.u3[q.n + i], q.u3[2 * q.n + i], wx, wy, wz, pdf, ij, comp, valid);
+                        in.u0 = make_float2(q.u3[i0], q.u3[i1]);
+                        in.u1 = make_float2(q.u3[q.n + i0], q.u3[q.n + i1]);
+                        in.u2 = make_float2(q.u3[2 * q.n + i0], q.u3[2 * q.n + i1]);
                     } else {
-                        wx = q.dir3[i]; wy = q.dir3[q.n + i]; wz = q.dir3[2 * q.n + i];
-                        query_one<true, false>(srec, K, wcols + threadIdx.x, QTHREADS, x, y, z, 0.f, 0.f, 0.f,
-                                               wx, wy, wz, pdf, ij, comp, valid);
+                        in.wx = make_float2(q.dir3[i0], q.dir3[i1]);
+                        in.wy = make_float2(q.dir3[q.n + i0], q.dir3[q.n + i1]);
+                        in.wz = make_float2(q.dir3[2 * q.n + i0], q.dir3[2 * q.n + i1]);
                     }
+                    query_pair<SAMPLE>(srec, K, wcols + threadIdx.x, QTHREADS, in, res);
                 }
                 if (SAMPLE) {
-                    q.out_dir3[i] = wx; q.out_dir3[q.n + i] = wy; q.out_dir3[2 * q.n + i] = wz;
-                    q.out_inv_jac[i] = ij;
-                    q.out_comp[i] = comp;
+                    q.out_dir3[i0] = in.wx.x; q.out_dir3[q.n + i0] = in.wy.x; q.out_dir3[2 * q.n + i0] = in.wz.x;
+                    q.out_inv_jac[i0] = res.ij.x;
+                    q.out_comp[i0] = res.comp[0];
                 }
-                q.out_pdf[i] = pdf;
-                if (q.out_valid) q.out_valid[i] = valid;
+                q.out_pdf[i0] = res.pdf.x;
+                if (q.out_valid) q.out_valid[i0] = res.valid[0];
+                if (m1) {
+                    if (SAMPLE) {
+                        q.out_dir3[i1] = in.wx.y; q.out_dir3[q.n + i1] = in.wy.y; q.out_dir3[2 * q.n + i1] = in.wz.y;
+                        q.out_inv_jac[i1] = res.ij.y;
+                        q.out_comp[i1] = res.comp[1];
+                    }
+                    q.out_pdf[i1] = res.pdf.y;
+                    if (q.out_valid) q.out_valid[i1] = res.valid[1];
+                }
             }
-            // the run ends inside this batch iff some thread saw another cell (or the tile ended)
-            const int n_mine = __syncthreads_count(mine ? 1 : 0);
+            const int n_mine = __syncthreads_count(m0 ? 1 : 0) + __syncthreads_count(m1 ? 1 : 0);
             pos += n_mine;
-            run_over = (n_mine < QTHREADS);
+            run_over = (n_mine < 2 * QTHREADS);
         }
     }
-}
-
-// Gather path: arbitrary vertex order; records come through L2 (one 128-byte line per component).
-template <bool SAMPLE>
-__global__ void __launch_bounds__(QTHREADS)
-query_gather_kernel(QueryLaunch q) {
-    extern __shared__ __align__(16) unsigned char qsmem[];
-    float* wcols = reinterpret_cast<float*>(qsmem);  // [K][QTHREADS]
-    const int K = q.K;
-    const size_t i = (size_t)blockIdx.x * QTHREADS + threadIdx.x;
-    if (i >= q.n) return;
-    const uint32_t cell = q.cell_idx[i];
-    float wx = 0.f, wy = 0.f, wz = 0.f, pdf = 0.f, ij = 0.f;
-    uint32_t comp = 0;
-    uint8_t valid = 0;
-    if (cell < (uint32_t)q.max_cells) {
-        const float4* rec = reinterpret_cast<const float4*>(q.qrec + (size_t)cell * K * QREC_FLOATS);
-        const float x = q.pos3[i], y = q.pos3[q.n + i], z = q.pos3[2 * q.n + i];
-        if (SAMPLE) {
-            query_one<false, true>(rec, K, wcols + threadIdx.x, QTHREADS, x, y, z, q.u3[i], q.u3[q.n + i],
-                                   q.u3[2 * q.n + i], wx, wy, wz, pdf, ij, comp, valid);
-        } else {
-            wx = q.dir3[i]; wy = q.dir3[q.n + i]; wz = q.dir3[2 * q.n + i];
-            query_one<false, false>(rec, K, wcols + threadIdx.x, QTHREADS, x, y, z, 0.f, 0.f, 0.f, wx, wy, wz,
-                                    pdf, ij, comp, valid);
-        }
-    }
-    if (SAMPLE) {
-        q.out_dir3[i] = wx; q.out_dir3[q.n + i] = wy; q.out_dir3[2 * q.n + i] = wz;
-        q.out_inv_jac[i] = ij;
-        q.out_comp[i] = comp;
-    }
-    q.out_pdf[i] = pdf;
-    if (q.out_valid) q.out_valid[i] = valid;
 }
 
 template <typename Kern>
@@ -272,30 +344,35 @@ cudaError_t set_smem(Kern kern, size_t smem) {
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     if (q.n == 0) return cudaSuccess;
     const bool sample = q.u3 != nullptr;
-    const size_t wcol_bytes = (size_t)q.K * QTHREADS * sizeof(float);
     cudaError_t e;
-    if (q.binned) {
-        const size_t smem = (size_t)q.K * QREC_FLOATS * 4 + wcol_bytes;
-        // tile: multiple of QTHREADS; ~8 tiles per SM-slot keeps the tail short without making
-        // the per-tile record staging (K*128 B) significant
-        int tile = 1024;
-        const size_t grid = (q.n + tile - 1) / tile;
-        if (sample) {
-            if ((e = set_smem(query_binned_kernel<true>, smem)) != cudaSuccess) return e;
-            query_binned_kernel<true><<<(unsigned)grid, QTHREADS, smem, st>>>(q, tile);
-        } else {
-            if ((e = set_smem(query_binned_kernel<false>, smem)) != cudaSuccess) return e;
-            query_binned_kernel<false><<<(unsigned)grid, QTHREADS, smem, st>>>(q, tile);
-        }
+    const uint32_t* cells = q.cell_idx;
+    const uint32_t* perm = nullptr;
+    if (!q.binned) {
+        // counting sort by cell into the caller-provided scratch: count[B] | cursor[B] | perm[n] | cells[n]
+        const uint32_t B = (uint32_t)q.max_cells + 1;
+        uint32_t* count = q.scratch;
+        uint32_t* cursor = count + B;
+        uint32_t* p = cursor + B;
+        uint32_t* sc = p + q.n;
+        if ((e = cudaMemsetAsync(count, 0, (size_t)B * 4, st)) != cudaSuccess) return e;
+        const unsigned grid = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
+        bin_count_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, count);
+        bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
+        bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+        cells = sc;
+        perm = p;
+    }
+    const size_t smem = (size_t)q.K * QREC_FLOATS * 4 + (size_t)q.K * QTHREADS * sizeof(float2);
+    // tile: multiple of 2 * QTHREADS; short enough that the last wave's tail is small, long enough that
+    // the per-run record staging (K * 128 B) stays negligible
+    const int tile = 2048;
+    const size_t grid = (q.n + tile - 1) / tile;
+    if (sample) {
+        if ((e = set_smem(query_pair_kernel<true>, smem)) != cudaSuccess) return e;
+        query_pair_kernel<true><<<(unsigned)grid, QTHREADS, smem, st>>>(q, cells, perm, tile);
     } else {
-        const size_t grid = (q.n + QTHREADS - 1) / QTHREADS;
-        if (sample) {
-            if ((e = set_smem(query_gather_kernel<true>, wcol_bytes)) != cudaSuccess) return e;
-            query_gather_kernel<true><<<(unsigned)grid, QTHREADS, wcol_bytes, st>>>(q);
-        } else {
-            if ((e = set_smem(query_gather_kernel<false>, wcol_bytes)) != cudaSuccess) return e;
-            query_gather_kernel<false><<<(unsigned)grid, QTHREADS, wcol_bytes, st>>>(q);
-        }
+        if ((e = set_smem(query_pair_kernel<false>, smem)) != cudaSuccess) return e;
+        query_pair_kernel<false><<<(unsigned)grid, QTHREADS, smem, st>>>(q, cells, perm, tile);
     }
     return cudaGetLastError();
 }
