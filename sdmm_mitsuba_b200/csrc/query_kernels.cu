@@ -12,8 +12,8 @@
 // for a given uniform then only depends on the pmf bits.  The cell's query records (K x 128 B) are
 // staged in shared memory once per run of vertices of that cell (all lanes read the same record ->
 // broadcast LDS); vertices that arrive unsorted are binned on the device first (counting sort).  The K
-// unnormalised conditional weights of a vertex pair live in a per-thread shared-memory column
-// (conflict-free) between the three passes.
+// unnormalised conditional weights of a vertex pair are recomputed in each of the three passes
+// (sum -> select -> pdf) instead of being parked anywhere: no per-thread storage, full occupancy.
 #include <algorithm>
 
 #include "kernels.h"
@@ -88,24 +88,83 @@ struct PairRes {
     uint8_t valid[2];
 };
 
-template <bool SAMPLE>
-__device__ __forceinline__ void query_pair(const float4* __restrict__ rec, int K, float2* __restrict__ wcol,
-                                           int wstride, PairIn& in, PairRes& out) {
-    // ---- pass 1: unnormalised conditional weights, sequential sums ------------------------------
+// unnormalised conditional weight pi_k N3(x; mu_a, Sigma_aa) of component k for both vertices
+// (R: sdmm_conditioner.h:242-244).  Called from all three passes: recomputing the K weights costs
+// 13 packed instructions per component but needs no per-thread storage, so occupancy is bounded by
+// registers, not by a K x threads shared-memory column.  Same instruction sequence each time ->
+// bit-identical weights in every pass.
+__device__ __forceinline__ float2 pair_weight(const float4* __restrict__ rec, int k, const PairIn& in) {
+    const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
+    // r0 = (mu0, mu1, mu2, wa00), r1 = (wa10, wa11, wa20, wa21), r2 = (wa22, nlca, m00, m01)
+    const float2 d0 = q_sub2(in.x, q_splat(r0.x)), d1 = q_sub2(in.y, q_splat(r0.y)), d2 = q_sub2(in.z, q_splat(r0.z));
+    const float2 z0 = q_mul2(q_splat(r0.w), d0);
+    const float2 z1 = q_fma2(q_splat(r1.y), d1, q_mul2(q_splat(r1.x), d0));
+    const float2 z2 = q_fma2(q_splat(r2.x), d2, q_fma2(q_splat(r1.w), d1, q_mul2(q_splat(r1.z), d0)));
+    float2 e = q_fma2(z0, z0, q_splat(r2.y));
+    e = q_fma2(z1, z1, e);
+    e = q_fma2(z2, z2, e);
+    return make_float2(q_ex2(-e.x), q_ex2(-e.y));
+}
+
+// The same weight for ONE vertex with scalar instructions (each half of a packed FFMA2 is an IEEE fma,
+// so this is bit-identical to the corresponding half of pair_weight).
+__device__ __forceinline__ float single_weight(const float4* __restrict__ rec, int k, float x, float y, float z) {
+    const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
+    const float d0 = x - r0.x, d1 = y - r0.y, d2 = z - r0.z;
+    const float z0 = r0.w * d0;
+    const float z1 = fmaf(r1.y, d1, r1.x * d0);
+    const float z2 = fmaf(r2.x, d2, fmaf(r1.w, d1, r1.z * d0));
+    float e = fmaf(z0, z0, r2.y);
+    e = fmaf(z1, z1, e);
+    e = fmaf(z2, z2, e);
+    return q_ex2(-e);
+}
+
+// First k with cdf[k] = run_k * inv >= u0 for one vertex, given the running sums at the end of every
+// block of QBLOCK components (`pref`, stride `ps`): find the block, then redo the sequential sum inside
+// it -- the association order, hence every cdf bit, is that of the full left-to-right scan
+// (== enoki::binary_search on the monotone cdf clamped to K-1; R: sdmm.h:220-233).
+constexpr int QBLOCK = 8;
+template <int K, int H>
+__device__ __forceinline__ int select_component(const float4* __restrict__ rec, const float2* __restrict__ pref,
+                                                int ps, float x, float y, float z, float u0, float inv) {
+    int b = K / QBLOCK;
+#pragma unroll
+    for (int j = K / QBLOCK - 1; j >= 0; --j) {
+        const float2 p = pref[j * ps];
+        if (!((H ? p.y : p.x) * inv < u0)) b = j;
+    }
+    int sel = K - 1;
+    if (b < K / QBLOCK) {
+        float run = 0.f;
+        if (b > 0) { const float2 p = pref[(b - 1) * ps]; run = H ? p.y : p.x; }
+        bool found = false;
+#pragma unroll
+        for (int j = 0; j < QBLOCK; ++j) {
+            const int k = b * QBLOCK + j;
+            const float w = single_weight(rec, k, x, y, z);
+            run = (k == 0) ? w : run + w;
+            if (!found && !(run * inv < u0)) { sel = k; found = true; }
+        }
+    }
+    // back off over zero-pmf components
+    while (sel > 0 && single_weight(rec, sel, x, y, z) * inv == 0.f) --sel;
+    return sel;
+}
+
+template <bool SAMPLE, int K>
+__device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float2* __restrict__ pref, int ps,
+                                           PairIn& in, PairRes& out) {
+    // ---- pass 1: sequential sum of the unnormalised conditional weights ---------------------------
     float2 total = q_splat(0.f);
-#pragma unroll 2
-    for (int k = 0; k < K; ++k) {
-        const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
-        const float2 d0 = q_sub2(in.x, q_splat(r0.x)), d1 = q_sub2(in.y, q_splat(r0.y)), d2 = q_sub2(in.z, q_splat(r0.z));
-        const float2 z0 = q_mul2(q_splat(r0.w), d0);
-        const float2 z1 = q_fma2(q_splat(r1.y), d1, q_mul2(q_splat(r1.x), d0));
-        const float2 z2 = q_fma2(q_splat(r2.x), d2, q_fma2(q_splat(r1.w), d1, q_mul2(q_splat(r1.z), d0)));
-        float2 e = q_fma2(z0, z0, q_splat(r2.y));
-        e = q_fma2(z1, z1, e);
-        e = q_fma2(z2, z2, e);
-        const float2 w = make_float2(q_ex2(-e.x), q_ex2(-e.y));
-        wcol[k * wstride] = w;
-        total = (k == 0) ? w : q_add2(total, w);
+#pragma unroll 1
+    for (int b = 0; b < K / QBLOCK; ++b) {
+#pragma unroll
+        for (int j = 0; j < QBLOCK; ++j) {
+            const float2 w = pair_weight(rec, b * QBLOCK + j, in);
+            total = (b == 0 && j == 0) ? w : q_add2(total, w);
+        }
+        if (SAMPLE) pref[b * ps] = total;   // running sums at the block ends, for pass 2
     }
     const bool v0 = total.x > 1e-20f, v1 = total.y > 1e-20f;      // R: categorical.h:97-101
     out.valid[0] = v0 ? 1 : 0;
@@ -114,20 +173,9 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, int K
     out.comp[0] = out.comp[1] = 0u;
     out.ij = q_splat(0.f);
     if (SAMPLE) {
-        // ---- pass 2: first k with cdf[k] * inv >= u0, then back off over zero-pmf components ------
-        int sel0 = K - 1, sel1 = K - 1;
-        bool f0 = false, f1 = false;
-        float2 run = q_splat(0.f);
-#pragma unroll 4
-        for (int k = 0; k < K; ++k) {
-            const float2 w = wcol[k * wstride];
-            run = (k == 0) ? w : q_add2(run, w);
-            const float2 c = q_mul2(run, inv);
-            if (!f0 && !(c.x < in.u0.x)) { sel0 = k; f0 = true; }
-            if (!f1 && !(c.y < in.u0.y)) { sel1 = k; f1 = true; }
-        }
-        while (sel0 > 0 && wcol[sel0 * wstride].x * inv.x == 0.f) --sel0;
-        while (sel1 > 0 && wcol[sel1 * wstride].y * inv.y == 0.f) --sel1;
+        // ---- pass 2: component select from the block prefix sums ---------------------------------
+        const int sel0 = select_component<K, 0>(rec, pref, ps, in.x.x, in.y.x, in.z.x, in.u0.x, inv.x);
+        const int sel1 = select_component<K, 1>(rec, pref, ps, in.x.y, in.y.y, in.z.y, in.u0.y, inv.y);
         out.comp[0] = (uint32_t)sel0;
         out.comp[1] = (uint32_t)sel1;
         // Box-Muller + exp map of the selected component, per vertex (scalar: once per vertex)
@@ -166,6 +214,7 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, int K
     float2 pdf = q_splat(0.f);
 #pragma unroll 2
     for (int k = 0; k < K; ++k) {
+        const float2 wk = pair_weight(rec, k, in);
         const QRec r = load_rec<true>(rec, k);
         const float2 dx0 = q_sub2(in.x, q_splat(r.f(QREC_MU + 0))), dx1 = q_sub2(in.y, q_splat(r.f(QREC_MU + 1))),
                      dx2 = q_sub2(in.z, q_splat(r.f(QREC_MU + 2)));
@@ -182,7 +231,7 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, int K
         float2 e = q_fma2(z0, z0, q_splat(r.f(QREC_NLCC)));
         e = q_fma2(z1, z1, e);
         const float2 pk = q_mul2(ij, make_float2(q_ex2(-e.x), q_ex2(-e.y)));
-        pdf = q_fma2(pk, q_mul2(wcol[k * wstride], inv), pdf);
+        pdf = q_fma2(pk, q_mul2(wk, inv), pdf);
     }
     out.pdf = pdf;
     if (!v0) { out.pdf.x = 0.f; out.ij.x = 0.f; out.comp[0] = 0u; if (SAMPLE) { in.wx.x = in.wy.x = in.wz.x = 0.f; } }
@@ -259,13 +308,11 @@ __global__ void bin_scatter_kernel(const uint32_t* __restrict__ cell_idx, size_t
 // tile, staging each cell's records in shared memory once, and handles 2 * QTHREADS vertices of the run
 // per round (thread t: sorted positions pos + t and pos + QTHREADS + t).  `perm` (nullable) maps sorted
 // positions to the caller's indices.
-template <bool SAMPLE>
+template <bool SAMPLE, int K>
 __global__ void __launch_bounds__(QTHREADS)
 query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint32_t* __restrict__ perm, int tile) {
-    extern __shared__ __align__(16) unsigned char qsmem[];
-    const int K = q.K;
-    float4* srec = reinterpret_cast<float4*>(qsmem);                                    // [K][8]
-    float2* wcols = reinterpret_cast<float2*>(qsmem + (size_t)K * QREC_FLOATS * 4);      // [K][QTHREADS]
+    __shared__ __align__(16) float4 srec[K * 8];                                        // [K][8]
+    __shared__ float2 spref[SAMPLE ? (K / QBLOCK) * QTHREADS : 1];                      // [K/8][QTHREADS]
     __shared__ uint32_t s_cell;
     const size_t tbegin = (size_t)blockIdx.x * tile;
     const size_t tend = (tbegin + tile < q.n) ? tbegin + tile : q.n;
@@ -308,7 +355,7 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
                         in.wy = make_float2(q.dir3[q.n + i0], q.dir3[q.n + i1]);
                         in.wz = make_float2(q.dir3[2 * q.n + i0], q.dir3[2 * q.n + i1]);
                     }
-                    query_pair<SAMPLE>(srec, K, wcols + threadIdx.x, QTHREADS, in, res);
+                    query_pair<SAMPLE, K>(srec, spref + (SAMPLE ? threadIdx.x : 0), QTHREADS, in, res);
                 }
                 if (SAMPLE) {
                     q.out_dir3[i0] = in.wx.x; q.out_dir3[q.n + i0] = in.wy.x; q.out_dir3[2 * q.n + i0] = in.wz.x;
@@ -334,11 +381,6 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
     }
 }
 
-template <typename Kern>
-cudaError_t set_smem(Kern kern, size_t smem) {
-    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-}
-
 }  // namespace
 
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
@@ -362,18 +404,23 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
         cells = sc;
         perm = p;
     }
-    const size_t smem = (size_t)q.K * QREC_FLOATS * 4 + (size_t)q.K * QTHREADS * sizeof(float2);
     // tile: multiple of 2 * QTHREADS; short enough that the last wave's tail is small, long enough that
     // the per-run record staging (K * 128 B) stays negligible
     const int tile = 2048;
-    const size_t grid = (q.n + tile - 1) / tile;
-    if (sample) {
-        if ((e = set_smem(query_pair_kernel<true>, smem)) != cudaSuccess) return e;
-        query_pair_kernel<true><<<(unsigned)grid, QTHREADS, smem, st>>>(q, cells, perm, tile);
-    } else {
-        if ((e = set_smem(query_pair_kernel<false>, smem)) != cudaSuccess) return e;
-        query_pair_kernel<false><<<(unsigned)grid, QTHREADS, smem, st>>>(q, cells, perm, tile);
+    const unsigned grid = (unsigned)((q.n + tile - 1) / tile);
+#define SDMMB_QLAUNCH(KK)                                                                         \
+    do {                                                                                          \
+        if (sample) query_pair_kernel<true, KK><<<grid, QTHREADS, 0, st>>>(q, cells, perm, tile);  \
+        else query_pair_kernel<false, KK><<<grid, QTHREADS, 0, st>>>(q, cells, perm, tile);        \
+    } while (0)
+    switch (q.K) {
+        case 16: SDMMB_QLAUNCH(16); break;
+        case 32: SDMMB_QLAUNCH(32); break;
+        case 64: SDMMB_QLAUNCH(64); break;
+        case 128: SDMMB_QLAUNCH(128); break;
+        default: return cudaErrorInvalidValue;
     }
+#undef SDMMB_QLAUNCH
     return cudaGetLastError();
 }
 
