@@ -304,6 +304,58 @@ __global__ void bin_scatter_kernel(const uint32_t* __restrict__ cell_idx, size_t
     }
 }
 
+// Shared-memory variants for bucket counts that fit on chip (2 * n_buckets words): a CTA histograms
+// its contiguous chunk of vertices with shared-memory atomics and touches global memory once per
+// non-empty bucket, instead of one contended global atomic per vertex.
+__global__ void __launch_bounds__(512) bin_count_smem_kernel(const uint32_t* __restrict__ cell_idx, size_t n,
+                                                             uint32_t n_buckets, uint32_t* __restrict__ count) {
+    extern __shared__ uint32_t sh_bins[];
+    for (uint32_t b = threadIdx.x; b < n_buckets; b += blockDim.x) sh_bins[b] = 0;
+    __syncthreads();
+    const size_t chunk = (n + gridDim.x - 1) / gridDim.x;
+    const size_t begin = (size_t)blockIdx.x * chunk, end = begin + chunk < n ? begin + chunk : n;
+    for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
+        const uint32_t c = cell_idx[i];
+        atomicAdd(&sh_bins[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < n_buckets; b += blockDim.x) {
+        const uint32_t v = sh_bins[b];
+        if (v) atomicAdd(&count[b], v);
+    }
+}
+
+__global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* __restrict__ cell_idx, size_t n,
+                                                               uint32_t n_buckets, uint32_t* __restrict__ cursor,
+                                                               uint32_t* __restrict__ perm,
+                                                               uint32_t* __restrict__ sorted_cell) {
+    extern __shared__ uint32_t sh_bins[];
+    uint32_t* sh_cnt = sh_bins;               // local count, then local cursor
+    uint32_t* sh_base = sh_bins + n_buckets;  // this CTA's reserved range per bucket
+    for (uint32_t b = threadIdx.x; b < n_buckets; b += blockDim.x) sh_cnt[b] = 0;
+    __syncthreads();
+    const size_t chunk = (n + gridDim.x - 1) / gridDim.x;
+    const size_t begin = (size_t)blockIdx.x * chunk, end = begin + chunk < n ? begin + chunk : n;
+    for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
+        const uint32_t c = cell_idx[i];
+        atomicAdd(&sh_cnt[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < n_buckets; b += blockDim.x) {
+        const uint32_t v = sh_cnt[b];
+        sh_base[b] = v ? atomicAdd(&cursor[b], v) : 0u;
+        sh_cnt[b] = 0;
+    }
+    __syncthreads();
+    for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
+        const uint32_t c = cell_idx[i];
+        const uint32_t b = c < n_buckets - 1 ? c : n_buckets - 1;
+        const uint32_t pos = sh_base[b] + atomicAdd(&sh_cnt[b], 1u);
+        perm[pos] = (uint32_t)i;
+        sorted_cell[pos] = c;
+    }
+}
+
 // A CTA owns a contiguous tile of the cell-sorted vertex order; it walks the cell runs inside the
 // tile, staging each cell's records in shared memory once, and handles 2 * QTHREADS vertices of the run
 // per round (thread t: sorted positions pos + t and pos + QTHREADS + t).  `perm` (nullable) maps sorted
@@ -397,10 +449,25 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
         uint32_t* p = cursor + B;
         uint32_t* sc = p + q.n;
         if ((e = cudaMemsetAsync(count, 0, (size_t)B * 4, st)) != cudaSuccess) return e;
-        const unsigned grid = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
-        bin_count_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, count);
-        bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
-        bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+        const size_t hist_smem = (size_t)2 * B * sizeof(uint32_t);
+        if (hist_smem <= 160 * 1024) {
+            static bool configured = false;
+            if (!configured) {
+                if ((e = cudaFuncSetAttribute(bin_count_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
+                if ((e = cudaFuncSetAttribute(bin_scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
+                configured = true;
+            }
+            // one chunk per CTA; few, fat CTAs keep the per-bucket global atomics rare
+            const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((q.n + 8191) / 8192, 148 * 2));
+            bin_count_smem_kernel<<<grid, 512, hist_smem / 2, st>>>(q.cell_idx, q.n, B, count);
+            bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
+            bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+        } else {
+            const unsigned grid = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
+            bin_count_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, count);
+            bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
+            bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+        }
         cells = sc;
         perm = p;
     }
