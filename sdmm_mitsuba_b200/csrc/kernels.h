@@ -90,7 +90,7 @@ struct QueryLaunch {
     uint8_t* out_valid;
     int binned;
     int max_cells;
-    uint32_t* scratch;  // unbinned only: 2 * (max_cells + 1) + 2 * n words (see launch_query)
+    uint32_t* scratch;  // unbinned only: 2 * (max_cells + 1) + 17 * n + 4 words (see launch_query)
 };
 
 cudaError_t launch_pack(const float* point6, size_t stride, const float* weight, float4* rec, size_t n,

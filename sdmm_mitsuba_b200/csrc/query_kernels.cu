@@ -240,7 +240,7 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float
 
 // ------------------------------------------------------------------------------------------------
 // Binning on the device for vertices that arrive in arbitrary order (the renderer's case): counting
-// sort by cell -> perm[] (sorted position -> original index) and the sorted cell ids.  Cell indices
+// sort by cell -> sorted 32-byte input records + the inverse permutation.  Cell indices
 // outside the context go to one extra trailing bucket.  The order inside a bucket is arbitrary
 // (atomic cursor); every vertex is independent, so results do not depend on it.
 // ------------------------------------------------------------------------------------------------
@@ -291,16 +291,33 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restri
     }
 }
 
+// What the scatter pass moves besides the index: the vertex's inputs as ONE 32-byte record
+//   (x, y, z, a0) (a1, a2, original index, cell)      a = uniforms (sample mode) or direction (pdf mode)
+// so that random DRAM access happens in whole 32-byte sectors (one scattered write here, one scattered
+// read in the un-permute pass) instead of thirteen scattered 4-byte accesses per vertex.
+struct BinPayload {
+    const float* pos3;   // 3 planes of n
+    const float* in3;    // 3 planes of n: u3 or dir3
+    float4* qin;         // [n][2] sorted input records
+    uint32_t* invperm;   // [n] original index -> sorted position
+};
+
+__device__ __forceinline__ void write_sorted_record(const BinPayload& pl, size_t n, size_t i, uint32_t pos, uint32_t c) {
+    const float4 a = make_float4(pl.pos3[i], pl.pos3[n + i], pl.pos3[2 * n + i], pl.in3[i]);
+    const float4 b = make_float4(pl.in3[n + i], pl.in3[2 * n + i], __uint_as_float((uint32_t)i), __uint_as_float(c));
+    pl.qin[2 * (size_t)pos] = a;
+    pl.qin[2 * (size_t)pos + 1] = b;
+    pl.invperm[i] = pos;
+}
+
 __global__ void bin_scatter_kernel(const uint32_t* __restrict__ cell_idx, size_t n, uint32_t n_buckets,
-                                   uint32_t* __restrict__ cursor, uint32_t* __restrict__ perm,
-                                   uint32_t* __restrict__ sorted_cell) {
+                                   uint32_t* __restrict__ cursor, BinPayload pl) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t step = (size_t)gridDim.x * blockDim.x;
     for (; i < n; i += step) {
         const uint32_t c = cell_idx[i];
         const uint32_t pos = atomicAdd(&cursor[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
-        perm[pos] = (uint32_t)i;
-        sorted_cell[pos] = c;
+        write_sorted_record(pl, n, i, pos, c);
     }
 }
 
@@ -327,8 +344,7 @@ __global__ void __launch_bounds__(512) bin_count_smem_kernel(const uint32_t* __r
 
 __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* __restrict__ cell_idx, size_t n,
                                                                uint32_t n_buckets, uint32_t* __restrict__ cursor,
-                                                               uint32_t* __restrict__ perm,
-                                                               uint32_t* __restrict__ sorted_cell) {
+                                                               BinPayload pl) {
     extern __shared__ uint32_t sh_bins[];
     uint32_t* sh_cnt = sh_bins;               // local count, then local cursor
     uint32_t* sh_base = sh_bins + n_buckets;  // this CTA's reserved range per bucket
@@ -351,18 +367,20 @@ __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* _
         const uint32_t c = cell_idx[i];
         const uint32_t b = c < n_buckets - 1 ? c : n_buckets - 1;
         const uint32_t pos = sh_base[b] + atomicAdd(&sh_cnt[b], 1u);
-        perm[pos] = (uint32_t)i;
-        sorted_cell[pos] = c;
+        write_sorted_record(pl, n, i, pos, c);
     }
 }
 
 // A CTA owns a contiguous tile of the cell-sorted vertex order; it walks the cell runs inside the
 // tile, staging each cell's records in shared memory once, and handles 2 * QTHREADS vertices of the run
-// per round (thread t: sorted positions pos + t and pos + QTHREADS + t).  `perm` (nullable) maps sorted
-// positions to the caller's indices.
-template <bool SAMPLE, int K>
+// per round (thread t: sorted positions pos + t and pos + QTHREADS + t).
+//   REC = false: the caller's arrays are already sorted by cell: SoA planes in, SoA planes out.
+//   REC = true : device-binned vertices: packed 32-byte records in (`qin`, written by the scatter pass)
+//                and out (`qout`: (dx, dy, dz, pdf) (inv_jac, comp, valid, -)), both in sorted order,
+//                i.e. coalesced; query_unpermute_kernel puts the results back in the caller's order.
+template <bool SAMPLE, int K, bool REC>
 __global__ void __launch_bounds__(QTHREADS)
-query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint32_t* __restrict__ perm, int tile) {
+query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restrict__ qout, int tile) {
     __shared__ __align__(16) float4 srec[K * 8];                                        // [K][8]
     __shared__ float2 spref[SAMPLE ? (K / QBLOCK) * QTHREADS : 1];                      // [K/8][QTHREADS]
     __shared__ uint32_t s_cell;
@@ -371,7 +389,7 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
     size_t pos = tbegin;
     while (pos < tend) {
         __syncthreads();
-        if (threadIdx.x == 0) s_cell = cells[pos];
+        if (threadIdx.x == 0) s_cell = REC ? __float_as_uint(qin[2 * pos + 1].w) : q.cell_idx[pos];
         __syncthreads();
         const uint32_t cell = s_cell;
         const bool cell_ok = cell < (uint32_t)q.max_cells;
@@ -383,11 +401,20 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
         bool run_over = false;
         while (!run_over && pos < tend) {
             const size_t p0 = pos + threadIdx.x, p1 = p0 + QTHREADS;
-            const bool m0 = (p0 < tend) && (cells[p0] == cell);
-            const bool m1 = (p1 < tend) && (cells[p1] == cell);
+            float4 a0, b0, a1, b1;   // REC: the two vertices' input records
+            bool m0, m1;
+            if (REC) {
+                m0 = p0 < tend;
+                m1 = p1 < tend;
+                if (m0) { a0 = qin[2 * p0]; b0 = qin[2 * p0 + 1]; m0 = __float_as_uint(b0.w) == cell; }
+                if (m1) { a1 = qin[2 * p1]; b1 = qin[2 * p1 + 1]; m1 = __float_as_uint(b1.w) == cell; }
+            } else {
+                m0 = (p0 < tend) && (q.cell_idx[p0] == cell);
+                m1 = (p1 < tend) && (q.cell_idx[p1] == cell);
+            }
             if (m0) {   // a sorted run is contiguous: m1 implies m0
-                const size_t i0 = perm ? perm[p0] : p0;
-                const size_t i1 = m1 ? (perm ? perm[p1] : p1) : i0;
+                if (!m1) { a1 = a0; b1 = b0; }
+                const size_t i1 = m1 ? p1 : p0;
                 PairIn in;
                 PairRes res;
                 res.pdf = res.ij = make_float2(0.f, 0.f);
@@ -395,35 +422,51 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
                 res.valid[0] = res.valid[1] = 0;
                 in.wx = in.wy = in.wz = make_float2(0.f, 0.f);
                 if (cell_ok) {
-                    in.x = make_float2(q.pos3[i0], q.pos3[i1]);
-                    in.y = make_float2(q.pos3[q.n + i0], q.pos3[q.n + i1]);
-                    in.z = make_float2(q.pos3[2 * q.n + i0], q.pos3[2 * q.n + i1]);
-                    if (SAMPLE) {
-                        in.u0 = make_float2(q.u3[i0], q.u3[i1]);
-                        in.u1 = make_float2(q.u3[q.n + i0], q.u3[q.n + i1]);
-                        in.u2 = make_float2(q.u3[2 * q.n + i0], q.u3[2 * q.n + i1]);
+                    float2 c0, c1, c2;   // uniforms or direction
+                    if (REC) {
+                        in.x = make_float2(a0.x, a1.x);
+                        in.y = make_float2(a0.y, a1.y);
+                        in.z = make_float2(a0.z, a1.z);
+                        c0 = make_float2(a0.w, a1.w);
+                        c1 = make_float2(b0.x, b1.x);
+                        c2 = make_float2(b0.y, b1.y);
                     } else {
-                        in.wx = make_float2(q.dir3[i0], q.dir3[i1]);
-                        in.wy = make_float2(q.dir3[q.n + i0], q.dir3[q.n + i1]);
-                        in.wz = make_float2(q.dir3[2 * q.n + i0], q.dir3[2 * q.n + i1]);
+                        const float* in3 = SAMPLE ? q.u3 : q.dir3;
+                        in.x = make_float2(q.pos3[p0], q.pos3[i1]);
+                        in.y = make_float2(q.pos3[q.n + p0], q.pos3[q.n + i1]);
+                        in.z = make_float2(q.pos3[2 * q.n + p0], q.pos3[2 * q.n + i1]);
+                        c0 = make_float2(in3[p0], in3[i1]);
+                        c1 = make_float2(in3[q.n + p0], in3[q.n + i1]);
+                        c2 = make_float2(in3[2 * q.n + p0], in3[2 * q.n + i1]);
                     }
+                    if (SAMPLE) { in.u0 = c0; in.u1 = c1; in.u2 = c2; }
+                    else { in.wx = c0; in.wy = c1; in.wz = c2; }
                     query_pair<SAMPLE, K>(srec, spref + (SAMPLE ? threadIdx.x : 0), QTHREADS, in, res);
                 }
-                if (SAMPLE) {
-                    q.out_dir3[i0] = in.wx.x; q.out_dir3[q.n + i0] = in.wy.x; q.out_dir3[2 * q.n + i0] = in.wz.x;
-                    q.out_inv_jac[i0] = res.ij.x;
-                    q.out_comp[i0] = res.comp[0];
-                }
-                q.out_pdf[i0] = res.pdf.x;
-                if (q.out_valid) q.out_valid[i0] = res.valid[0];
-                if (m1) {
-                    if (SAMPLE) {
-                        q.out_dir3[i1] = in.wx.y; q.out_dir3[q.n + i1] = in.wy.y; q.out_dir3[2 * q.n + i1] = in.wz.y;
-                        q.out_inv_jac[i1] = res.ij.y;
-                        q.out_comp[i1] = res.comp[1];
+                if (REC) {
+                    qout[2 * p0] = make_float4(in.wx.x, in.wy.x, in.wz.x, res.pdf.x);
+                    qout[2 * p0 + 1] = make_float4(res.ij.x, __uint_as_float(res.comp[0]), __uint_as_float((uint32_t)res.valid[0]), 0.f);
+                    if (m1) {
+                        qout[2 * p1] = make_float4(in.wx.y, in.wy.y, in.wz.y, res.pdf.y);
+                        qout[2 * p1 + 1] = make_float4(res.ij.y, __uint_as_float(res.comp[1]), __uint_as_float((uint32_t)res.valid[1]), 0.f);
                     }
-                    q.out_pdf[i1] = res.pdf.y;
-                    if (q.out_valid) q.out_valid[i1] = res.valid[1];
+                } else {
+                    if (SAMPLE) {
+                        q.out_dir3[p0] = in.wx.x; q.out_dir3[q.n + p0] = in.wy.x; q.out_dir3[2 * q.n + p0] = in.wz.x;
+                        q.out_inv_jac[p0] = res.ij.x;
+                        q.out_comp[p0] = res.comp[0];
+                    }
+                    q.out_pdf[p0] = res.pdf.x;
+                    if (q.out_valid) q.out_valid[p0] = res.valid[0];
+                    if (m1) {
+                        if (SAMPLE) {
+                            q.out_dir3[p1] = in.wx.y; q.out_dir3[q.n + p1] = in.wy.y; q.out_dir3[2 * q.n + p1] = in.wz.y;
+                            q.out_inv_jac[p1] = res.ij.y;
+                            q.out_comp[p1] = res.comp[1];
+                        }
+                        q.out_pdf[p1] = res.pdf.y;
+                        if (q.out_valid) q.out_valid[p1] = res.valid[1];
+                    }
                 }
             }
             const int n_mine = __syncthreads_count(m0 ? 1 : 0) + __syncthreads_count(m1 ? 1 : 0);
@@ -433,21 +476,48 @@ query_pair_kernel(QueryLaunch q, const uint32_t* __restrict__ cells, const uint3
     }
 }
 
+// Results of device-binned vertices back into the caller's order: thread i reads its sorted position
+// (coalesced), fetches the 32-byte result record there (one scattered sector) and writes the output
+// planes coalesced.
+template <bool SAMPLE>
+__global__ void query_unpermute_kernel(QueryLaunch q, const uint32_t* __restrict__ invperm,
+                                       const float4* __restrict__ qout) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (; i < q.n; i += step) {
+        const size_t p = invperm[i];
+        const float4 a = __ldg(qout + 2 * p), b = __ldg(qout + 2 * p + 1);
+        if (SAMPLE) {
+            q.out_dir3[i] = a.x; q.out_dir3[q.n + i] = a.y; q.out_dir3[2 * q.n + i] = a.z;
+            q.out_inv_jac[i] = b.x;
+            q.out_comp[i] = __float_as_uint(b.y);
+        }
+        q.out_pdf[i] = a.w;
+        if (q.out_valid) q.out_valid[i] = (uint8_t)__float_as_uint(b.z);
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     if (q.n == 0) return cudaSuccess;
     const bool sample = q.u3 != nullptr;
     cudaError_t e;
-    const uint32_t* cells = q.cell_idx;
-    const uint32_t* perm = nullptr;
+    float4* qin = nullptr;
+    float4* qout = nullptr;
+    uint32_t* invperm = nullptr;
     if (!q.binned) {
-        // counting sort by cell into the caller-provided scratch: count[B] | cursor[B] | perm[n] | cells[n]
+        // counting sort by cell into the caller-provided scratch (words):
+        //   count[B] | cursor[B] | invperm[n] | pad to 16 B | qin[8 n] | qout[8 n]
         const uint32_t B = (uint32_t)q.max_cells + 1;
         uint32_t* count = q.scratch;
         uint32_t* cursor = count + B;
-        uint32_t* p = cursor + B;
-        uint32_t* sc = p + q.n;
+        invperm = cursor + B;
+        size_t off = (size_t)2 * B + q.n;
+        off = (off + 3) & ~(size_t)3;
+        qin = reinterpret_cast<float4*>(q.scratch + off);
+        qout = qin + 2 * q.n;
+        BinPayload pl{q.pos3, sample ? q.u3 : q.dir3, qin, invperm};
         if ((e = cudaMemsetAsync(count, 0, (size_t)B * 4, st)) != cudaSuccess) return e;
         const size_t hist_smem = (size_t)2 * B * sizeof(uint32_t);
         if (hist_smem <= 160 * 1024) {
@@ -461,24 +531,24 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
             const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((q.n + 8191) / 8192, 148 * 2));
             bin_count_smem_kernel<<<grid, 512, hist_smem / 2, st>>>(q.cell_idx, q.n, B, count);
             bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
-            bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+            bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(q.cell_idx, q.n, B, cursor, pl);
         } else {
             const unsigned grid = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
             bin_count_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, count);
             bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
-            bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, p, sc);
+            bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, pl);
         }
-        cells = sc;
-        perm = p;
     }
     // tile: multiple of 2 * QTHREADS; short enough that the last wave's tail is small, long enough that
     // the per-run record staging (K * 128 B) stays negligible
     const int tile = 2048;
     const unsigned grid = (unsigned)((q.n + tile - 1) / tile);
-#define SDMMB_QLAUNCH(KK)                                                                         \
-    do {                                                                                          \
-        if (sample) query_pair_kernel<true, KK><<<grid, QTHREADS, 0, st>>>(q, cells, perm, tile);  \
-        else query_pair_kernel<false, KK><<<grid, QTHREADS, 0, st>>>(q, cells, perm, tile);        \
+#define SDMMB_QLAUNCH(KK)                                                                               \
+    do {                                                                                                \
+        if (sample && qin) query_pair_kernel<true, KK, true><<<grid, QTHREADS, 0, st>>>(q, qin, qout, tile);        \
+        else if (sample) query_pair_kernel<true, KK, false><<<grid, QTHREADS, 0, st>>>(q, nullptr, nullptr, tile);  \
+        else if (qin) query_pair_kernel<false, KK, true><<<grid, QTHREADS, 0, st>>>(q, qin, qout, tile);            \
+        else query_pair_kernel<false, KK, false><<<grid, QTHREADS, 0, st>>>(q, nullptr, nullptr, tile);             \
     } while (0)
     switch (q.K) {
         case 16: SDMMB_QLAUNCH(16); break;
@@ -488,6 +558,11 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
         default: return cudaErrorInvalidValue;
     }
 #undef SDMMB_QLAUNCH
+    if (qin) {
+        const unsigned ug = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
+        if (sample) query_unpermute_kernel<true><<<ug, 256, 0, st>>>(q, invperm, qout);
+        else query_unpermute_kernel<false><<<ug, 256, 0, st>>>(q, invperm, qout);
+    }
     return cudaGetLastError();
 }
 
