@@ -100,9 +100,17 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     hbm_src = "MEASURED_PEAKS.json" if hbm_peak else "fallback (B200_PROFILING.md)"
     hbm_peak = hbm_peak or 6650.0
     hbm_gbs = 32.0 * C_local * N / (est_ms * 1e-3) / 1e9
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_estep_traffic.json")) as f:
+            tj = json.load(f)
+        traffic = tj["dram_bytes_per_sample"] * C_local * N
+        traffic_src = tj["source"]
+    except Exception:
+        pass
     roofline = dict(
         bound="fp32", kernel="em_estep_kernel", achieved=achieved_tf, peak=peak_tf, unit="TFLOP/s",
-        frac=achieved_tf / peak_tf, traffic=None,
+        frac=achieved_tf / peak_tf, traffic=traffic, traffic_source=traffic_src,
         peak_source="FFMA2 micro-benchmark run by this process on this GPU (sdmmb_measure_peaks); "
                     "MEASURED_PEAKS.json carries no FP32 figure",
         flop_per_update=FLOP_PER_UPDATE, updates_per_launch=upd_per_launch, ms_per_launch=est_ms,
@@ -146,7 +154,29 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                                      peak=peaks["fp32_ffma_tflops"], unit="TFLOP/s",
                                      frac=flop_q * res["binned"]["value"] / world / 1e12 / peaks["fp32_ffma_tflops"],
                                      flop_per_query=flop_q))
-        del d_cell, d_pos, d_u, r_cell, r_pos, r_u, out
+        # end to end through the host-buffer API (pinned inputs and outputs, copies inside the call)
+        hq = dict(cell=torch.from_numpy(cell_q.view(np.int32)).pin_memory(), pos=torch.from_numpy(pos_q).pin_memory(),
+                  u=torch.from_numpy(u_q).pin_memory())
+        perm_h = perm.cpu()
+        hr = dict(cell=hq["cell"][perm_h].contiguous().pin_memory(), pos=hq["pos"][:, perm_h].contiguous().pin_memory(),
+                  u=hq["u"][:, perm_h].contiguous().pin_memory())
+        ho = dict(dir=torch.empty((3, nq), dtype=torch.float32).pin_memory().numpy(),
+                  pdf=torch.empty(nq, dtype=torch.float32).pin_memory().numpy(),
+                  inv_jac=torch.empty(nq, dtype=torch.float32).pin_memory().numpy(),
+                  comp=torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32),
+                  valid=torch.empty(nq, dtype=torch.uint8).pin_memory().numpy())
+        e2e_q = {}
+        for name, (hh, binned) in dict(binned=(hq, True), random=(hr, False)).items():
+            a_cell, a_pos, a_u = hh["cell"].numpy().view(np.uint32), hh["pos"].numpy(), hh["u"].numpy()
+            cells.sample_pdf(a_cell, a_pos, a_u, binned=binned, out=ho)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                cells.sample_pdf(a_cell, a_pos, a_u, binned=binned, out=ho)
+            qms = _maxreduce(torch, dist, world, (time.perf_counter() - t0) * 1e3 / 3, device)
+            e2e_q[name] = dict(value=world * nq / (qms * 1e-3), unit="queries/s", ms=qms)
+        queries["e2e"] = dict(binned=e2e_q["binned"], random_order=e2e_q["random"], h2d_bytes_per_query=28,
+                              d2h_bytes_per_query=25, api="SDMMCells.sample_pdf(host arrays) = sdmmb_sample_pdf_host")
+        del d_cell, d_pos, d_u, r_cell, r_pos, r_u, out, hq, hr
 
     # ---- end to end through the host-buffer API --------------------------------------------------
     e2e = None

@@ -54,8 +54,9 @@ struct sdmmb_ctx {
     // sdmmb_optimize_host pipeline: H2D copy stream, D2H stream, events
     // [0,1] chunk copied, [2,3] chunk packed (staging buffer reusable), [4] entry fence, [5] chunk fitted
     cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
-    cudaEvent_t pipe_ev[6] = {};
+    cudaEvent_t pipe_ev[8] = {};  // [6,7] query_host: chunk's results copied out (staging reusable)
     size_t pipe_chunk_samples = 2u << 20;
+    size_t query_chunk = 2u << 20;  // vertices per chunk of the host-buffer query pipeline
     // nccl (resolved lazily)
     void* nccl_handle = nullptr;
     int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
@@ -178,6 +179,10 @@ int sdmmb_create(sdmmb_ctx** out, int device, int max_cells, int K) {
     if (const char* s = std::getenv("SDMMB_ITEM_SAMPLES")) {
         long v = std::atol(s);
         if (v >= 32) ctx->item_samples = (uint32_t)v;
+    }
+    if (const char* s = std::getenv("SDMMB_QUERY_CHUNK")) {
+        long v = std::atol(s);
+        if (v >= 256) ctx->query_chunk = (size_t)v;
     }
     if (const char* s = std::getenv("SDMMB_PIPE_CHUNK_SAMPLES")) {
         long v = std::atol(s);

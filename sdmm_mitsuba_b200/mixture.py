@@ -178,7 +178,7 @@ class SDMMCells:
         check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, None), "sdmmb_prepare_conditioner", self._h)
 
     # ---- queries ------------------------------------------------------------------------------
-    def sample_pdf(self, cell_idx, pos3, u3, binned=False):
+    def sample_pdf(self, cell_idx, pos3, u3, binned=False, out=None):
         """Per vertex: create_conditional(x) -> sample(u) -> posterior(omega) summed.
         u3 planes by role: select, Box-Muller radius, Box-Muller angle."""
         if _is_torch(pos3):
@@ -200,8 +200,9 @@ class SDMMCells:
         pos3 = _np(pos3, np.float32)
         u3 = _np(u3, np.float32)
         n = pos3.shape[1]
-        out = dict(dir=np.zeros((3, n), np.float32), pdf=np.zeros(n, np.float32), inv_jac=np.zeros(n, np.float32),
-                   comp=np.zeros(n, np.uint32), valid=np.zeros(n, np.uint8))
+        if out is None:   # `out`: caller-provided (e.g. pinned) host arrays of the same shapes
+            out = dict(dir=np.zeros((3, n), np.float32), pdf=np.zeros(n, np.float32), inv_jac=np.zeros(n, np.float32),
+                       comp=np.zeros(n, np.uint32), valid=np.zeros(n, np.uint8))
         check(self._L.sdmmb_sample_pdf_host(self._h, n, _hp(cell_idx), _hp(pos3), _hp(u3), _hp(out["dir"]),
                                             _hp(out["pdf"]), _hp(out["inv_jac"]), _hp(out["comp"]),
                                             _hp(out["valid"]), 1 if binned else 0, None),
