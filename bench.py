@@ -170,6 +170,33 @@ def cpu_baseline(K, N, iters, seconds_target=12.0, n_threads=0):
                        "OpenMP over cells" % (C, K, N, iters, secs)), secs
 
 
+def cpu_query_baseline(K, n_queries=1 << 20, n_cells=64, n_threads=0):
+    """The reference's per-vertex create_conditional + SDMM::sample + posterior (sdmm_proc.cpp:361-372,
+    419-421, 539-545) with OpenMP over vertices and per-thread scratch, on mixtures fitted by the same
+    CPU code; a bounded sample (n_queries over n_cells cells) of cfg3."""
+    from oracle import portbind, refbind
+    from sdmm_mitsuba_b200 import synth
+    if refbind.available():
+        mod, cls, kind = refbind, refbind.RefCells, "reference"
+        cores = mod.lib().sdmm_ref_max_threads()
+    else:
+        mod, cls, kind = portbind, portbind.PortCells, "port"
+        cores = mod.lib().oracle_max_threads()
+    if n_threads:
+        cores = n_threads
+    point6, weight, off = synth.make_samples(n_cells, 1024, seed=321)
+    joint, em, scal = synth.make_initial_model(n_cells, K, seed=322)
+    o = cls(n_cells, K)
+    o.set(joint, em, scal)
+    o.em_batch(off, point6, weight, 2, with_prepare=True, n_threads=n_threads)
+    o.prepare_conditioner()
+    cell, pos3, u3 = synth.make_queries(n_queries, n_cells, seed=323, binned=False)
+    o.sample_pdf(cell[:4096].copy(), np.ascontiguousarray(pos3[:, :4096]), np.ascontiguousarray(u3[:, :4096]), n_threads=n_threads)
+    _, secs = o.sample_pdf(cell, pos3, u3, n_threads=n_threads)
+    return dict(value=n_queries / secs, unit="queries/s", cores=int(cores), kind=kind,
+                sample="%d vertices over %d fitted cells (K=%d), %.1f s, OpenMP over vertices" % (n_queries, n_cells, K, secs))
+
+
 def run_reference(args, cfg, rank, world):
     if rank != 0:
         return

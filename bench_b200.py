@@ -220,6 +220,11 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cb, _ = cpu_baseline(K, N, iters)
+        one, _ = cpu_baseline(K, N, iters, seconds_target=4.0, n_threads=1)
+        cb["single_core"] = dict(value=one["value"], unit=one["unit"], sample=one["sample"])
+        if queries is not None:
+            from bench import cpu_query_baseline
+            queries["cpu_baseline"] = cpu_query_baseline(K, n_threads=cb["cores"])   # all host threads again
 
     if rank == 0:
         line = dict(

@@ -153,6 +153,15 @@ int sdmmb_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const f
                    const float* h_dir3, float* h_out_pdf, uint8_t* h_out_valid, int binned,
                    void* stream);
 
+/* optimizeAsync (the plugin's default, volpath_sdmm.cpp:180-242, 446-448): the fit of iteration i runs
+ * while iteration i+1 is rendered with the PREVIOUS conditioners, which are swapped in by
+ * optimize_async_wait_and_update (:227-242).  With async records enabled the fit (sdmmb_em_step /
+ * sdmmb_optimize_host / sdmmb_prepare_conditioner) writes a back copy of the query records and queries
+ * keep reading the published ones until sdmmb_publish_records copies a cell range over (stream-ordered).
+ * Run the fit and the queries on different streams to overlap them. */
+int sdmmb_set_async_records(sdmmb_ctx* ctx, int enabled);
+int sdmmb_publish_records(sdmmb_ctx* ctx, int first_cell, int n_cells, void* stream);
+
 /* Multi-GPU: cells are partitioned across ranks; after a training iteration every rank needs every
  * cell's query records.  The context can hold records for a GLOBAL cell range while fitting only
  * its own slice: records live in one device array of max_cells * K * 32 floats. */

@@ -26,7 +26,8 @@ struct sdmmb_ctx {
     uint32_t* d_scal = nullptr;  // [max_cells][8]
     float* d_cdf = nullptr;      // [max_cells][K]
     float* d_erec = nullptr;     // [max_cells][28][K]
-    float* d_qrec = nullptr;     // [max_cells][K][32]
+    float* d_qrec = nullptr;     // [max_cells][K][32]  records the queries (and the all-gather) read
+    float* d_qrec_back = nullptr;  // async mode: records the fit writes, published by sdmmb_publish_records
     // bound samples
     float4* d_samples = nullptr;
     size_t samples_cap = 0, n_samples = 0;
@@ -121,7 +122,7 @@ MStepArgs base_mstep_args(sdmmb_ctx* ctx, int first_cell, int n_cells, int mode)
     a.scal = ctx->d_scal;
     a.cdf = ctx->d_cdf;
     a.erec = ctx->d_erec;
-    a.qrec = ctx->d_qrec;
+    a.qrec = ctx->d_qrec_back ? ctx->d_qrec_back : ctx->d_qrec;
     return a;
 }
 
@@ -215,7 +216,7 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     if (!ctx) return SDMMB_OK;
     DeviceGuard g(ctx->device);
     cudaFree(ctx->d_joint); cudaFree(ctx->d_em); cudaFree(ctx->d_scal); cudaFree(ctx->d_cdf);
-    cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
+    cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_qrec_back); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch);
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);

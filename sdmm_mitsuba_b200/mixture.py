@@ -177,6 +177,15 @@ class SDMMCells:
         n = self.max_cells - first_cell if n_cells is None else n_cells
         check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, None), "sdmmb_prepare_conditioner", self._h)
 
+    def set_async_records(self, enabled=True):
+        """optimizeAsync: fits write a back copy of the query records until publish_records()."""
+        check(self._L.sdmmb_set_async_records(self._h, 1 if enabled else 0), "sdmmb_set_async_records", self._h)
+
+    def publish_records(self, first_cell=0, n_cells=None):
+        """optimize_async_wait_and_update (volpath_sdmm.cpp:227-242) for a cell range."""
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        check(self._L.sdmmb_publish_records(self._h, first_cell, n, None), "sdmmb_publish_records", self._h)
+
     # ---- queries ------------------------------------------------------------------------------
     def sample_pdf(self, cell_idx, pos3, u3, binned=False, out=None):
         """Per vertex: create_conditional(x) -> sample(u) -> posterior(omega) summed.

@@ -225,3 +225,43 @@ def test_host_query_pipeline_chunking_is_invisible(monkeypatch):
         # pdfSurface at the sampled direction reproduces the pdf the sampler reported
         ok = a[0]["valid"].astype(bool) & (a[0]["inv_jac"] > 0)
         np.testing.assert_allclose(a[1][ok], a[0]["pdf"][ok], rtol=1e-5, atol=1e-12)
+
+
+def test_async_records_visible_only_after_publish():
+    """optimizeAsync semantics: with async records a refit does not change what queries see until
+    publish_records (optimize_async_wait_and_update, volpath_sdmm.cpp:227-242)."""
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, K, N, n = 4, 32, 600, 4000
+    point6, weight, off = synth.make_samples(C, N, seed=61)
+    joint, em, scal = synth.make_initial_model(C, K, seed=62)
+    cell, pos3, u3 = synth.make_queries(n, C, seed=63, binned=True)
+    sync = SDMMCells(C, K)
+    sync.upload(joint, em, scal)
+    sync.prepare()
+    before = sync.sample_pdf(cell, pos3, u3, binned=True)
+    sync.set_samples(point6, weight, off)
+    sync.em_step(2, with_conditioner=True)
+    after = sync.sample_pdf(cell, pos3, u3, binned=True)
+    assert (before["pdf"] != after["pdf"]).mean() > 0.9
+
+    a = SDMMCells(C, K)
+    a.upload(joint, em, scal)
+    a.prepare()
+    a.set_async_records(True)
+    a.set_samples(point6, weight, off)
+    a.em_step(2, with_conditioner=True)
+    held = a.sample_pdf(cell, pos3, u3, binned=True)
+    for key in ("dir", "pdf", "comp", "valid"):
+        np.testing.assert_array_equal(held[key], before[key], err_msg="refit leaked into queries before publish")
+    a.publish_records(0, 2)            # only cells 0 and 1
+    part = a.sample_pdf(cell, pos3, u3, binned=True)
+    lo = cell < 2
+    np.testing.assert_array_equal(part["pdf"][lo], after["pdf"][lo])
+    np.testing.assert_array_equal(part["pdf"][~lo], before["pdf"][~lo])
+    a.publish_records()
+    full = a.sample_pdf(cell, pos3, u3, binned=True)
+    for key in ("dir", "pdf", "comp", "valid"):
+        np.testing.assert_array_equal(full[key], after[key])
+    a.set_async_records(False)
+    np.testing.assert_array_equal(a.sample_pdf(cell, pos3, u3, binned=True)["pdf"], after["pdf"])
