@@ -29,6 +29,8 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line (no "NCCL version" banner)
         dist.init_process_group("nccl", device_id=device)
 
     K, N, iters = cfg["K"], cfg["N"], cfg["iters"]
