@@ -153,6 +153,36 @@ int sdmmb_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const f
                    const float* h_dir3, float* h_out_pdf, uint8_t* h_out_valid, int binned,
                    void* stream);
 
+/* ---- spatial cell structure on the device ------------------------------------
+ * The STree (sdmm/accelerators/spatial_tree.h:83-349) is built and split on the host by the reference's
+ * own code; the host flattens it into this node table (host_shim.hpp: flatten_tree).  Inner node: axis in
+ * {0,1,2}, split = aabb.min[axis] of children[0], child0/child1 = node indices.  Leaf: axis = -1,
+ * child0 = the cell's device slot. */
+typedef struct sdmmb_tree_node {
+    int32_t axis;
+    float split;
+    uint32_t child0;
+    uint32_t child1;
+} sdmmb_tree_node;
+int sdmmb_set_tree(sdmmb_ctx* ctx, int n_nodes, const sdmmb_tree_node* h_nodes);
+/* STree::find (spatial_tree.h:19-51, called from sdmm_proc.cpp:311-315, 917-920) for a batch of points:
+ * pos3 = 3 planes of n; out = the leaf's cell slot (0xffffffff if the walk fails). */
+int sdmmb_find_cells(sdmmb_ctx* ctx, size_t n, const float* d_pos3, uint32_t* d_out_cell, void* stream);
+int sdmmb_find_cells_host(sdmmb_ctx* ctx, size_t n, const float* h_pos3, uint32_t* h_out_cell, void* stream);
+/* The renderer's sample collection (sdmm_proc.cpp:880-928: find the vertex's cell, Data::push_back under
+ * the cell's mutex) for a whole batch of UNSORTED samples: find + counting sort by cell straight into the
+ * E-step's packed records.  Binds the result as the training samples of ALL cells [0, max_cells), i.e. it
+ * replaces sdmmb_set_samples.  Samples Data::push_back rejects (weight < 1e-8 or non-finite,
+ * opt/data.h:20-23) and samples without a cell are dropped and counted.  d_key3 (nullable) = the
+ * positions used for the cell lookup when they differ from the sample's own position planes.
+ * h_out_counts (nullable): [max_cells] samples per cell.  Synchronises the stream once (counts). */
+int sdmmb_collect_samples(sdmmb_ctx* ctx, size_t n, const float* d_point6, size_t plane_stride,
+                          const float* d_weight, const float* d_key3, size_t key_stride,
+                          uint32_t* h_out_counts, uint64_t* h_out_dropped, void* stream);
+/* canBeOptimized (volpath_sdmm.cpp:140-149): cells with fewer bound samples than this are left untouched
+ * by sdmmb_em_step (default 0 = train every cell of the range). */
+int sdmmb_set_min_samples(sdmmb_ctx* ctx, uint32_t min_samples);
+
 /* optimizeAsync (the plugin's default, volpath_sdmm.cpp:180-242, 446-448): the fit of iteration i runs
  * while iteration i+1 is rendered with the PREVIOUS conditioners, which are swapped in by
  * optimize_async_wait_and_update (:227-242).  With async records enabled the fit (sdmmb_em_step /

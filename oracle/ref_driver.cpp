@@ -32,6 +32,12 @@
 #include "sdmm/core/utils.h"
 #include "sdmm/distributions/sdmm.h"
 #include "sdmm/distributions/sdmm_conditioner.h"
+// the json.hpp vendored with the reference (ext/jmm) predates this macro; serialisation is not on the path
+#ifndef NLOHMANN_DEFINE_TYPE_INTRUSIVE
+#define NLOHMANN_DEFINE_TYPE_INTRUSIVE(...)
+#endif
+#include "sdmm/accelerators/spatial_tree.h"
+#include "sdmm/distributions/sdmm_context.h"
 #include "sdmm/linalg/cholesky.h"
 #include "sdmm/linalg/coordinate_system.h"
 #include "sdmm/opt/data.h"
@@ -612,6 +618,86 @@ void sdmm_ref_joint_to(const float* mean6, const float* point6, float* tangent5,
     auto t = ts.to(sdmm::Vector<float, 6>(point6[0], point6[1], point6[2], point6[3], point6[4], point6[5]), ij);
     for (int i = 0; i < 5; ++i) tangent5[i] = t.coeff(i);
     *inv_jac = ij;
+}
+
+}  // extern "C"
+
+// ---- spatial cell structure: the reference's own STree (accelerators/spatial_tree.h) ---------------
+// create -> push points (find leaf; stats + data like push_back_data, sdmm_proc.cpp:880-910) ->
+// split_to_depth / split_leaf_recurse -> export the node table -> find.
+namespace {
+using TreeRNG = enoki::PCG32<float, 1>;
+using TreeContext = sdmm::SDMMContext<JointSDMM, Conditioner, TreeRNG>;
+using Tree = sdmm::accelerators::STree<float, 3, TreeContext>;
+struct RefTree {
+    std::unique_ptr<Tree> tree;
+    size_t capacity;
+};
+}  // namespace
+
+extern "C" {
+
+void* sdmm_ref_tree_create(const float* aabb_min, const float* aabb_max, long capacity) {
+    auto* t = new RefTree();
+    t->capacity = (size_t)capacity;
+    Tree::AABB aabb(Tree::Point(aabb_min[0], aabb_min[1], aabb_min[2]), Tree::Point(aabb_max[0], aabb_max[1], aabb_max[2]));
+    t->tree = std::make_unique<Tree>(aabb, std::make_unique<TreeContext>((size_t)capacity));
+    return t;
+}
+void sdmm_ref_tree_destroy(void* h) { delete static_cast<RefTree*>(h); }
+void sdmm_ref_tree_split_to_depth(void* h, int depth) { static_cast<RefTree*>(h)->tree->split_to_depth(depth); }
+
+// returns the number of points for which no leaf was found (the renderer throws there)
+long sdmm_ref_tree_push(void* h, long n, const float* pos3) {
+    auto& tree = *static_cast<RefTree*>(h)->tree;
+    long missing = 0;
+    for (long i = 0; i < n; ++i) {
+        Tree::Point key(pos3[i], pos3[n + i], pos3[2 * n + i]);
+        auto* ctx = tree.find(key);
+        if (!ctx) { ++missing; continue; }
+        sdmm::embedded_s_t<JointSDMM> point(pos3[i], pos3[n + i], pos3[2 * n + i], 0.f, 0.f, 1.f);
+        ctx->data.push_back(point, sdmm::Vector<float, 3>(0.f, 0.f, 1.f), 1.f);
+        ctx->stats.push_back(sdmm::SpatialStats::Point((double)pos3[i], (double)pos3[n + i], (double)pos3[2 * n + i]));
+    }
+    return missing;
+}
+
+void sdmm_ref_tree_split_leaves(void* h, long threshold) {
+    auto& tree = *static_cast<RefTree*>(h)->tree;
+    const int size = (int)tree.size();
+    for (int node_i = 0; node_i < size; ++node_i) tree.split_leaf_recurse((uint32_t)node_i, (size_t)threshold);
+}
+
+int sdmm_ref_tree_size(void* h) { return (int)static_cast<RefTree*>(h)->tree->size(); }
+
+// per node 11 values: is_leaf, axis, child0, child1, stats.size (leaf) , aabb.min[3], aabb.max[3]
+void sdmm_ref_tree_export(void* h, float* out) {
+    auto& tree = *static_cast<RefTree*>(h)->tree;
+    const auto& nodes = tree.data();
+    for (int i = 0; i < (int)tree.size(); ++i) {
+        float* o = out + 11 * (size_t)i;
+        o[0] = nodes[i].is_leaf ? 1.f : 0.f;
+        o[1] = (float)nodes[i].axis;
+        o[2] = (float)nodes[i].children[0];
+        o[3] = (float)nodes[i].children[1];
+        o[4] = (nodes[i].is_leaf && nodes[i].value) ? (float)nodes[i].value->stats.size : 0.f;
+        for (int d = 0; d < 3; ++d) { o[5 + d] = nodes[i].aabb.min.coeff(d); o[8 + d] = nodes[i].aabb.max.coeff(d); }
+    }
+}
+
+// node index of the leaf STree::find returns (-1 if none)
+void sdmm_ref_tree_find(void* h, long n, const float* pos3, int32_t* out_node) {
+    auto& tree = *static_cast<RefTree*>(h)->tree;
+    const auto& nodes = tree.data();
+    for (long i = 0; i < n; ++i) {
+        Tree::Point key(pos3[i], pos3[n + i], pos3[2 * n + i]);
+        auto* ctx = tree.find(key);
+        int found = -1;
+        if (ctx)
+            for (int j = 0; j < (int)tree.size(); ++j)
+                if (nodes[j].is_leaf && nodes[j].value.get() == ctx) { found = j; break; }
+        out_node[i] = found;
+    }
 }
 
 }  // extern "C"

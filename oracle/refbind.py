@@ -56,6 +56,16 @@ def lib():
         L.sdmm_ref_kat_categorical.argtypes = [C.c_int, fp, fp, fp]
         L.sdmm_ref_kat_frame.argtypes = [fp, fp]
         L.sdmm_ref_joint_to.argtypes = [fp, fp, fp, fp]
+        L.sdmm_ref_tree_create.restype = C.c_void_p
+        L.sdmm_ref_tree_create.argtypes = [fp, fp, C.c_long]
+        L.sdmm_ref_tree_destroy.argtypes = [C.c_void_p]
+        L.sdmm_ref_tree_split_to_depth.argtypes = [C.c_void_p, C.c_int]
+        L.sdmm_ref_tree_push.restype = C.c_long
+        L.sdmm_ref_tree_push.argtypes = [C.c_void_p, C.c_long, fp]
+        L.sdmm_ref_tree_split_leaves.argtypes = [C.c_void_p, C.c_long]
+        L.sdmm_ref_tree_size.argtypes = [C.c_void_p]
+        L.sdmm_ref_tree_export.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_tree_find.argtypes = [C.c_void_p, C.c_long, fp, C.POINTER(C.c_int32)]
         _lib = L
     return _lib
 
@@ -242,3 +252,42 @@ def joint_to(mean6, point6):
     ij = np.zeros(1, np.float32)
     lib().sdmm_ref_joint_to(_f(mean6), _f(point6), _f(t), _f(ij))
     return t, float(ij[0])
+
+
+class RefTree:
+    """The reference's STree (sdmm/accelerators/spatial_tree.h) over SDMMContext cells."""
+
+    def __init__(self, aabb_min=(0, 0, 0), aabb_max=(1, 1, 1), capacity=100000):
+        lo = np.asarray(aabb_min, np.float32)
+        hi = np.asarray(aabb_max, np.float32)
+        self.h = lib().sdmm_ref_tree_create(_f(lo), _f(hi), capacity)
+
+    def __del__(self):
+        try:
+            lib().sdmm_ref_tree_destroy(self.h)
+        except Exception:
+            pass
+
+    def split_to_depth(self, depth):
+        lib().sdmm_ref_tree_split_to_depth(self.h, depth)
+
+    def push(self, pos3):
+        """pos3 [3,n]: find the leaf of every point, push it into the leaf's data + stats."""
+        pos3 = np.ascontiguousarray(pos3, np.float32)
+        return int(lib().sdmm_ref_tree_push(self.h, pos3.shape[1], _f(pos3)))
+
+    def split_leaves(self, threshold):
+        lib().sdmm_ref_tree_split_leaves(self.h, threshold)
+
+    def nodes(self):
+        """[n_nodes, 11]: is_leaf, axis, child0, child1, stats.size, aabb.min[3], aabb.max[3]."""
+        n = lib().sdmm_ref_tree_size(self.h)
+        out = np.zeros((n, 11), np.float32)
+        lib().sdmm_ref_tree_export(self.h, _f(out))
+        return out
+
+    def find(self, pos3):
+        pos3 = np.ascontiguousarray(pos3, np.float32)
+        out = np.zeros(pos3.shape[1], np.int32)
+        lib().sdmm_ref_tree_find(self.h, pos3.shape[1], _f(pos3), out.ctypes.data_as(C.POINTER(C.c_int32)))
+        return out

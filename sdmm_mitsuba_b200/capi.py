@@ -24,7 +24,8 @@ SYMBOLS = [
     "sdmmb_num_components", "sdmmb_max_cells", "sdmmb_upload_cells", "sdmmb_download_cells",
     "sdmmb_download_derived", "sdmmb_set_samples", "sdmmb_set_samples_host", "sdmmb_em_step",
     "sdmmb_optimize_host", "sdmmb_prepare_conditioner", "sdmmb_download_conditioner", "sdmmb_sample_pdf", "sdmmb_pdf",
-    "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
+    "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_set_tree", "sdmmb_find_cells", "sdmmb_find_cells_host", "sdmmb_collect_samples",
+    "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks",
 ]
 
@@ -77,6 +78,11 @@ def lib():
     L.sdmmb_pdf.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
     L.sdmmb_sample_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]
     L.sdmmb_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
+    L.sdmmb_set_tree.argtypes = [vp, i, vp]
+    L.sdmmb_find_cells.argtypes = [vp, sz, fp, up, vp]
+    L.sdmmb_find_cells_host.argtypes = [vp, sz, fp, up, vp]
+    L.sdmmb_collect_samples.argtypes = [vp, sz, fp, sz, fp, fp, sz, up, C.POINTER(C.c_uint64), vp]
+    L.sdmmb_set_min_samples.argtypes = [vp, C.c_uint32]
     L.sdmmb_set_async_records.argtypes = [vp, i]
     L.sdmmb_publish_records.argtypes = [vp, i, i, vp]
     L.sdmmb_query_records.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]

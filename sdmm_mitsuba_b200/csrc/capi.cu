@@ -44,6 +44,9 @@ struct sdmmb_ctx {
     size_t stage_cap = 0;
     void* d_stage2 = nullptr;
     size_t stage2_cap = 0;
+    TreeNode* d_tree = nullptr;  // flattened STree
+    int n_tree_nodes = 0;
+    uint32_t min_samples = 0;    // canBeOptimized threshold applied by the M-step
     void* d_qscratch = nullptr;  // query binning scratch
     size_t qscratch_cap = 0;
     // bookkeeping
@@ -123,6 +126,7 @@ MStepArgs base_mstep_args(sdmmb_ctx* ctx, int first_cell, int n_cells, int mode)
     a.cdf = ctx->d_cdf;
     a.erec = ctx->d_erec;
     a.qrec = ctx->d_qrec_back ? ctx->d_qrec_back : ctx->d_qrec;
+    a.min_samples = ctx->min_samples;
     return a;
 }
 
@@ -218,7 +222,7 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_joint); cudaFree(ctx->d_em); cudaFree(ctx->d_scal); cudaFree(ctx->d_cdf);
     cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_qrec_back); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
-    cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch);
+    cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch); cudaFree(ctx->d_tree);
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     if (ctx->copy_stream) {
         cudaStreamDestroy(ctx->copy_stream);

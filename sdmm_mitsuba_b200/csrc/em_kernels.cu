@@ -698,7 +698,9 @@ em_mstep_kernel(MStepArgs a) {
         for (int i = 0; i < 25; ++i) cov[i] = joint[(7 + i) * K + k];
     }
 
-    if (active && (a.mode & 1)) {
+    // canBeOptimized (volpath_sdmm.cpp:140-149): cells that hold too few samples are not trained
+    const bool trainable = active && (a.mode & 1) && a.cell_sample_count[ci] >= a.min_samples;
+    if (trainable) {
         // ---- reduce the E-step partials of this cell's items (fixed order) ---------------------
         const uint32_t ib = a.cell_item_begin[ci] - a.item_base, ie = a.cell_item_begin[ci + 1] - a.item_base;
         float bt[ESTAT_PLANES];

@@ -228,3 +228,40 @@ void optimize(Device& dev, int first_slot, const std::vector<ContextPtr>& contex
 }
 
 }  // namespace sdmm_b200
+
+// ---- spatial cell structure -------------------------------------------------------
+// Flattens the reference's STree (accelerators/spatial_tree.h) into the device node table and assigns
+// device slots to the leaves (in node order).  `slot_of_node[i]` = slot of leaf node i, -1 for inner
+// nodes; `contexts[slot]` = the leaf's SDMMContext*, ready for sdmm_b200::optimize.
+namespace sdmm_b200 {
+
+template <typename Tree, typename ContextPtr>
+void flatten_tree(Tree& tree, std::vector<sdmmb_tree_node>& nodes, std::vector<int>& slot_of_node,
+                  std::vector<ContextPtr>& contexts) {
+    const auto& src = tree.data();
+    const int n = (int)tree.size();
+    nodes.assign(n, sdmmb_tree_node{});
+    slot_of_node.assign(n, -1);
+    contexts.clear();
+    for (int i = 0; i < n; ++i) {
+        if (src[i].is_leaf) {
+            slot_of_node[i] = (int)contexts.size();
+            contexts.push_back(src[i].value.get());
+            nodes[i] = sdmmb_tree_node{-1, 0.f, (uint32_t)slot_of_node[i], 0u};
+        } else {
+            const int axis = src[i].axis;
+            const uint32_t c0 = src[i].children[0], c1 = src[i].children[1];
+            // find() descends into children[0] iff nodes[children[0]].aabb.min[axis] < p[axis]  (:36-45)
+            nodes[i] = sdmmb_tree_node{axis, (float)src[c0].aabb.min.coeff(axis), c0, c1};
+        }
+    }
+}
+
+template <typename Tree, typename ContextPtr>
+void upload_tree(Device& dev, Tree& tree, std::vector<int>& slot_of_node, std::vector<ContextPtr>& contexts) {
+    std::vector<sdmmb_tree_node> nodes;
+    flatten_tree(tree, nodes, slot_of_node, contexts);
+    check(sdmmb_set_tree(dev.ctx(), (int)nodes.size(), nodes.data()), "sdmmb_set_tree", dev.ctx());
+}
+
+}  // namespace sdmm_b200

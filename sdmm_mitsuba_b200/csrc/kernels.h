@@ -73,6 +73,7 @@ struct MStepArgs {
     const uint32_t* cell_item_begin;    // [n_cells+1] absolute item indices, entry 0 = this launch's first cell
     uint32_t item_base;                 // item index that `partials` / `item_scal` start at
     const uint32_t* cell_sample_count;  // [n_cells]
+    uint32_t min_samples;               // cells with fewer bound samples are left untouched by the EM update
 };
 
 struct QueryLaunch {
@@ -93,6 +94,22 @@ struct QueryLaunch {
     uint32_t* scratch;  // unbinned only: 2 * (max_cells + 1) + 17 * n + 4 words (see launch_query)
 };
 
+// flattened STree node (tree_kernels.cu): inner node: axis 0..2, split = aabb.min[axis] of child 0;
+// leaf: axis = -1, child0 = cell slot
+struct TreeNode {
+    int32_t axis;
+    float split;
+    uint32_t child0;
+    uint32_t child1;
+};
+
+cudaError_t launch_find_cells(const TreeNode* nodes, int n_nodes, const float* pos3, size_t stride, size_t n,
+                              uint32_t* out, uint32_t miss, cudaStream_t st);
+cudaError_t launch_collect_count(const TreeNode* nodes, int n_nodes, const float* key3, size_t key_stride,
+                                 const float* weight, size_t n, uint32_t n_buckets, uint32_t* cell, uint32_t* count,
+                                 uint32_t* cursor, cudaStream_t st);
+cudaError_t launch_collect_scatter(const uint32_t* cell, const float* point6, size_t stride, const float* weight,
+                                   size_t n, uint32_t dropped, uint32_t* cursor, float4* rec, cudaStream_t st);
 cudaError_t launch_pack(const float* point6, size_t stride, const float* weight, float4* rec, size_t n,
                         cudaStream_t st);
 cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st);

@@ -177,6 +177,50 @@ class SDMMCells:
         n = self.max_cells - first_cell if n_cells is None else n_cells
         check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, None), "sdmmb_prepare_conditioner", self._h)
 
+    # ---- spatial cell structure ---------------------------------------------------------------
+    def set_tree(self, nodes):
+        """nodes: structured array of tree.TREE_NODE_DTYPE (see tree.flatten)."""
+        from .tree import TREE_NODE_DTYPE
+        nodes = np.ascontiguousarray(nodes, dtype=TREE_NODE_DTYPE)
+        check(self._L.sdmmb_set_tree(self._h, nodes.shape[0], C.c_void_p(nodes.ctypes.data)), "sdmmb_set_tree", self._h)
+
+    def find_cells(self, pos3):
+        """STree::find for a batch of points: pos3 [3,n] -> cell slot per point (0xffffffff = none)."""
+        if _is_torch(pos3):
+            import torch
+            out = torch.empty(pos3.shape[1], dtype=torch.int32, device=pos3.device)
+            check(self._L.sdmmb_find_cells(self._h, pos3.shape[1], C.c_void_p(pos3.data_ptr()),
+                                           C.c_void_p(out.data_ptr()), _stream(self.device)), "sdmmb_find_cells", self._h)
+            return out
+        pos3 = _np(pos3, np.float32)
+        out = np.zeros(pos3.shape[1], np.uint32)
+        check(self._L.sdmmb_find_cells_host(self._h, pos3.shape[1], _hp(pos3), _hp(out), None),
+              "sdmmb_find_cells_host", self._h)
+        return out
+
+    def collect_samples(self, point6, weight, key3=None):
+        """The renderer's sample collection for a batch of unsorted samples (torch CUDA tensors):
+        find each sample's cell and bin it; binds the result as the training samples of all cells.
+        Returns (counts [max_cells] u32, dropped)."""
+        assert _is_torch(point6) and point6.is_cuda and point6.is_contiguous() and point6.shape[0] == 6
+        n = point6.shape[1]
+        counts = np.zeros(self.max_cells, np.uint32)
+        dropped = C.c_uint64()
+        kp, ks = None, 0
+        if key3 is not None:
+            assert key3.is_cuda and key3.is_contiguous() and key3.shape == (3, n)
+            kp, ks = C.c_void_p(key3.data_ptr()), n
+        self._keep = (point6, weight, key3)
+        check(self._L.sdmmb_collect_samples(self._h, n, C.c_void_p(point6.data_ptr()), n, C.c_void_p(weight.data_ptr()),
+                                            kp, ks, _hp(counts), C.byref(dropped), _stream(self.device)),
+              "sdmmb_collect_samples", self._h)
+        self.n_samples = int(counts.sum())
+        self._bound = (0, self.max_cells)
+        return counts, int(dropped.value)
+
+    def set_min_samples(self, n):
+        check(self._L.sdmmb_set_min_samples(self._h, int(n)), "sdmmb_set_min_samples", self._h)
+
     def set_async_records(self, enabled=True):
         """optimizeAsync: fits write a back copy of the query records until publish_records()."""
         check(self._L.sdmmb_set_async_records(self._h, 1 if enabled else 0), "sdmmb_set_async_records", self._h)

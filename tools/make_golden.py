@@ -68,7 +68,33 @@ def make(name, C, K, N, iters, nq):
     print(path, "%.0f KB" % (os.path.getsize(path) / 1e3))
 
 
+def make_tree():
+    """The reference's STree: bootstrap split_to_depth(2) (volpath_sdmm.cpp:398), 30000 clustered points
+    pushed through find + stats, data-driven splits at threshold 400, then the node table and find()
+    results for fresh points (some exactly on split planes)."""
+    rng = np.random.default_rng(77)
+    n_points = 30000
+    t = refbind.RefTree(capacity=n_points + 16)
+    t.split_to_depth(2)
+    centres = rng.uniform(0.15, 0.85, (5, 3))
+    which = rng.integers(0, 5, n_points)
+    p = np.clip(centres[which] + rng.normal(0, 0.07, (n_points, 3)), 1e-4, 1 - 1e-4).astype(np.float32).T.copy()
+    assert t.push(p) == 0
+    t.split_leaves(400)
+    nodes = t.nodes()
+    q = rng.uniform(0, 1, (3, 20000)).astype(np.float32)
+    inner = np.nonzero(nodes[:, 0] == 0)[0]
+    for j, i in enumerate(inner[:300]):
+        ax = int(nodes[i, 1])
+        q[ax, j] = nodes[int(nodes[i, 2]), 5 + ax]
+    path = os.path.join(ROOT, "tests", "golden", "tree.npz")
+    np.savez_compressed(path, nodes=nodes, points=p[:, :4000], points_node=t.find(p[:, :4000]), queries=q,
+                        queries_node=t.find(q))
+    print(path, "%.0f KB" % (os.path.getsize(path) / 1e3), "nodes", nodes.shape[0], "leaves", int(nodes[:, 0].sum()))
+
+
 if __name__ == "__main__":
     assert refbind.available(), "build oracle/_ref first (make -C oracle ref)"
+    make_tree()
     for name, cfg in CASES.items():
         make(name, *cfg)
