@@ -102,6 +102,29 @@ int sdmmb_set_samples_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const fl
                            size_t plane_stride, const float* h_weight,
                            const uint32_t* h_cell_offsets, void* stream);
 
+/* sdmm::initialize (sdmm/include/sdmm/opt/init.h:17-193) for cells [first_cell, first_cell+n_cells), as
+ * initializeSDMMContext calls it for a cell that has no mixture yet (volpath_sdmm.cpp:132-137, 292-294):
+ * K/8 spatial seeds drawn farthest-point style from the cell's samples (sampling weight clamp(w, 1e-3, 3)
+ * x distance^5 in position + normal space), 2 x 4 directional lobes per seed, manifold covariance from the
+ * seed's normal, depth prior 1e-6 n n^T, priors weight 1/K, strength 5/K, cov diag(2e-3 x3, 2e-4 x2);
+ * EM state zeroed; then set_mean + prepare_vectorized.  K must be a multiple of 8.
+ * d_point6 / d_normal3: SoA planes `plane_stride` floats apart; h_cell_offsets: HOST, n_cells+1, relative
+ * to the first sample passed; h_spatial_distance: HOST, per cell (the integrator passes
+ * 3 * max AABB diagonal / (K/8)).  rng_state / rng_stream: the PCG32 seed of the context's generator,
+ * which the reference passes BY VALUE (every cell replays the same stream; the defaults are
+ * SDMMB_PCG32_DEFAULT_STATE / _STREAM).  h_out_seed_idx (nullable): HOST, [n_cells][K/8] sample index of
+ * every seed (relative to the cell's first sample).  Synchronous. */
+#define SDMMB_PCG32_DEFAULT_STATE 0x853c49e6748fea9bULL
+#define SDMMB_PCG32_DEFAULT_STREAM 0xda3e39cb94b95bdbULL
+int sdmmb_initialize(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d_point6,
+                     const float* d_normal3, size_t plane_stride, const float* d_weight,
+                     const uint32_t* h_cell_offsets, const float* h_spatial_distance,
+                     uint64_t rng_state, uint64_t rng_stream, int32_t* h_out_seed_idx, void* stream);
+int sdmmb_initialize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* h_point6,
+                          const float* h_normal3, size_t plane_stride, const float* h_weight,
+                          const uint32_t* h_cell_offsets, const float* h_spatial_distance,
+                          uint64_t rng_state, uint64_t rng_stream, int32_t* h_out_seed_idx, void* stream);
+
 /* n_iters x sdmm::em_step (sdmm/opt/em.h:218-253) on every bound cell of the range, i.e. the body
  * of the ThreadPool::parallelFor in SDMMVolumetricPathTracer::optimize (volpath_sdmm.cpp:287-311):
  * E-step + sufficient statistics (em.h:255-314), stepwise blend (:316-328), normalise (:330-351),

@@ -56,6 +56,9 @@ def lib():
         L.oracle_categorical_prepare.argtypes = [C.c_int, fp, fp]
         L.oracle_frame.argtypes = [fp, fp, fp]
         L.oracle_joint_to.argtypes = [fp, fp, fp, fp]
+        L.oracle_initialize.argtypes = [C.c_void_p, C.c_int, fp, fp, C.c_long, fp, C.c_int, C.c_float,
+                                        C.c_uint64, C.c_uint64, C.POINTER(C.c_int32)]
+        L.oracle_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int, fp]
         _lib = L
     return _lib
 
@@ -78,6 +81,9 @@ def _b(a):
 def _off(a, n):
     return C.cast(a.ctypes.data + 4 * n, C.POINTER(C.c_float))
 
+PCG32_DEFAULT_STATE = 0x853c49e6748fea9b
+PCG32_DEFAULT_STREAM = 0xda3e39cb94b95bdb
+
 
 class PortCells:
     def __init__(self, n_cells, K):
@@ -95,6 +101,20 @@ class PortCells:
 
     def _hp(self):
         return C.cast(self.handles, C.POINTER(C.c_void_p))
+
+    def initialize(self, offsets, point6, normal3, weight, spatial_distance,
+                   rng_state=PCG32_DEFAULT_STATE, rng_stream=PCG32_DEFAULT_STREAM):
+        """sdmm::initialize per cell with K/8 seeds; returns the seed sample indices [C, K/8]."""
+        L = lib()
+        stride = point6.shape[1]
+        seeds = np.zeros((self.C, self.K // 8), np.int32)
+        for c in range(self.C):
+            b, e = int(offsets[c]), int(offsets[c + 1])
+            k = L.oracle_initialize(self.handles[c], e - b, _off(point6, b), _off(normal3, b), stride,
+                                    _off(weight, b), self.K // 8, float(spatial_distance[c]), rng_state,
+                                    rng_stream, seeds[c].ctypes.data_as(C.POINTER(C.c_int32)))
+            assert k == self.K, (k, self.K)
+        return seeds
 
     def set(self, joint, em=None, scal=None):
         L = lib()
@@ -184,6 +204,12 @@ class PortCells:
         idx = np.array([cell], np.uint32)
         L.oracle_pdf(self._hp(), 1, _u(idx), _f(pos), _f(d), _f(pdf), _b(valid), _f(pmf), _f(cdf), 1)
         return pmf, cdf, bool(valid[0])
+
+
+def pcg32_floats(n, state=PCG32_DEFAULT_STATE, stream=PCG32_DEFAULT_STREAM):
+    out = np.zeros(n, np.float32)
+    lib().oracle_pcg32_floats(state, stream, n, _f(out))
+    return out
 
 
 def cholesky(m):

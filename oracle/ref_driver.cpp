@@ -42,6 +42,7 @@
 #include "sdmm/linalg/coordinate_system.h"
 #include "sdmm/opt/data.h"
 #include "sdmm/opt/em.h"
+#include "sdmm/opt/init.h"  // boost chi_squared comes from oracle/stubs (constant quantile)
 #include "sdmm/spaces/directional.h"
 #include "sdmm/spaces/euclidian.h"
 #include "sdmm/spaces/offset_directional.h"
@@ -280,6 +281,35 @@ int sdmm_ref_em_step(void* h, int N, const float* point6, long stride, const flo
     }
     c.conditioner_ready = false;
     return 0;
+}
+
+// sdmm::initialize (opt/init.h:17-193) on one cell, exactly as initializeSDMMContext calls it
+// (volpath_sdmm.cpp:132-137): the context's RNG is a default-seeded enoki::PCG32<float,1>
+// passed BY VALUE.  The handle must have been created with K = 8 * n_spatial.  normal3: 3 planes
+// with the same stride as point6.  Afterwards the cell holds the initial model + EM priors.
+int sdmm_ref_initialize(void* h, int N, const float* point6, const float* normal3, long stride,
+                        const float* weight, int n_spatial, float spatial_distance,
+                        uint64_t rng_state, uint64_t rng_stream) {
+    auto& c = *static_cast<RefCell*>(h);
+    Data data;
+    load_data(data, N, point6, (size_t)stride, weight);
+    for (int n = 0; n < N; ++n)
+        for (int d = 0; d < 3; ++d) data.normal.coeff(d).coeff(n) = normal3[d * stride + n];
+    enoki::PCG32<float, 1> rng(rng_state, rng_stream);
+    sdmm::initialize(c.sdmm, c.em, data, rng, (size_t)n_spatial, spatial_distance);
+    c.K = (int)enoki::slices(c.sdmm);
+    enoki::set_slices(c.conditioner, c.K);
+    enoki::set_slices(c.conditional, c.K);
+    enoki::set_slices(c.posterior, c.K);
+    c.conditioner_ready = false;
+    return c.K;
+}
+
+// enoki::PCG32<float,1>::next_float32 draws (ext/enoki/include/enoki/random.h:33-101), to pin the
+// port's and the device's restatement of the generator.
+void sdmm_ref_pcg32_floats(uint64_t state, uint64_t stream, int n, float* out) {
+    enoki::PCG32<float, 1> rng(state, stream);
+    for (int i = 0; i < n; ++i) out[i] = rng.next_float32();
 }
 
 // The timed CPU baseline: OpenMP parallel-for over cells, one cell per task -- the same

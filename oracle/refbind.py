@@ -15,6 +15,9 @@ LIB_PATH = os.path.join(_HERE, "_ref", "libsdmm_ref.so")
 JOINT_PLANES = 32
 EM_PLANES = 81
 SCALAR_WORDS = 8
+# enoki::PCG32 defaults (ext/enoki/include/enoki/random.h:33-35)
+PCG32_DEFAULT_STATE = 0x853c49e6748fea9b
+PCG32_DEFAULT_STREAM = 0xda3e39cb94b95bdb
 
 _lib = None
 
@@ -41,6 +44,9 @@ def lib():
         L.sdmm_ref_cell_get.argtypes = [C.c_void_p, fp, fp, up]
         L.sdmm_ref_cell_get_derived.argtypes = [C.c_void_p, fp]
         L.sdmm_ref_em_step.argtypes = [C.c_void_p, C.c_int, fp, C.c_long, fp, C.c_int, fp]
+        L.sdmm_ref_initialize.argtypes = [C.c_void_p, C.c_int, fp, fp, C.c_long, fp, C.c_int, C.c_float,
+                                          C.c_uint64, C.c_uint64]
+        L.sdmm_ref_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int, fp]
         L.sdmm_ref_em_batch.restype = C.c_double
         L.sdmm_ref_em_batch.argtypes = [vpp, C.c_int, up, fp, C.c_long, fp, C.c_int, C.c_int, C.c_int]
         L.sdmm_ref_prepare_conditioner.argtypes = [C.c_void_p]
@@ -126,6 +132,19 @@ class RefCells:
             L.sdmm_ref_cell_get(self.handles[c], _f(joint[c]), _f(em[c]), _u(scal[c]))
         return joint, em, scal
 
+    def initialize(self, offsets, point6, normal3, weight, spatial_distance,
+                   rng_state=PCG32_DEFAULT_STATE, rng_stream=PCG32_DEFAULT_STREAM):
+        """sdmm::initialize per cell (opt/init.h:17-193) with n_spatial = K / 8 seeds, as
+        initializeSDMMContext does (volpath_sdmm.cpp:132-137).  spatial_distance: per-cell array."""
+        L = lib()
+        stride = point6.shape[1]
+        for c in range(self.C):
+            b, e = int(offsets[c]), int(offsets[c + 1])
+            k = L.sdmm_ref_initialize(self.handles[c], e - b, _off(point6, b), _off(normal3, b), stride,
+                                      _off(weight, b), self.K // 8, float(spatial_distance[c]),
+                                      rng_state, rng_stream)
+            assert k == self.K, (k, self.K)
+
     def derived(self):
         L = lib()
         out = np.zeros((self.C, 38, self.K), np.float32)
@@ -205,6 +224,12 @@ class RefCells:
         L.sdmm_ref_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), 1, _u(idx), _f(pos), _f(d),
                        _f(pdf), _b(valid), _f(pmf), _f(cdf), 1)
         return pmf, cdf, bool(valid[0])
+
+
+def pcg32_floats(n, state=PCG32_DEFAULT_STATE, stream=PCG32_DEFAULT_STREAM):
+    out = np.zeros(n, np.float32)
+    lib().sdmm_ref_pcg32_floats(state, stream, n, _f(out))
+    return out
 
 
 def kat_pdf_scalar():

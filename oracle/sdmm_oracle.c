@@ -16,7 +16,15 @@
 #endif
 
 #define MAXD 8
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
 #define PI_F 3.14159265358979323846f
+
+/* enoki's packet exp (ext/enoki/include/enoki/array_math.h:711-770) returns exactly 0 below
+ * -88.3762588501 (no gradual underflow); libm's expf would keep denormals down to e^-103.  The cut
+ * decides which outlier samples the E-step skips (hsum == 0, opt/em.h:289-293). */
+static float enoki_expf(float x) { return (x < -88.3762588501f) ? 0.f : expf(x); }
 
 /* R: core/constants.h:31-47  gaussian_normalization = (1/sqrt(2 pi))^D */
 static float gaussian_normalization(int D) {
@@ -131,7 +139,7 @@ float oracle_gauss_pdf_euclid(int D, const float* mean, const float* cov, const 
     oracle_solve_lower(D, L, t, z);
     float sq = 0.f;
     for (int i = 0; i < D; ++i) sq += z[i] * z[i];
-    return inv_det * 1.f * gaussian_normalization(D) * expf(-0.5f * sq);
+    return inv_det * 1.f * gaussian_normalization(D) * enoki_expf(-0.5f * sq);
 }
 
 /* R: distributions/sdmm_conditioner.h:170-212 (prepare_vectorized) + :7-26 (create_marginal),
@@ -391,7 +399,7 @@ static float joint_posterior(const oracle_cell* c, int k, const float x[6], floa
     oracle_solve_lower(5, L, t, z);
     float sq = 0.f;
     for (int i = 0; i < 5; ++i) sq += z[i] * z[i];
-    float pdf = c->inv_det[k] * inv_jac * gaussian_normalization(5) * expf(-0.5f * sq);
+    float pdf = c->inv_det[k] * inv_jac * gaussian_normalization(5) * enoki_expf(-0.5f * sq);
     return pdf * c->pmf[k];
 }
 
@@ -720,7 +728,7 @@ static int create_conditional(const oracle_cell* c, const float x[3], float* pmf
         for (int i = 0; i < 9; ++i) L[i] = P(c->m_L, i, k);
         oracle_solve_lower(3, L, t, z);
         float sq = z[0] * z[0] + z[1] * z[1] + z[2] * z[2];
-        float pdf = c->m_inv_det[k] * 1.f * gaussian_normalization(3) * expf(-0.5f * sq);
+        float pdf = c->m_inv_det[k] * 1.f * gaussian_normalization(3) * enoki_expf(-0.5f * sq);
         pmf[k] = pdf * c->m_pmf[k];
     }
     return oracle_categorical_prepare(K, pmf, cdf);
@@ -767,7 +775,7 @@ static float conditional_pdf(const oracle_cell* c, const float* pmf, const float
         float z[2];
         oracle_solve_lower(2, L, t, z);
         float sq = z[0] * z[0] + z[1] * z[1];
-        float pdf = c->c_inv_det[k] * inv_jac * gaussian_normalization(2) * expf(-0.5f * sq);
+        float pdf = c->c_inv_det[k] * inv_jac * gaussian_normalization(2) * enoki_expf(-0.5f * sq);
         sum += pdf * pmf[k];
     }
     return sum;
@@ -894,4 +902,170 @@ double oracle_pdf(oracle_cell** cells, long n, const uint32_t* cell_idx, const f
     t1 = omp_get_wtime();
 #endif
     return t1 - t0;
+}
+
+/* ================================================================================================
+ * sdmm::initialize                                                       R: opt/init.h:17-193
+ * ================================================================================================
+ * Called once per cell by initializeSDMMContext (mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:
+ * 132-137) with n_spatial = K/8 seeds and a COPY of the context's default-seeded PCG32. */
+
+/* enoki::PCG32<float,1>                              R: ext/enoki/include/enoki/random.h:33-101 */
+typedef struct { uint64_t state, inc; } oracle_pcg32;
+static uint32_t pcg32_next_uint32(oracle_pcg32* r) {
+    uint64_t oldstate = r->state;
+    r->state = oldstate * 0x5851f42d4c957f2dULL + r->inc;
+    uint32_t xorshifted = (uint32_t)(((oldstate >> 18) ^ oldstate) >> 27);
+    uint32_t rot = (uint32_t)(oldstate >> 59);
+    return (xorshifted >> rot) | (xorshifted << ((32u - rot) & 31u));
+}
+static void pcg32_seed(oracle_pcg32* r, uint64_t initstate, uint64_t initseq) {
+    r->state = 0;
+    r->inc = (initseq << 1) | 1u;
+    pcg32_next_uint32(r);
+    r->state += initstate;
+    pcg32_next_uint32(r);
+}
+static float pcg32_next_float32(oracle_pcg32* r) {
+    uint32_t w = (pcg32_next_uint32(r) >> 9) | 0x3f800000u;
+    return w2f(w) - 1.f;
+}
+/* exposed so tests can pin the generator against the reference's */
+void oracle_pcg32_floats(uint64_t state, uint64_t stream, int n, float* out) {
+    oracle_pcg32 r;
+    pcg32_seed(&r, state, stream);
+    for (int i = 0; i < n; ++i) out[i] = pcg32_next_float32(&r);
+}
+
+/* sdmm::sample(Categorical&, RNG&)                         R: distributions/categorical.h:27-40 */
+static uint32_t categorical_sample(int n, const float* pmf, const float* cdf, float u) {
+    return select_component(n, pmf, cdf, u);
+}
+
+static float clamp_weight(float w) { /* enoki::min(enoki::max(w, 1e-3), 3)   R: init.h:64-66, 111-112 */
+    double m = (double)w > 1e-3 ? (double)w : 1e-3;
+    m = m < 3.0 ? m : 3.0;
+    return (float)m;
+}
+
+/* enoki::pow(float, int 5): square-and-multiply in float  R: ext/enoki array_math.h:960-973 */
+static float pow5f(float d) {
+    float x2 = d * d;
+    float x4 = x2 * x2;
+    return d * x4;
+}
+
+int oracle_initialize(oracle_cell* c, int N, const float* point6, const float* normal3, long stride,
+                      const float* weight, int n_spatial, float spatial_distance,
+                      uint64_t rng_state, uint64_t rng_stream, int32_t* out_seed_idx) {
+    const int K = c->K;
+    const int n_thetas = 2, n_phis = 4;
+    if (n_spatial * n_thetas * n_phis != K || N <= 0) return -1;
+    oracle_pcg32 rng;
+    pcg32_seed(&rng, rng_state, rng_stream);
+
+    /* em = zero<EM>(K); sdmm.cov = 0                                       R: init.h:36-39 */
+    memset(c->st_w, 0, sizeof(float) * K); memset(c->st_mean, 0, sizeof(float) * 5 * K);
+    memset(c->st_cov, 0, sizeof(float) * 25 * K);
+    memset(c->bt_w, 0, sizeof(float) * K); memset(c->bt_mean, 0, sizeof(float) * 5 * K);
+    memset(c->bt_cov, 0, sizeof(float) * 25 * K);
+    memset(c->sn_w, 0, sizeof(float) * K); memset(c->sn_mean, 0, sizeof(float) * 5 * K);
+    memset(c->sn_cov, 0, sizeof(float) * 25 * K);
+    memset(c->cov_prior, 0, sizeof(float) * 25 * K); memset(c->depth_prior, 0, sizeof(float) * 25 * K);
+    memset(c->cov, 0, sizeof(float) * 25 * K);
+    c->total_weight = 0.f; c->iterations_run = 0; c->samples_seen = 0;
+
+    const float max_rad_sqr = (float)6.251388631170325;  /* quantile(chi2(3), 0.90)  R: init.h:40-44 */
+    const float width_var = spatial_distance * spatial_distance / max_rad_sqr;
+    const float depth_var = (float)(3e-2 * 3e-2 / (double)max_rad_sqr);
+    const float directional_var = (float)(1.f * M_PI / 8.f);
+    for (int k = 0; k < K; ++k) { P(c->cov, 18, k) = directional_var; P(c->cov, 24, k) = directional_var; }
+
+    float* min_d = (float*)malloc(sizeof(float) * N);
+    float* min_sp = (float*)malloc(sizeof(float) * N);
+    float* min_nd = (float*)malloc(sizeof(float) * N);
+    float* pmf = (float*)malloc(sizeof(float) * N);
+    float* cdf = (float*)malloc(sizeof(float) * N);
+    for (int j = 0; j < N; ++j) {
+        min_d[j] = min_sp[j] = min_nd[j] = INFINITY;
+        pmf[j] = clamp_weight(weight[j]);                                   /* R: init.h:64-66 */
+    }
+    oracle_categorical_prepare(N, pmf, cdf);                                /* R: init.h:68 */
+    const float SPATIAL_THRESHOLD = (float)(2e-2 * 2e-2), NORMAL_THRESHOLD = (float)(2e-1 * 2e-1);
+
+    int comp = 0;
+    for (int sc = 0; sc < n_spatial; ++sc) {
+        const uint32_t pi_ = categorical_sample(N, pmf, cdf, pcg32_next_float32(&rng));  /* R: init.h:77 */
+        if (out_seed_idx) out_seed_idx[sc] = (int32_t)pi_;
+        float mean[6];
+        for (int d = 0; d < 6; ++d) mean[d] = point6[d * stride + pi_];
+        const float n[3] = {normal3[pi_], normal3[stride + pi_], normal3[2 * stride + pi_]};
+        float to[9], from[9];
+        oracle_frame(n, to, from);                                          /* R: init.h:84-87 */
+        const float s[3] = {from[0], from[3], from[6]}, t[3] = {from[1], from[4], from[7]};
+        float manifold[9], dprior[9];
+        for (int r = 0; r < 3; ++r)
+            for (int q = 0; q < 3; ++q) {
+                manifold[3 * r + q] = width_var * (s[r] * s[q]) + width_var * (t[r] * t[q]) + depth_var * (n[r] * n[q]);
+                dprior[3 * r + q] = (float)((double)(n[r] * n[q]) * 1e-6);  /* R: init.h:88-92 */
+            }
+        for (int j = 0; j < N; ++j) {                                       /* R: init.h:96-126 */
+            const float nj[3] = {normal3[j], normal3[stride + j], normal3[2 * stride + j]};
+            const float ndot = n[0] * nj[0] + n[1] * nj[1] + n[2] * nj[2];
+            const double a = (double)safe_acosf(ndot) / M_PI;
+            const float normal_d = (float)(a * a);
+            const float dx = mean[0] - point6[j], dy = mean[1] - point6[stride + j], dz = mean[2] - point6[2 * stride + j];
+            const float position_d = dx * dx + dy * dy + dz * dz;
+            const float d = normal_d + position_d;
+            if (d < min_d[j]) {
+                min_d[j] = d;
+                pmf[j] = clamp_weight(weight[j]) * pow5f(d);
+            }
+            if (normal_d < NORMAL_THRESHOLD && position_d < min_sp[j]) {
+                min_sp[j] = position_d;
+                min_nd[j] = normal_d;
+            }
+            if (min_nd[j] < NORMAL_THRESHOLD && min_sp[j] < SPATIAL_THRESHOLD) {
+                min_d[j] = 0;
+                pmf[j] = 0;
+            }
+        }
+        if (!oracle_categorical_prepare(N, pmf, cdf)) {                     /* R: init.h:127-139 */
+            for (int j = 0; j < N; ++j) pmf[j] = 1.f / (float)N;
+            oracle_categorical_prepare(N, pmf, cdf);
+        }
+        float theta = 0;
+        for (int ti = 0; ti < n_thetas; ++ti) {                             /* R: init.h:141-174 */
+            theta = (float)(theta + 0.5 * M_PI / ((float)n_thetas + 1.f));
+            const float cos_theta = cosf(theta);
+            const float sin_theta = safe_sqrtf(1.f - cos_theta * cos_theta);
+            float phi = 0;
+            for (int pi2 = 0; pi2 < n_phis; ++pi2) {
+                phi = (float)(phi + 2 * M_PI / (float)n_phis);
+                const float sin_phi = sinf(phi), cos_phi = cosf(phi);
+                const float dl[3] = {sin_theta * cos_phi, sin_theta * sin_phi, cos_theta};
+                float m6[6] = {mean[0], mean[1], mean[2], 0, 0, 0};
+                for (int r = 0; r < 3; ++r) m6[3 + r] = from[3 * r] * dl[0] + from[3 * r + 1] * dl[1] + from[3 * r + 2] * dl[2];
+                joint_set_mean(c, comp, m6);
+                /* mean.coeff(3..5) of the NEXT lobe reuses `mean`, whose direction part was just
+                 * overwritten (init.h:152-158) -- irrelevant, only the position part is read */
+                for (int r = 0; r < 3; ++r)
+                    for (int q = 0; q < 3; ++q) {
+                        P(c->depth_prior, 5 * r + q, comp) = dprior[3 * r + q];
+                        P(c->cov, 5 * r + q, comp) = manifold[3 * r + q];
+                    }
+                ++comp;
+            }
+        }
+    }
+    for (int k = 0; k < K; ++k) c->pmf[k] = 1.f / (float)K;                 /* R: init.h:177-179 */
+    joint_prepare_vectorized(c);
+    c->weight_prior = 1.f / (float)K;                                       /* R: init.h:181-192 */
+    c->cov_prior_strength = 5.f / (float)K;
+    const float cp[5] = {2e-3f, 2e-3f, 2e-3f, 2e-4f, 2e-4f};
+    for (int k = 0; k < K; ++k)
+        for (int i = 0; i < 5; ++i) P(c->cov_prior, 6 * i, k) = cp[i];
+    c->conditioner_ready = 0;
+    free(min_d); free(min_sp); free(min_nd); free(pmf); free(cdf);
+    return K;
 }

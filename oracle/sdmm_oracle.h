@@ -64,6 +64,12 @@ int oracle_categorical_prepare(int n, float* pmf, float* cdf);
 void oracle_frame(const float* n, float* to, float* from);
 void oracle_joint_to(const float* mean6, const float* point6, float* tangent5, float* inv_jac);
 int oracle_max_threads(void);
+/* sdmm::initialize (opt/init.h:17-193) with the default-seeded PCG32 copy of initializeSDMMContext;
+ * out_seed_idx (may be NULL): the n_spatial sample indices drawn as seeds.  Returns K or -1. */
+int oracle_initialize(oracle_cell*, int N, const float* point6, const float* normal3, long stride,
+                      const float* weight, int n_spatial, float spatial_distance,
+                      uint64_t rng_state, uint64_t rng_stream, int32_t* out_seed_idx);
+void oracle_pcg32_floats(uint64_t state, uint64_t stream, int n, float* out);
 
 #ifdef __cplusplus
 }

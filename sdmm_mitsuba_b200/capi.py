@@ -16,6 +16,9 @@ EM_PLANES = 81
 SCALAR_WORDS = 8
 QUERY_RECORD_FLOATS = 32
 
+PCG32_DEFAULT_STATE = 0x853c49e6748fea9b
+PCG32_DEFAULT_STREAM = 0xda3e39cb94b95bdb
+
 ST_STEP_ABORTED, ST_CDF_INVALID, ST_NON_PSD, ST_COND_INVALID = 1, 2, 4, 8
 
 # every symbol include/sdmm_b200.h declares (tests check the library exports exactly these)
@@ -26,7 +29,7 @@ SYMBOLS = [
     "sdmmb_optimize_host", "sdmmb_prepare_conditioner", "sdmmb_download_conditioner", "sdmmb_sample_pdf", "sdmmb_pdf",
     "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_set_tree", "sdmmb_find_cells", "sdmmb_find_cells_host", "sdmmb_collect_samples",
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
-    "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks",
+    "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
 ]
 
 _lib = None
@@ -90,6 +93,8 @@ def lib():
     L.sdmmb_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.sdmmb_last_estep_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i)]
     L.sdmmb_measure_peaks.argtypes = [i, C.POINTER(C.c_float)]
+    L.sdmmb_initialize.argtypes = [vp, i, i, fp, fp, sz, fp, up, fp, C.c_uint64, C.c_uint64, vp, vp]
+    L.sdmmb_initialize_host.argtypes = [vp, i, i, fp, fp, sz, fp, up, fp, C.c_uint64, C.c_uint64, vp, vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):
             getattr(L, name).restype = i

@@ -84,6 +84,11 @@ __global__ void pack_samples_kernel(const float* __restrict__ point6, size_t str
 #define SDMMB_ACOS_C5 -1.114577623e-02f
 #define SDMMB_ACOS_C6 2.295893482e-03f
 #define SDMMB_ONE_MINUS 0.99999994f
+// Sample weights enter the accumulation scaled by 2^-64 and the partial sums leave scaled by 2^64
+// (exact powers of two: bit-identical statistics).  w_n / sum_k pi_k p_k overflows float32 when the
+// mixture density at an outlier is tiny (the reference forms gamma = p / sum <= 1 first, em.h:295-309).
+#define SDMMB_W_SCALE 5.421010862427522e-20f
+#define SDMMB_W_UNSCALE 18446744073709551616.f
 // Broadcast constants as 64-bit pairs in constant memory so FFMA2 can take them as a c[][] operand
 // instead of burning two registers (or two MOVs per use) each.
 __constant__ float2 kC2[10] = {
@@ -360,7 +365,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
         __syncwarp();
         // per-warp staging slot of a sample: (x, y, z, dx) (dy, -dz, w_eff, -)
         wbuf[lane * 2 + 0] = make_float4(ra.x, ra.y, ra.z, rb.x);
-        wbuf[lane * 2 + 1] = make_float4(rb.y, -rb.z, rb.w, 0.f);
+        wbuf[lane * 2 + 1] = make_float4(rb.y, -rb.z, rb.w * SDMMB_W_SCALE, 0.f);
         wsum += ra.w;
         n_wvalid += (rb.w > 0.f) ? 1 : 0;
         __syncwarp();
@@ -406,7 +411,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
                     const float rs = rcp_approx(sum[j]);
                     const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);
                     const float sc = ok ? B[j].z * rs : 0.f;
-                    n_ok += (sc > 0.f) ? 1 : 0;
+                    n_ok += (ok && B[j].z > 0.f) ? 1 : 0;
                     if (LL) {
                         if (l == 0 && cbase + si < item.end) out_loglik[cbase + si] = logf(sum[j]);
                     }
@@ -438,7 +443,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             const float rs = rcp_approx(sum);
             const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);   // sum finite, > 0, 1/sum finite
             const float sc = ok ? w * rs : 0.f;                       // w_n / sum   R: em.h:295-298, 309
-            n_ok += (sc > 0.f) ? 1 : 0;
+            n_ok += (ok && w > 0.f) ? 1 : 0;
             if (LL) {
                 if (l == 0 && cbase + si < item.end) out_loglik[cbase + si] = logf(sum);
             }
@@ -506,7 +511,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
         float s = red[i];
 #pragma unroll
         for (int wv = 1; wv < WARPS; ++wv) s += red[(size_t)wv * ESTAT_PLANES * K + i];
-        out[i] = s;
+        out[i] = s * SDMMB_W_UNSCALE;
     }
     if (threadIdx.x == 0) {
         float ws = s_wsum[0];

@@ -103,6 +103,25 @@ struct TreeNode {
     uint32_t child1;
 };
 
+// sdmm::initialize on the device (init_kernels.cu): one CTA per cell
+struct InitArgs {
+    int K, K_user;
+    int first_cell, n_cells;
+    const float* point6;    // 6 planes, `stride` floats apart
+    const float* normal3;   // 3 planes, same stride
+    const float* weight;
+    size_t stride;
+    const uint32_t* offsets;          // device, [n_cells+1] sample ranges (relative to the plane starts)
+    const float* spatial_distance;    // device, [n_cells]
+    uint64_t rng_state, rng_stream;   // PCG32 seed every cell's COPY of the generator starts from
+    float* scratch;                   // 5 floats per sample
+    float* joint;
+    float* em;
+    uint32_t* scal;
+    int32_t* out_seed_idx;            // nullable, device, [n_cells][K_user/8]
+};
+cudaError_t launch_init_cells(const InitArgs& a, cudaStream_t st);
+
 cudaError_t launch_find_cells(const TreeNode* nodes, int n_nodes, const float* pos3, size_t stride, size_t n,
                               uint32_t* out, uint32_t miss, cudaStream_t st);
 cudaError_t launch_collect_count(const TreeNode* nodes, int n_nodes, const float* key3, size_t key_stride,

@@ -129,6 +129,31 @@ class SDMMCells:
         self.n_samples = int(off[-1] - off[0])
         self._bound = (first_cell, n_cells)
 
+    def initialize(self, point6, normal3, weight, cell_offsets, spatial_distance, first_cell=0,
+                   rng_state=capi.PCG32_DEFAULT_STATE, rng_stream=capi.PCG32_DEFAULT_STREAM):
+        """sdmm::initialize (sdmm/include/sdmm/opt/init.h:17-193) for every cell of the range from its own
+        samples (point6 [6,N], normal3 [3,N], weight [N]); spatial_distance: per-cell array.  Returns the seed
+        sample indices [C, K/8] (relative to each cell's first sample)."""
+        off = _np(np.asarray(cell_offsets), np.uint32)
+        n_cells = off.shape[0] - 1
+        sd = _np(np.broadcast_to(np.asarray(spatial_distance, np.float32), (n_cells,)), np.float32)
+        seeds = np.zeros((n_cells, self.K // 8), np.int32)
+        if _is_torch(point6):
+            assert point6.is_cuda and normal3.is_cuda and weight.is_cuda
+            assert point6.is_contiguous() and normal3.is_contiguous() and weight.is_contiguous()
+            assert point6.shape[0] == 6 and normal3.shape[0] == 3 and normal3.shape[1] == point6.shape[1]
+            check(self._L.sdmmb_initialize(self._h, first_cell, n_cells, C.c_void_p(point6.data_ptr()),
+                                           C.c_void_p(normal3.data_ptr()), point6.shape[1],
+                                           C.c_void_p(weight.data_ptr()), _hp(off), _hp(sd), rng_state, rng_stream,
+                                           _hp(seeds), _stream(self.device)), "sdmmb_initialize", self._h)
+        else:
+            point6, normal3, weight = _np(point6, np.float32), _np(normal3, np.float32), _np(weight, np.float32)
+            assert point6.shape[0] == 6 and normal3.shape == (3, point6.shape[1])
+            check(self._L.sdmmb_initialize_host(self._h, first_cell, n_cells, _hp(point6), _hp(normal3),
+                                                point6.shape[1], _hp(weight), _hp(off), _hp(sd), rng_state,
+                                                rng_stream, _hp(seeds), None), "sdmmb_initialize_host", self._h)
+        return seeds
+
     def em_step(self, n_iters=1, first_cell=None, n_cells=None, with_conditioner=True, want_loglik=False):
         """n_iters x sdmm::em_step on every bound cell (+ sdmm::prepare of the conditioner after the
         last one).  want_loglik -> torch tensor [n_iters, N] of per-sample log-likelihoods."""

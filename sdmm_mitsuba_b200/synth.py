@@ -61,6 +61,56 @@ def make_samples(n_cells, n_per_cell, seed=0, n_lobes=8, dtype=np.float32):
     return np.ascontiguousarray(point6), weight, offsets
 
 
+def make_normals(n_cells, n_per_cell, seed=0, n_patches=6, jitter=0.05):
+    """Surface normals for sdmm::initialize inputs: each sample belongs to one of n_patches flat-ish
+    patches per cell (patch normal + small jitter), unit length in float32.  Returns [3, C*N]."""
+    rng = np.random.default_rng(seed + 7919)
+    C, N, G = n_cells, n_per_cell, n_patches
+    pn = _unit(rng.normal(size=(C, G, 3)))
+    which = rng.integers(0, G, (C, N))
+    n = pn[np.arange(C)[:, None], which] + jitter * rng.normal(size=(C, N, 3))
+    n = n.astype(np.float32)
+    n /= np.sqrt((n * n).sum(-1, keepdims=True, dtype=np.float32))
+    return np.ascontiguousarray(n.reshape(C * N, 3).T)
+
+
+def make_surface_samples(n_cells, n_per_cell, seed=0, n_patches=4, dtype=np.float32):
+    """Renderer-like training samples for sdmm::initialize + the first fits: positions ON a few planar
+    patches per cell (tiny noise along the normal), the patch normal as the sample normal, directions from
+    two lobes in the patch's upper hemisphere, log-normal weights.  Returns point6 [6,C*N], normal3 [3,C*N],
+    weight [C*N], offsets [C+1]."""
+    rng = np.random.default_rng(seed + 104729)
+    C, N, G = n_cells, n_per_cell, n_patches
+    centre = rng.uniform(0.25, 0.75, (C, G, 3))
+    pn = _unit(rng.normal(size=(C, G, 3)))
+    ps, pt = _frame(pn)
+    extent = rng.uniform(0.08, 0.25, (C, G, 2))
+    which = rng.integers(0, G, (C, N))
+    ci = np.arange(C)[:, None]
+    ab = rng.uniform(-1, 1, (C, N, 2)) * extent[ci, which]
+    n = pn[ci, which]
+    x = centre[ci, which] + ab[..., :1] * ps[ci, which] + ab[..., 1:] * pt[ci, which] + 0.003 * rng.normal(size=(C, N, 1)) * n
+    x = np.clip(x, 0.0, 1.0)
+    # two directional lobes per patch, tilted away from the normal by up to ~60 degrees
+    lobe_dir = _unit(pn[:, :, None, :] + 0.9 * rng.normal(size=(C, G, 2, 3)) * 0.6)
+    lobe = rng.integers(0, 2, (C, N))
+    m = lobe_dir[ci, which, lobe]
+    d = _unit(m + 0.25 * rng.normal(size=(C, N, 3)))
+    flip = (d * n).sum(-1, keepdims=True) < 0.05          # keep directions in the upper hemisphere
+    d = np.where(flip, _unit(d - 2 * (d * n).sum(-1, keepdims=True) * n + 0.1 * n), d)
+    d = d.astype(np.float32)
+    d /= np.sqrt((d * d).sum(-1, keepdims=True, dtype=np.float32))
+    nn = n.astype(np.float32)
+    nn /= np.sqrt((nn * nn).sum(-1, keepdims=True, dtype=np.float32))
+    w = np.clip(np.exp(rng.normal(size=(C, N))), 1e-3, 1e3)
+    point6 = np.empty((6, C * N), dtype)
+    point6[0:3] = x.reshape(C * N, 3).T
+    point6[3:6] = d.reshape(C * N, 3).T
+    normal3 = np.ascontiguousarray(nn.reshape(C * N, 3).T)
+    offsets = (np.arange(C + 1, dtype=np.uint64) * N).astype(np.uint32)
+    return np.ascontiguousarray(point6), normal3, w.reshape(C * N).astype(dtype), offsets
+
+
 def make_initial_model(n_cells, K, seed=1):
     """Initial mixtures + EM state as the integrator sets them (sdmm/opt/init.h:178-192 priors):
     position means ~U[0,1]^3, direction means uniform on S^2, cov = 0.05 I_5, pmf = 1/K,

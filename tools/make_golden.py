@@ -93,8 +93,39 @@ def make_tree():
     print(path, "%.0f KB" % (os.path.getsize(path) / 1e3), "nodes", nodes.shape[0], "leaves", int(nodes[:, 0].sum()))
 
 
+INIT_CASES = {
+    # name: (cells, K, samples per cell)
+    "init_k64": (3, 64, 1500),
+    "init_k16": (4, 16, 600),
+}
+
+
+def make_init(name, C, K, N):
+    """sdmm::initialize (opt/init.h:17-193) run by the reference on seeded surface-like samples, with the
+    default-seeded PCG32 copy of initializeSDMMContext (volpath_sdmm.cpp:132-137); plus the first draws of
+    the reference's generator."""
+    point6, weight, off = synth.make_samples(C, N, seed=5000 + K)
+    normal3 = synth.make_normals(C, N, seed=5000 + K)
+    weight[5] = 0.0            # clamped up to 1e-3 by the sampling weight
+    weight[7] = 50.0           # clamped down to 3
+    rng = np.random.default_rng(6000 + K)
+    sd = (3.0 * rng.uniform(0.3, 1.0, C) / (K // 8)).astype(np.float32)
+    o = refbind.RefCells(C, K)
+    o.initialize(off, point6, normal3, weight, sd)
+    j, e, s = o.get()
+    path = os.path.join(ROOT, "tests", "golden", name + ".npz")
+    np.savez_compressed(path, point6=point6, normal3=normal3, weight=weight, offsets=off, spatial_distance=sd,
+                        joint=j, em=e, scal=s, derived=o.derived(), pcg32=refbind.pcg32_floats(64),
+                        meta=np.array([C, K, N], np.int64))
+    print(path, "%.0f KB" % (os.path.getsize(path) / 1e3))
+
+
 if __name__ == "__main__":
     assert refbind.available(), "build oracle/_ref first (make -C oracle ref)"
+    for name, cfg in INIT_CASES.items():
+        make_init(name, *cfg)
+    if "--init-only" in sys.argv:
+        sys.exit(0)
     make_tree()
     for name, cfg in CASES.items():
         make(name, *cfg)
