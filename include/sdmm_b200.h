@@ -125,6 +125,11 @@ int sdmmb_initialize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const flo
                           const uint32_t* h_cell_offsets, const float* h_spatial_distance,
                           uint64_t rng_state, uint64_t rng_stream, int32_t* h_out_seed_idx, void* stream);
 
+/* STree::create_child's inheritance (sdmm/accelerators/spatial_tree.h:187-196): when a leaf is split, both
+ * children start from copies of the parent's mixture, conditioner and EM state.  Copies the complete
+ * per-cell device state of cell h_src[i] into cell h_dst[i] (in order).  Synchronous. */
+int sdmmb_copy_cells(sdmmb_ctx* ctx, int n, const int32_t* h_src, const int32_t* h_dst, void* stream);
+
 /* n_iters x sdmm::em_step (sdmm/opt/em.h:218-253) on every bound cell of the range, i.e. the body
  * of the ThreadPool::parallelFor in SDMMVolumetricPathTracer::optimize (volpath_sdmm.cpp:287-311):
  * E-step + sufficient statistics (em.h:255-314), stepwise blend (:316-328), normalise (:330-351),

@@ -1,0 +1,77 @@
+/* sdmm_b200_render.h -- C ABI of the device-resident guided path tracer for analytic scenes, the front
+ * end of the progressive training loop.  It replaces, for scenes made of
+ * diffuse quads and quad area lights, the render pass of one iteration of the reference integrator:
+ *   SDMMProcess::process / SDMMRenderer::Li   mitsuba/src/integrators/sdmm/sdmm_proc.cpp:106-195, 592-968
+ *   sampleSurface / pdfSurface                mitsuba/src/integrators/sdmm/sdmm_proc.cpp:275-590
+ * The guided queries inside it go through the same fused query kernel as sdmmb_sample_pdf / sdmmb_pdf
+ * (include/sdmm_b200.h).  The training half of an iteration (optimize(), volpath_sdmm.cpp:244-312) is the
+ * existing sdmmb_initialize / sdmmb_set_samples / sdmmb_em_step; the loop around both lives in
+ * sdmm_mitsuba_b200/integrator.py.  Mitsuba's scene loading, film and samplers are out of scope: the caller
+ * passes quads and a pinhole camera.  All `d_` pointers are device pointers; return codes as sdmm_b200.h. */
+#ifndef SDMM_B200_RENDER_H
+#define SDMM_B200_RENDER_H
+#include "sdmm_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sdmmb_pt sdmmb_pt;
+
+/* parallelogram p0 + u e1 + v e2, (u, v) in [0,1]^2, e1 orthogonal to e2; front side = e1 x e2.
+ * One-sided diffuse reflectance (Mitsuba `diffuse`), one-sided emitted radiance (Mitsuba `area`). */
+typedef struct {
+    float p0[3], e1[3], e2[3];
+    float reflectance[3];
+    float emission[3];
+} sdmmb_quad;
+
+/* pinhole camera: direction through film position (sx, sy) in pixels =
+ * forward + (1 - 2 sx / width) tan(fov_x / 2) right + (1 - 2 sy / height) tan(fov_x / 2) (height / width) up */
+typedef struct {
+    float origin[3], right[3], up[3], forward[3];
+    float fov_x_degrees;
+    int width, height;
+} sdmmb_camera;
+
+typedef struct {
+    float aabb_min[3];      /* scene AABB minimum and largest extent: createCondition, sdmm_proc.cpp:263-273 */
+    float spatial_norm;
+    float root_min[3];      /* STree root box in normalised coordinates (getAABB, volpath_sdmm.cpp:314-330) */
+    float root_max[3];
+    int max_depth;          /* integrator maxDepth (== rrDepth, volpath_sdmm.cpp:78-79); <= 9 */
+    int saved_per_path;     /* savedSamplesPerPath, default 8 (volpath_sdmm.cpp:60) */
+} sdmmb_pt_config;
+
+typedef struct {
+    uint64_t paths;
+    uint64_t guided_queries;   /* sample + pdf queries (mixture-sampled vertices) */
+    uint64_t mis_queries;      /* pdf-only queries (BSDF-sampled vertices that need the mixture pdf) */
+    uint64_t pool_count;       /* samples in the pool after this pass */
+    uint64_t pool_overflow;    /* samples dropped because the pool was full ("Data full.", opt/data.h:60-66) */
+    uint64_t launches;
+} sdmmb_pt_stats;
+
+int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, int n_quads,
+                    const sdmmb_camera* h_camera, const sdmmb_pt_config* h_config);
+int sdmmb_pt_destroy(sdmmb_pt* pt);
+
+/* One render pass = `spp` paths per pixel (one iteration's samplesPerIteration).  Uses the tree bound with
+ * sdmmb_set_tree and the query records of ctx.  guided = 0 reproduces iteration 0 (BSDF sampling only,
+ * sdmm_proc.cpp:316-323); d_cell_initialized [max_cells] marks cells whose conditioner may be used
+ * (SDMMContext::initialized).  d_image_sum [3][height*width] accumulates radiance sums (divide by the total
+ * spp).  If collect != 0, training samples are appended to d_pool [15][pool_capacity] planes
+ * (x y z dx dy dz | nx ny nz | weight | key x y z | is_main | seq) starting at index pool_count:
+ * key = the position whose leaf cell receives the sample (the vertex itself, or its jittered copy,
+ * sdmm_proc.cpp:932-964); is_main = 1 for the pushes that also feed the cell's SpatialStats; seq (uint32 bits) = path * 32 +
+ * vertex * 4 + jitter, the order in which a single-threaded reference would have pushed (the pool itself is
+ * filled in scheduling order; sdmm::initialize depends on the order of a cell's samples).  Needs
+ * width * height * spp < 2^27.  Synchronous. */
+int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collect,
+                    const uint8_t* d_cell_initialized, float* d_image_sum, float* d_pool,
+                    size_t pool_capacity, size_t pool_count, sdmmb_pt_stats* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

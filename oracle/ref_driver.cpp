@@ -275,10 +275,15 @@ int sdmm_ref_em_step(void* h, int N, const float* point6, long stride, const flo
     auto& c = *static_cast<RefCell*>(h);
     Data data;
     load_data(data, N, point6, (size_t)stride, weight);
+    // the integrator's own floating-point mode: flushDenormals = true by default
+    // (mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:62, 85-87 -> enoki::set_flush_denormals(true))
+    const bool was = enoki::flush_denormals();
+    enoki::set_flush_denormals(true);
     for (int it = 0; it < n_iters; ++it) {
         if (out_loglik) loglik(c, data, out_loglik + (size_t)it * N);
         sdmm::em_step(c.sdmm, c.em, data);
     }
+    enoki::set_flush_denormals(was);
     c.conditioner_ready = false;
     return 0;
 }
@@ -332,7 +337,10 @@ double sdmm_ref_em_batch(void** cells, int C, const uint32_t* offsets, const flo
 #endif
     for (int ci = 0; ci < C; ++ci) {
         auto& c = *static_cast<RefCell*>(cells[ci]);
+        const bool was = enoki::flush_denormals();
+        enoki::set_flush_denormals(true);   // the integrator's mode (volpath_sdmm.cpp:62, 85-87)
         for (int it = 0; it < n_iters; ++it) sdmm::em_step(c.sdmm, c.em, datas[ci]);
+        enoki::set_flush_denormals(was);
         if (with_prepare) {
             enoki::set_slices(c.conditioner, enoki::slices(c.sdmm));
             sdmm::prepare(c.conditioner, c.sdmm);
@@ -731,3 +739,4 @@ void sdmm_ref_tree_find(void* h, long n, const float* pos3, int32_t* out_node) {
 }
 
 }  // extern "C"
+#include "ref_render.inc"

@@ -316,3 +316,64 @@ class RefTree:
         out = np.zeros(pos3.shape[1], np.int32)
         lib().sdmm_ref_tree_find(self.h, pos3.shape[1], _f(pos3), out.ctypes.data_as(C.POINTER(C.c_int32)))
         return out
+
+
+class RefRenderer:
+    """The CPU restatement of the reference integrator's progressive loop (oracle/ref_render.inc) for a quad
+    scene; mixture, tree and EM work is the reference's own code."""
+
+    def __init__(self, quads, camera, lo, norm, root_min, root_max, K=16, max_depth=5, saved_per_path=8,
+                 capacity=200000, split_threshold=4000):
+        L = lib()
+        fp = C.POINTER(C.c_float)
+        L.sdmm_ref_renderer_create.restype = C.c_void_p
+        L.sdmm_ref_renderer_create.argtypes = [fp, C.c_int, fp, C.c_int, C.c_int, fp, C.c_float, fp, fp, C.c_int, C.c_int,
+                                               C.c_int, C.c_long, C.c_uint64, C.c_long]
+        L.sdmm_ref_renderer_destroy.argtypes = [C.c_void_p]
+        L.sdmm_ref_renderer_iteration.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.sdmm_ref_renderer_image.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_renderer_tree_size.argtypes = [C.c_void_p]
+        L.sdmm_ref_renderer_tree_export.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_renderer_leaf_joint.argtypes = [C.c_void_p, C.c_int, fp, C.POINTER(C.c_uint32)]
+        q = np.zeros((len(quads), 15), np.float32)
+        for i, x in enumerate(quads):
+            q[i] = np.concatenate([x["p0"], x["e1"], x["e2"], x["reflectance"], x["emission"]])
+        cam = np.concatenate([camera["origin"], camera["right"], camera["up"], camera["forward"],
+                              [camera["fov_x_degrees"]]]).astype(np.float32)
+        self.K, self.W, self.H = K, int(camera["width"]), int(camera["height"])
+        self._h = C.c_void_p(L.sdmm_ref_renderer_create(
+            _f(q), len(quads), _f(cam), self.W, self.H, _f(np.asarray(lo, np.float32)), float(norm),
+            _f(np.asarray(root_min, np.float32)), _f(np.asarray(root_max, np.float32)), max_depth, saved_per_path, K,
+            capacity, 0, split_threshold))
+        self.total_spp = 0
+
+    def __del__(self):
+        try:
+            lib().sdmm_ref_renderer_destroy(self._h)
+        except Exception:
+            pass
+
+    def iteration(self, spp, pass_seed, still_training, force_unguided=False):
+        st = (C.c_double * 7)()
+        lib().sdmm_ref_renderer_iteration(self._h, spp, pass_seed, 1 if still_training else 0,
+                                          1 if force_unguided else 0, st)
+        self.total_spp += spp
+        keys = ["trained", "leaves", "fresh", "train_samples", "data_samples", "guided_queries", "mis_queries"]
+        return {k: int(v) for k, v in zip(keys, st)}
+
+    def image(self):
+        out = np.zeros((3, self.H, self.W), np.float32)
+        lib().sdmm_ref_renderer_image(self._h, _f(out))
+        return out / max(1, self.total_spp)
+
+    def nodes(self):
+        n = lib().sdmm_ref_renderer_tree_size(self._h)
+        out = np.zeros((n, 13), np.float32)
+        lib().sdmm_ref_renderer_tree_export(self._h, _f(out))
+        return out
+
+    def leaf_joint(self, node):
+        joint = np.zeros((JOINT_PLANES, self.K), np.float32)
+        scal = np.zeros(SCALAR_WORDS, np.uint32)
+        k = lib().sdmm_ref_renderer_leaf_joint(self._h, node, _f(joint), _u(scal))
+        return (joint, scal) if k else (None, None)

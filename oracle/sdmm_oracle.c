@@ -9,6 +9,7 @@
 #include "sdmm_oracle.h"
 
 #include <math.h>
+#include <xmmintrin.h>
 #include <stdlib.h>
 #include <string.h>
 #ifdef _OPENMP
@@ -25,6 +26,12 @@
  * -88.3762588501 (no gradual underflow); libm's expf would keep denormals down to e^-103.  The cut
  * decides which outlier samples the E-step skips (hsum == 0, opt/em.h:289-293). */
 static float enoki_expf(float x) { return (x < -88.3762588501f) ? 0.f : expf(x); }
+
+/* The reference INTEGRATOR runs with flush-to-zero / denormals-are-zero (flushDenormals = true by default,
+ * mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:62, 85-87 -> enoki::set_flush_denormals), so densities below
+ * 2^-126 are exactly 0 there.  The EM / query entry points of this restatement run under the same mode. */
+static unsigned ftz_enter(void) { unsigned old = _mm_getcsr(); _mm_setcsr(old | 0x8040u); return old; }
+static void ftz_leave(unsigned old) { _mm_setcsr(old); }
 
 /* R: core/constants.h:31-47  gaussian_normalization = (1/sqrt(2 pi))^D */
 static float gaussian_normalization(int D) {
@@ -634,8 +641,10 @@ static void em_step(oracle_cell* c, int N, const float* point6, long stride, con
 
 int oracle_em_step(oracle_cell* c, int N, const float* point6, long stride, const float* weight,
                    int n_iters, float* out_loglik, int sum_mode) {
+    const unsigned csr = ftz_enter();
     for (int it = 0; it < n_iters; ++it)
         em_step(c, N, point6, stride, weight, out_loglik ? out_loglik + (size_t)it * N : NULL, sum_mode);
+    ftz_leave(csr);
     c->conditioner_ready = 0;
     return 0;
 }

@@ -30,7 +30,30 @@ SYMBOLS = [
     "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_set_tree", "sdmmb_find_cells", "sdmmb_find_cells_host", "sdmmb_collect_samples",
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
+    "sdmmb_copy_cells", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
 ]
+
+
+
+class Quad(C.Structure):   # sdmmb_quad (include/sdmm_b200_render.h)
+    _fields_ = [("p0", C.c_float * 3), ("e1", C.c_float * 3), ("e2", C.c_float * 3),
+                ("reflectance", C.c_float * 3), ("emission", C.c_float * 3)]
+
+
+class Camera(C.Structure):   # sdmmb_camera
+    _fields_ = [("origin", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3),
+                ("forward", C.c_float * 3), ("fov_x_degrees", C.c_float), ("width", C.c_int), ("height", C.c_int)]
+
+
+class PtConfig(C.Structure):   # sdmmb_pt_config
+    _fields_ = [("aabb_min", C.c_float * 3), ("spatial_norm", C.c_float), ("root_min", C.c_float * 3),
+                ("root_max", C.c_float * 3), ("max_depth", C.c_int), ("saved_per_path", C.c_int)]
+
+
+class PtStats(C.Structure):   # sdmmb_pt_stats
+    _fields_ = [("paths", C.c_uint64), ("guided_queries", C.c_uint64), ("mis_queries", C.c_uint64),
+                ("pool_count", C.c_uint64), ("pool_overflow", C.c_uint64), ("launches", C.c_uint64)]
+
 
 _lib = None
 
@@ -95,6 +118,10 @@ def lib():
     L.sdmmb_measure_peaks.argtypes = [i, C.POINTER(C.c_float)]
     L.sdmmb_initialize.argtypes = [vp, i, i, fp, fp, sz, fp, up, fp, C.c_uint64, C.c_uint64, vp, vp]
     L.sdmmb_initialize_host.argtypes = [vp, i, i, fp, fp, sz, fp, up, fp, C.c_uint64, C.c_uint64, vp, vp]
+    L.sdmmb_pt_create.argtypes = [vp, C.POINTER(vp), C.POINTER(Quad), i, C.POINTER(Camera), C.POINTER(PtConfig)]
+    L.sdmmb_pt_destroy.argtypes = [vp]
+    L.sdmmb_copy_cells.argtypes = [vp, i, vp, vp, vp]
+    L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):
             getattr(L, name).restype = i

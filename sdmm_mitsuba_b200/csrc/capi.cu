@@ -11,7 +11,10 @@
 #include <vector>
 
 #include "../../include/sdmm_b200.h"
+#include "../../include/sdmm_b200_render.h"
+#include <cmath>
 #include "kernels.h"
+#include "render.h"
 
 using namespace sdmmb;
 

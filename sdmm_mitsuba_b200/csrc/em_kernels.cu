@@ -28,6 +28,15 @@ __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
 __device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
+// flush-to-zero product: the reference integrator runs with FTZ/DAZ (flushDenormals = true by default,
+// mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:62, 85-87), so a component density below 2^-126 is exactly 0
+__device__ __forceinline__ float2 mul2_ftz(float2 a, float2 b) {
+    unsigned long long ra, rb, rc;
+    ra = *reinterpret_cast<unsigned long long*>(&a);
+    rb = *reinterpret_cast<unsigned long long*>(&b);
+    asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(rc) : "l"(ra), "l"(rb));
+    return *reinterpret_cast<float2*>(&rc);
+}
 
 __device__ __forceinline__ float rsqrt_approx(float x) {
     float y;
@@ -91,10 +100,11 @@ __global__ void pack_samples_kernel(const float* __restrict__ point6, size_t str
 #define SDMMB_W_UNSCALE 18446744073709551616.f
 // Broadcast constants as 64-bit pairs in constant memory so FFMA2 can take them as a c[][] operand
 // instead of burning two registers (or two MOVs per use) each.
-__constant__ float2 kC2[10] = {
+__constant__ float2 kC2[11] = {
     {SDMMB_ACOS_C0, SDMMB_ACOS_C0}, {SDMMB_ACOS_C1, SDMMB_ACOS_C1}, {SDMMB_ACOS_C2, SDMMB_ACOS_C2},
     {SDMMB_ACOS_C3, SDMMB_ACOS_C3}, {SDMMB_ACOS_C4, SDMMB_ACOS_C4}, {SDMMB_ACOS_C5, SDMMB_ACOS_C5},
-    {SDMMB_ACOS_C6, SDMMB_ACOS_C6}, {1.f, 1.f}, {-1.f, -1.f}, {-3.14159265358979323846f, -3.14159265358979323846f}};
+    {SDMMB_ACOS_C6, SDMMB_ACOS_C6}, {1.f, 1.f}, {-1.f, -1.f}, {-3.14159265358979323846f, -3.14159265358979323846f},
+    {-1.5f, -1.5f}};
 
 struct PairOut {
     float2 p;     // pi_k p_k(x) for the two components of the pair
@@ -158,14 +168,18 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
     z3 = fma2(W[9], o.t[3], z3);
     z4 = fma2(W[13], o.t[3], z4);
     z4 = fma2(W[14], o.t[4], z4);
-    // e = |z|^2 - log2(pi_k inv_det (2 pi)^-5/2);  p = inv_jac * 2^-e       R: distributions/sdmm.h:292-294, 337
-    float2 e = fma2(z0, z0, prm[EREC_NLC]);
+    // e = |z|^2 (log2 units);  p = (inv_jac * c_k) * 2^-e                   R: distributions/sdmm.h:292-294, 337
+    // The reference integrator runs with FTZ/DAZ (flushDenormals = true, volpath_sdmm.cpp:62, 85-87): its exp
+    // result is dead below 2^-126 and so is every product below 2^-126.  ex2.ftz gives 0 for e > 126 whatever
+    // the component's coefficient c_k, the FTZ product does the rest -- this decides which outlier samples the
+    // E-step skips (hsum == 0, opt/em.h:289-293).
+    float2 e = mul2(z0, z0);
     e = fma2(z1, z1, e);
     e = fma2(z2, z2, e);
     e = fma2(z3, z3, e);
     e = fma2(z4, z4, e);
     float2 ex = make_float2(ex2_approx(-e.x), ex2_approx(-e.y));
-    o.p = mul2(r, ex);
+    o.p = mul2_ftz(mul2(r, prm[EREC_NLC]), ex);
     return o;
 }
 
@@ -237,7 +251,7 @@ __device__ __forceinline__ void estep_pair_multi(const float2* __restrict__ prm,
     }
     float2 ee[S];
 #pragma unroll
-    SDMMB_EACH ee[s] = fma2(z[s][0], z[s][0], prm[EREC_NLC]);
+    SDMMB_EACH ee[s] = mul2(z[s][0], z[s][0]);
 #pragma unroll
     for (int row = 1; row < 5; ++row)
 #pragma unroll
@@ -245,7 +259,7 @@ __device__ __forceinline__ void estep_pair_multi(const float2* __restrict__ prm,
 #pragma unroll
     SDMMB_EACH {
         float2 ex = make_float2(ex2_approx(-ee[s].x), ex2_approx(-ee[s].y));
-        o[s].p = mul2(r[s], ex);
+        o[s].p = mul2_ftz(mul2(r[s], prm[EREC_NLC]), ex);
     }
 #undef SDMMB_EACH
 }
@@ -569,9 +583,8 @@ __device__ inline void write_erec(float* __restrict__ erec_cell, int K, int k, f
                 erec_cell[(EREC_W + e++) * K + k] = (c == 4) ? sign * w : w;
             }
     }
-    // -log2(pi_k * inv_det * (2 pi)^-5/2); +inf switches a zero-weight component off (2^-inf = 0)
-    float coef = pmf * cp.inv_det * gaussian_normalization(5);
-    erec_cell[EREC_NLC * K + k] = (coef > 0.f) ? -log2f(coef) : (coef == 0.f ? INFINITY : NAN);
+    // pi_k * inv_det * (2 pi)^-5/2; 0 switches a zero-weight component off
+    erec_cell[EREC_NLC * K + k] = pmf * cp.inv_det * gaussian_normalization(5);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -17,7 +17,7 @@ constexpr int EREC_ROT = 3;   // 6: the Duff frame in factored form: n.x, n.y, n
                               //    sign * n.x, sign * n.y  (sign = copysign(1, n.z)); see estep_pair()
 constexpr int EREC_W = 9;     // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major; the (4,4) entry
                               //    carries the factor `sign` because the kernel works with sign * t_4
-constexpr int EREC_NLC = 24;  // 1: -log2(pmf * inv_cov_sqrt_det * (2 pi)^-5/2)
+constexpr int EREC_NLC = 24;  // 1: pmf * inv_cov_sqrt_det * (2 pi)^-5/2
 constexpr int EREC_PLANES = 25;
 
 // E-step partial statistics per item: 21 planes of K floats

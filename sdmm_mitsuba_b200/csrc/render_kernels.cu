@@ -1,0 +1,427 @@
+// render_kernels.cu -- device-resident guided path tracer for analytic (quad) scenes: the front end of
+// the progressive training loop.
+//
+// Reference ("R:" = /root/reference/mitsuba/src/integrators/sdmm/sdmm_proc.cpp):
+//   SDMMRenderer::Li                R: 592-968   path loop, vertex records, sample weights, collection
+//   SDMMRenderer::sampleSurface     R: 275-508   BSDF / guided one-sample MIS (fraction 0.5)
+//   SDMMRenderer::pdfSurface        R: 510-590   0.5 bsdfPdf + 0.5 gmmPdf
+//   createCondition                 R: 263-273   position normalised by the scene's largest extent
+// specialised to what the analytic scenes contain: one-sided diffuse BSDFs, one-sided area emitters, no
+// media, no next-event estimation (NEE is compiled out in the reference: `#ifdef NEE`, R: 696), maxDepth ==
+// rrDepth as the integrator enforces (volpath_sdmm.cpp:78-79), which makes Russian roulette unreachable
+// (R: 838: depth++ >= rrDepth never holds inside the loop).
+//
+// B200 design: WAVEFRONT, not a megakernel.  The guided query (conditional mixture of K components per
+// vertex) is the expensive part and is served by the fused query kernel K4, which wants vertices batched and
+// binned by cell.  So one bounce = one `pt_bounce_kernel` launch over all paths (finalise the previous
+// bounce's sampling decision, trace, emission, vertex bookkeeping, decide BSDF vs guided and append a query
+// record to list A (guided: sample + pdf) or list B (BSDF-sampled: pdf only)), then two K4 launches over the
+// compacted lists.  Paths keep a private PCG32 stream (6 draws per bounce in a fixed order), so results do
+// not depend on scheduling.
+#include "kernels.h"
+#include "render.h"
+
+namespace sdmmb {
+
+namespace {
+
+constexpr float PT_RAY_EPS = 1e-4f;       // Mitsuba's ray epsilon
+constexpr float PT_SPEC_EPS = 1e-4f;      // Mitsuba's Epsilon in Vertex::record          R: 615-619
+constexpr float PT_INV_PI = 0.31830988618379067154f;
+constexpr float PT_PI = 3.14159265358979323846f;
+
+struct Rng {
+    uint64_t state, inc;
+    __device__ uint32_t next_uint32() {
+        uint64_t oldstate = state;
+        state = oldstate * 0x5851f42d4c957f2dULL + inc;
+        uint32_t xorshifted = (uint32_t)(((oldstate >> 18) ^ oldstate) >> 27);
+        uint32_t rot = (uint32_t)(oldstate >> 59);
+        return (xorshifted >> rot) | (xorshifted << ((32u - rot) & 31u));
+    }
+    __device__ void seed(uint64_t initstate, uint64_t initseq) {
+        state = 0;
+        inc = (initseq << 1) | 1u;
+        next_uint32();
+        state += initstate;
+        next_uint32();
+    }
+    __device__ float next() { return __uint_as_float((next_uint32() >> 9) | 0x3f800000u) - 1.f; }
+};
+
+struct V3 {
+    float x, y, z;
+};
+__device__ __forceinline__ V3 v3(float x, float y, float z) { return V3{x, y, z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
+
+// nearest quad along (o, d); returns quad index or -1
+__device__ int intersect(const PtScene& sc, V3 o, V3 d, float& t_hit) {
+    int best = -1;
+    float tb = 3.0e38f;
+    for (int q = 0; q < sc.n_quads; ++q) {
+        const PtQuad& Q = sc.quads[q];
+        const V3 n = ld3(Q.n);
+        const float dn = dot(n, d);
+        if (dn == 0.f) continue;
+        const V3 p0 = ld3(Q.p0);
+        const float t = dot(n, p0 - o) / dn;
+        if (!(t > PT_RAY_EPS && t < tb)) continue;
+        const V3 h = o + d * t - p0;
+        const float u = dot(h, ld3(Q.e1)) * Q.inv_len2[0];
+        const float v = dot(h, ld3(Q.e2)) * Q.inv_len2[1];
+        if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) continue;
+        tb = t;
+        best = q;
+    }
+    t_hit = tb;
+    return best;
+}
+
+// Mitsuba warp::squareToCosineHemisphere (concentric disk + projection)
+__device__ V3 cosine_hemisphere(float u1, float u2) {
+    const float r1 = 2.f * u1 - 1.f, r2 = 2.f * u2 - 1.f;
+    float r, phi;
+    if (r1 == 0.f && r2 == 0.f) {
+        r = phi = 0.f;
+    } else if (r1 * r1 > r2 * r2) {
+        r = r1;
+        phi = (PT_PI / 4.f) * (r2 / r1);
+    } else {
+        r = r2;
+        phi = (PT_PI / 2.f) - (r1 / r2) * (PT_PI / 4.f);
+    }
+    float s, c;
+    sincosf(phi, &s, &c);
+    const float x = r * c, y = r * s;
+    return v3(x, y, sqrtf(fmaxf(0.f, 1.f - x * x - y * y)));
+}
+
+// STree::find with the leaf's AABB (R: sdmm/include/sdmm/accelerators/spatial_tree.h:19-51); the AABB is
+// rebuilt during the descent: child 0 is the upper half (its min[axis] = split), child 1 the lower half.
+__device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, int n_nodes, V3 p, const float* root_min,
+                                   const float* root_max, float* amin, float* amax, uint32_t miss) {
+    for (int i = 0; i < 3; ++i) { amin[i] = root_min[i]; amax[i] = root_max[i]; }
+    uint32_t node = 0;
+    for (int depth = 0; depth < 96; ++depth) {
+        if (node >= (uint32_t)n_nodes) return miss;
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
+        const int axis = raw.x;
+        if (axis < 0) return (uint32_t)raw.z;
+        const float split = __int_as_float(raw.y);
+        const float c = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
+        if (split < c) { node = (uint32_t)raw.z; amin[axis] = split; }
+        else { node = (uint32_t)raw.w; amax[axis] = split; }
+    }
+    return miss;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// camera rays (process(): samplePos = pixel + next2D, sensor ray; R: 146-176)
+// ------------------------------------------------------------------------------------------------
+__global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, PtFrame F) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    const PtScene& sc = *scp;
+    const size_t npix = (size_t)sc.width * sc.height;
+    const size_t pix = i % npix;
+    const int px = (int)(pix % sc.width), py = (int)(pix / sc.width);
+    Rng rng;
+    rng.seed(F.seed, (uint64_t)i);
+    const float sx = (float)px + rng.next(), sy = (float)py + rng.next();
+    const float cx = (1.f - 2.f * sx / (float)sc.width) * sc.tan_x;
+    const float cy = (1.f - 2.f * sy / (float)sc.height) * sc.tan_y;
+    V3 d = ld3(sc.cam_forward) + ld3(sc.cam_right) * cx + ld3(sc.cam_up) * cy;
+    d = d * rsqrtf(dot(d, d));
+    const size_t n = P.n;
+    P.o[i] = sc.cam_origin[0]; P.o[n + i] = sc.cam_origin[1]; P.o[2 * n + i] = sc.cam_origin[2];
+    P.d[i] = d.x; P.d[n + i] = d.y; P.d[2 * n + i] = d.z;
+    for (int c = 0; c < 3; ++c) { P.thr[c * n + i] = 1.f; P.li[c * n + i] = 0.f; }
+    P.rng[i] = rng.state; P.rng[n + i] = rng.inc;
+    P.depth[i] = 1;   // rRec.newQuery: depth = 1 at the first intersection
+    P.vcount[i] = 0;
+    P.mode[i] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// one bounce of every live path
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
+                                                        int first, size_t nA, size_t nB) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    int depth = P.depth[i];
+    if (depth <= 0) return;
+    const PtScene& sc = *scp;
+    const size_t n = P.n;
+    Rng rng{P.rng[i], P.rng[n + i]};
+    V3 thr = v3(P.thr[i], P.thr[n + i], P.thr[2 * n + i]);
+    V3 li = v3(P.li[i], P.li[n + i], P.li[2 * n + i]);
+    int vc = P.vcount[i];
+    V3 o, d;
+    int hq;
+    float t_hit;
+    bool alive = true;
+
+    if (!first) {
+        // ---- finalise the sampling decision taken at the pending hit (sampleSurface, R: 383-507) ----
+        const PtQuad& Q = sc.quads[P.quad[i]];
+        const V3 nrm = ld3(Q.n), rho = ld3(Q.reflectance);
+        const V3 p = v3(P.pend[i], P.pend[n + i], P.pend[2 * n + i]);
+        const float b1 = P.pend[3 * n + i], b2 = P.pend[4 * n + i];
+        const V3 npos = v3(P.pend[5 * n + i], P.pend[6 * n + i], P.pend[7 * n + i]);
+        const int mode = P.mode[i];
+        const uint32_t slot = P.slot[i];
+        V3 wo = v3(0.f, 0.f, 0.f), weight = v3(0.f, 0.f, 0.f);
+        float misPdf = 0.f;
+        bool use_bsdf = (mode != 2);
+        if (mode == 2) {
+            if (L.validA[slot]) {                        // validConditional
+                if (L.ijA[slot] == 0.f) alive = false;   // inv_jacobian == 0 -> Spectrum(0)   R: 436-439
+                wo = v3(L.dirA[slot], L.dirA[nA + slot], L.dirA[2 * nA + slot]);
+                const float cos_o = dot(nrm, wo);
+                const float bsdfPdf = cos_o * PT_INV_PI;
+                if (!(bsdfPdf > 0.f)) alive = false;     // pdfSurface: bsdfPdf <= 0 -> 0       R: 527-530
+                misPdf = 0.5f * bsdfPdf + 0.5f * L.pdfA[slot];
+                const float f = PT_INV_PI * cos_o / misPdf;   // bsdf->eval / pdf               R: 464, 507
+                weight = rho * f;
+            } else {
+                use_bsdf = true;                         // !validConditional -> BSDF, weight 1 R: 388-393
+            }
+        }
+        if (use_bsdf) {
+            const V3 loc = cosine_hemisphere(b1, b2);
+            V3 s = ld3(Q.e1);
+            s = s * rsqrtf(dot(s, s));
+            const V3 tt = v3(nrm.y * s.z - nrm.z * s.y, nrm.z * s.x - nrm.x * s.z, nrm.x * s.y - nrm.y * s.x);
+            wo = s * loc.x + tt * loc.y + nrm * loc.z;
+            const float bsdfPdf = loc.z * PT_INV_PI;
+            if (!(bsdfPdf > 0.f)) alive = false;
+            if (mode == 1 && L.validB[slot]) {
+                misPdf = 0.5f * bsdfPdf + 0.5f * L.pdfB[slot];   // bsdfWeight *= pdf; / pdfSurface  R: 404, 507
+                weight = rho * (bsdfPdf / misPdf);
+            } else {
+                misPdf = bsdfPdf;                        // pdf *= 1; bsdfWeight / 1            R: 398-402
+                weight = rho;
+            }
+        }
+        if (!(weight.x > 0.f || weight.y > 0.f || weight.z > 0.f) || !(misPdf > 0.f)) alive = false;  // R: 760
+        if (alive) {
+            thr = thr * weight;
+            o = p;
+            d = wo;
+            hq = intersect(sc, o, d, t_hit);            // rayIntersectAndLookForEmitter      R: 796-798
+            V3 value = v3(0.f, 0.f, 0.f);
+            if (hq >= 0) {
+                const PtQuad& H = sc.quads[hq];
+                if (dot(ld3(H.n), d) < 0.f) value = ld3(H.emission);
+            }
+            if (value.x > 0.f || value.y > 0.f || value.z > 0.f) {   // recordRadiance     R: 628-637, 810-812
+                const V3 rad = thr * value;
+                li = li + rad;
+                for (int v = 0; v < vc && v < PT_MAX_VERTS; ++v) {
+                    float* vp = P.verts + ((size_t)v * PT_VERT_FLOATS) * n + i;
+                    const float vpdf = vp[15 * n];
+                    const float r3[3] = {rad.x, rad.y, rad.z};
+                    for (int c = 0; c < 3; ++c) {
+                        const float vthr = vp[(12 + c) * n];
+                        if (vthr > PT_SPEC_EPS) vp[(9 + c) * n] += r3[c] / (vthr * vpdf);
+                    }
+                }
+            }
+            if (vc < PT_MAX_VERTS) {                     // the cacheable vertex               R: 814-840
+                float* vp = P.verts + ((size_t)vc * PT_VERT_FLOATS) * n + i;
+                const float clamped = fmaxf(misPdf, 0.1f);
+                const float inv = 1.f / clamped;
+                vp[0] = npos.x; vp[n] = npos.y; vp[2 * n] = npos.z;
+                vp[3 * n] = wo.x; vp[4 * n] = wo.y; vp[5 * n] = wo.z;
+                vp[6 * n] = nrm.x; vp[7 * n] = nrm.y; vp[8 * n] = nrm.z;
+                vp[9 * n] = value.x * inv; vp[10 * n] = value.y * inv; vp[11 * n] = value.z * inv;
+                vp[12 * n] = thr.x; vp[13 * n] = thr.y; vp[14 * n] = thr.z;
+                vp[15 * n] = clamped;
+            }
+            ++vc;
+            ++depth;                                     // rRec.depth++                       R: 852
+            if (hq < 0) alive = false;
+        }
+    } else {
+        o = v3(P.o[i], P.o[n + i], P.o[2 * n + i]);
+        d = v3(P.d[i], P.d[n + i], P.d[2 * n + i]);
+        hq = intersect(sc, o, d, t_hit);
+        if (hq < 0) alive = false;
+        else {
+            const PtQuad& H = sc.quads[hq];              // emitted radiance seen directly   R: 672-675
+            if (dot(ld3(H.n), d) < 0.f) li = li + thr * ld3(H.emission);
+        }
+    }
+
+    if (alive && depth >= sc.max_depth) alive = false;   // R: 682-683
+    if (alive) {
+        const PtQuad& H = sc.quads[hq];
+        const V3 hn = ld3(H.n);
+        // one-sided diffuse: sample()/eval() return 0 from behind or for a black surface
+        if (!(dot(hn, d) < 0.f) || !(H.reflectance[0] > 0.f || H.reflectance[1] > 0.f || H.reflectance[2] > 0.f))
+            alive = false;
+    }
+    if (alive) {
+        const V3 p = o + d * t_hit;
+        const float u_mis = rng.next(), b1 = rng.next(), b2 = rng.next();
+        const float g0 = rng.next(), g1 = rng.next(), g2 = rng.next();
+        const V3 npos = (p - ld3(sc.aabb_min)) * sc.inv_spatial_norm;    // createCondition  R: 263-273
+        int mode = 0;
+        uint32_t slot = 0;
+        if (F.guided) {
+            float amin[3], amax[3];
+            const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, npos, sc.root_min, sc.root_max, amin, amax,
+                                                 0xffffffffu);
+            if (cell < F.max_cells && F.cell_initialized[cell]) {
+                if (u_mis <= 0.5f) {                     // heuristicConditionalWeight       R: 383-392
+                    mode = 1;
+                    const PtQuad& H = sc.quads[hq];
+                    const V3 hn = ld3(H.n);
+                    const V3 loc = cosine_hemisphere(b1, b2);
+                    V3 s = ld3(H.e1);
+                    s = s * rsqrtf(dot(s, s));
+                    const V3 tt = v3(hn.y * s.z - hn.z * s.y, hn.z * s.x - hn.x * s.z, hn.x * s.y - hn.y * s.x);
+                    const V3 wo = s * loc.x + tt * loc.y + hn * loc.z;
+                    slot = atomicAdd(&L.counters[1], 1u);
+                    float4* r = reinterpret_cast<float4*>(L.recB + (size_t)slot * 8);
+                    r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
+                    r[1] = make_float4(wo.x, wo.y, wo.z, 0.f);
+                } else {
+                    mode = 2;
+                    slot = atomicAdd(&L.counters[0], 1u);
+                    float4* r = reinterpret_cast<float4*>(L.recA + (size_t)slot * 8);
+                    r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
+                    r[1] = make_float4(g0, g1, g2, 0.f);
+                }
+            }
+        }
+        P.quad[i] = hq;
+        P.mode[i] = mode;
+        P.slot[i] = slot;
+        P.pend[i] = p.x; P.pend[n + i] = p.y; P.pend[2 * n + i] = p.z;
+        P.pend[3 * n + i] = b1; P.pend[4 * n + i] = b2;
+        P.pend[5 * n + i] = npos.x; P.pend[6 * n + i] = npos.y; P.pend[7 * n + i] = npos.z;
+    }
+    P.rng[i] = rng.state;
+    P.thr[i] = thr.x; P.thr[n + i] = thr.y; P.thr[2 * n + i] = thr.z;
+    P.li[i] = li.x; P.li[n + i] = li.y; P.li[2 * n + i] = li.z;
+    P.vcount[i] = vc;
+    P.depth[i] = alive ? depth : 0;
+}
+
+// AoS staging records -> the dense SoA planes (stride = list length) the query kernels take
+__global__ void pt_pack_lists_kernel(PtLists L, size_t nA, size_t nB) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nA) {
+        const float4* r = reinterpret_cast<const float4*>(L.recA + i * 8);
+        const float4 a = r[0], b = r[1];
+        L.cellA[i] = __float_as_uint(a.x);
+        L.posA[i] = a.y; L.posA[nA + i] = a.z; L.posA[2 * nA + i] = a.w;
+        L.uA[i] = b.x; L.uA[nA + i] = b.y; L.uA[2 * nA + i] = b.z;
+    }
+    if (i < nB) {
+        const float4* r = reinterpret_cast<const float4*>(L.recB + i * 8);
+        const float4 a = r[0], b = r[1];
+        L.cellB[i] = __float_as_uint(a.x);
+        L.posB[i] = a.y; L.posB[nB + i] = a.z; L.posB[2 * nB + i] = a.w;
+        L.dirB[i] = b.x; L.dirB[nB + i] = b.y; L.dirB[2 * nB + i] = b.z;
+    }
+}
+
+__device__ void pool_push(const PtLists& L, const PtFrame& F, const float* vp, size_t n, float w, V3 key, float is_main,
+                          uint32_t seq) {
+    const uint32_t idx = atomicAdd(&L.counters[2], 1u);
+    if (idx >= F.pool_cap) {
+        atomicAdd(&L.counters[3], 1u);   // "Data full." (R: sdmm/include/sdmm/opt/data.h:60-66)
+        return;
+    }
+    float* o = F.pool + idx;
+    const size_t S = F.pool_cap;
+    for (int c = 0; c < 9; ++c) o[c * S] = vp[c * n];   // point6 | normal3
+    o[9 * S] = w;
+    o[10 * S] = key.x; o[11 * S] = key.y; o[12 * S] = key.z;
+    o[13 * S] = is_main;
+    o[14 * S] = __uint_as_float(seq);   // order a single-threaded reference would push in: path, vertex, jitter
+}
+
+// end of every path: film accumulation + the sample collection of Li's tail (R: 862-965)
+__global__ void pt_finish_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n) return;
+    const PtScene& sc = *scp;
+    const size_t n = P.n;
+    const size_t npix = (size_t)sc.width * sc.height;
+    const size_t pix = i % npix;
+    for (int c = 0; c < 3; ++c) atomicAdd(&F.image[c * npix + pix], P.li[c * n + i]);
+    const int depth = min(P.vcount[i], PT_MAX_VERTS);
+    if (depth == 0 || !F.collect) return;
+    Rng rng{P.rng[i], P.rng[n + i]};
+    const int first_saved = max(depth - sc.saved_per_path, 0);
+    for (int dv = depth - 1; dv >= first_saved; --dv) {
+        const float* vp = P.verts + ((size_t)dv * PT_VERT_FLOATS) * n + i;
+        const float w = (vp[9 * n] + vp[10 * n] + vp[11 * n]) * (1.f / 3.f);   // weight.average()
+        const bool valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);         // is_valid_sample
+        const V3 pos = v3(vp[0], vp[n], vp[2 * n]);
+        float smin[3], smax[3];
+        const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
+        if (cell >= F.max_cells) continue;   // the reference throws here; positions are inside the root AABB
+        const uint32_t seq0 = ((uint32_t)i << 5) | ((uint32_t)(depth - 1 - dv) << 2);
+        if (valid) pool_push(L, F, vp, n, w, pos, 1.f, seq0);
+        uint32_t pushed = 0;
+        int n_jitters = (dv >= depth - 1) ? 1 : 0;
+        if (w > 1000.f) ++n_jitters;
+        int attempts = 0;
+        for (int j = 0; j < n_jitters; ++j) {
+            const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next();
+            const V3 key = v3(pos.x + (u0 - 0.5f) * (smax[0] - smin[0]), pos.y + (u1 - 0.5f) * (smax[1] - smin[1]),
+                              pos.z + (u2 - 0.5f) * (smax[2] - smin[2]));
+            float jmin[3], jmax[3];
+            const uint32_t jc = find_leaf_aabb(F.tree, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
+            // find() never fails for a point outside the root box (it lands in a boundary leaf), as in the reference
+            if (jc >= F.max_cells || (jmin[0] == smin[0] && jmin[1] == smin[1] && jmin[2] == smin[2])) {
+                ++attempts;
+                if (attempts < 8) --j;
+                continue;
+            }
+            if (valid) pool_push(L, F, vp, n, w, key, 0.f, seq0 + (++pushed));
+        }
+    }
+}
+
+namespace {
+unsigned blocks_for(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
+}  // namespace
+
+cudaError_t pt_launch_generate(const PtScene* d_scene, const PtPaths& P, const PtFrame& F, cudaStream_t st) {
+    pt_generate_kernel<<<blocks_for(P.n, 256), 256, 0, st>>>(d_scene, P, F);
+    return cudaGetLastError();
+}
+
+cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, int first,
+                             size_t nA, size_t nB, cudaStream_t st) {
+    pt_bounce_kernel<<<blocks_for(P.n, 128), 128, 0, st>>>(d_scene, P, L, F, first, nA, nB);
+    return cudaGetLastError();
+}
+
+cudaError_t pt_launch_pack_lists(const PtLists& L, size_t nA, size_t nB, cudaStream_t st) {
+    const size_t m = nA > nB ? nA : nB;
+    if (m == 0) return cudaSuccess;
+    pt_pack_lists_kernel<<<blocks_for(m, 256), 256, 0, st>>>(L, nA, nB);
+    return cudaGetLastError();
+}
+
+cudaError_t pt_launch_finish(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, cudaStream_t st) {
+    pt_finish_kernel<<<blocks_for(P.n, 256), 256, 0, st>>>(d_scene, P, L, F);
+    return cudaGetLastError();
+}
+
+}  // namespace sdmmb

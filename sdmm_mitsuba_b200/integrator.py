@@ -1,0 +1,259 @@
+"""Progressive training loop with device-resident mixtures: the host side of
+the reference integrator's render() / optimize() for analytic scenes.
+
+Reference mirrored (paths relative to /root/reference/mitsuba/src/integrators/sdmm):
+  SDMMVolumetricPathTracer::render    volpath_sdmm.cpp:334-516   iteration loop, m_still_training, m_totalSpp
+  optimize()                          volpath_sdmm.cpp:244-312   split, canBeOptimized, initialize, em_step x 2|1,
+                                                                 prepare, data.clear()
+  canBeOptimized                      volpath_sdmm.cpp:140-149
+  initializeSDMMContext               volpath_sdmm.cpp:132-137
+The render pass itself (Li, sampleSurface, sample collection) runs on the device: sdmmb_pt_render
+(include/sdmm_b200_render.h).  Everything numeric runs in the CUDA library; torch is used here for device
+buffers and for index glue (sorting the sample pool by cell, per-cell counts and SpatialStats sums).
+Synchronous schedule (optimizeAsync = false, as scripts/run_tests.sh:29 runs the reference)."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi, scenes
+from .capi import check
+from .mixture import SDMMCells
+from .tree import HostTree
+
+SPLIT_THRESHOLD = 4000      # volpath_sdmm.cpp:528
+MAX_LEAF_NODES = 2048       # volpath_sdmm.cpp:529
+POOL_PLANES = 15
+
+
+class SDMMIntegrator:
+    def __init__(self, quads, camera, K=16, max_depth=5, samples_per_iteration=4, saved_per_path=8, max_cells=4096,
+                 pool_capacity=8_000_000, device=0, seed=1234, split_threshold=SPLIT_THRESHOLD):
+        import torch
+        self.torch = torch
+        self.dev = torch.device("cuda", device)
+        self.K, self.spi, self.max_depth = int(K), int(samples_per_iteration), int(max_depth)
+        self.seed = int(seed)
+        self.split_threshold = int(split_threshold)
+        self.cells = SDMMCells(max_cells, K, device=device)
+        self.cells.set_min_samples(1)
+        lo, hi, norm = scenes.scene_bounds(quads)
+        rmin, rmax = scenes.root_aabb(lo, hi, norm)
+        self.tree = HostTree(rmin, rmax, max_cells)
+        self.tree.split_to_depth(2)                                   # volpath_sdmm.cpp:398
+        self.cells.set_tree(self.tree.flatten())
+        self.width, self.height = int(camera["width"]), int(camera["height"])
+        qs = (capi.Quad * len(quads))()
+        for i, q in enumerate(quads):
+            for name in ("p0", "e1", "e2", "reflectance", "emission"):
+                getattr(qs[i], name)[:] = [float(v) for v in q[name]]
+        cam = capi.Camera()
+        for name in ("origin", "right", "up", "forward"):
+            getattr(cam, name)[:] = [float(v) for v in camera[name]]
+        cam.fov_x_degrees, cam.width, cam.height = float(camera["fov_x_degrees"]), self.width, self.height
+        cfg = capi.PtConfig()
+        cfg.aabb_min[:] = [float(v) for v in lo]
+        cfg.spatial_norm = float(norm)
+        cfg.root_min[:] = [float(v) for v in rmin]
+        cfg.root_max[:] = [float(v) for v in rmax]
+        cfg.max_depth, cfg.saved_per_path = self.max_depth, int(saved_per_path)
+        self._pt = C.c_void_p()
+        check(self.cells._L.sdmmb_pt_create(self.cells._h, C.byref(self._pt), qs, len(quads), C.byref(cam), C.byref(cfg)),
+              "sdmmb_pt_create", self.cells._h)
+        self.pool = torch.zeros((POOL_PLANES, pool_capacity), dtype=torch.float32, device=self.dev)
+        self.pool_count = 0
+        self.initialized = torch.zeros(max_cells, dtype=torch.uint8, device=self.dev)   # SDMMContext::initialized
+        self.has_mixture = np.zeros(max_cells, bool)                                   # slices(context->sdmm) != 0
+        self.image_sum = torch.zeros((3, self.height * self.width), dtype=torch.float32, device=self.dev)
+        self.iteration = 0
+        self.total_spp = 0
+        self.stats = []
+
+    def close(self):
+        if getattr(self, "_pt", None) is not None and self._pt:
+            self.cells._L.sdmmb_pt_destroy(self._pt)
+            self._pt = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- one render pass (SDMMProcess::process) ---------------------------------------------------
+    def render_pass(self, spp, collect, guided=None, image_sum=None):
+        torch = self.torch
+        guided = (self.iteration != 0) if guided is None else guided        # sdmm_proc.cpp:316-323
+        img = self.image_sum if image_sum is None else image_sum
+        st = capi.PtStats()
+        seed = (self.seed * 0x9E3779B97F4A7C15 + self.iteration) & 0xFFFFFFFFFFFFFFFF
+        check(self.cells._L.sdmmb_pt_render(self._pt, int(spp), seed, 1 if guided else 0, 1 if collect else 0,
+                                            C.c_void_p(self.initialized.data_ptr()), C.c_void_p(img.data_ptr()),
+                                            C.c_void_p(self.pool.data_ptr()), self.pool.shape[1], self.pool_count,
+                                            C.byref(st), C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
+              "sdmmb_pt_render", self.cells._h)
+        new = (self.pool_count, int(st.pool_count))
+        self.pool_count = int(st.pool_count)
+        if collect and new[1] > new[0]:
+            # canonical order: the pool is filled in scheduling order; put this pass's samples in the order a
+            # single-threaded reference would have pushed them (older passes stay in front)
+            seg = self.pool[:, new[0]:new[1]]
+            order = torch.argsort(seg[14].contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF)
+            self.pool[:, new[0]:new[1]] = seg.index_select(1, order)
+        return st, new
+
+    # ---- optimize() -------------------------------------------------------------------------------
+    def _pool_cells(self, lo=0, hi=None):
+        hi = self.pool_count if hi is None else hi
+        key = self.pool[10:13, lo:hi].contiguous()
+        return self.cells.find_cells(key).to(self.torch.int64)
+
+    def optimize(self, new_range):
+        torch = self.torch
+        t = self.tree
+        n = self.pool_count
+        if n == 0:
+            return dict(trained=0, leaves=t.n_leaves)
+        # cell of every pooled sample = the Data it was pushed into (key = vertex or its jittered copy)
+        cell_of = self._pool_cells()
+        # SpatialStats of the leaves: only the main pushes of this pass feed them (sdmm_proc.cpp:893-895)
+        lo, hi = new_range
+        if hi > lo:
+            main = self.pool[13, lo:hi] > 0.5
+            pos = self.pool[0:3, lo:hi].to(torch.float64)
+            cm = cell_of[lo:hi][main]
+            size = torch.bincount(cm, minlength=self.cells.max_cells).cpu().numpy()
+            s1 = torch.zeros((3, self.cells.max_cells), dtype=torch.float64, device=self.dev).index_add_(1, cm, pos[:, main])
+            s2 = torch.zeros((3, self.cells.max_cells), dtype=torch.float64, device=self.dev).index_add_(1, cm, pos[:, main] ** 2)
+            s1, s2 = s1.cpu().numpy(), s2.cpu().numpy()
+            for node in t.leaves():
+                sl = t.slot[node]
+                if size[sl]:
+                    t.st_size[node] += int(size[sl])
+                    t.st_sum[node] = t.st_sum[node] + s1[:, sl]
+                    t.st_sqr[node] = t.st_sqr[node] + s2[:, sl]
+        # data-driven splits (volpath_sdmm.cpp:253-259); children inherit the parent's state
+        if t.n_leaves <= MAX_LEAF_NODES:
+            ppos = self.pool[0:3, :n]
+
+            def on_split(parent_slot, slot0, slot1, axis, c0_min, c1_max):
+                # create_child (spatial_tree.h:190-203): the parent's data is re-bucketed by the sample POSITION along
+                # the split axis: child 0 takes min < p, child 1 takes max >= p
+                m = cell_of == parent_slot
+                upper = ppos[axis] > c0_min
+                lower = ppos[axis] <= c1_max
+                cell_of[m & upper] = slot0
+                cell_of[m & ~upper & lower] = slot1
+                cell_of[m & ~upper & ~lower] = -1          # falls between the two boxes (rounding gap): dropped
+
+            def child_stats(slot, amin, amax):
+                p = ppos[:, cell_of == slot]
+                a = torch.as_tensor(amin, device=self.dev)[:, None]
+                b = torch.as_tensor(amax, device=self.dev)[:, None]
+                inside = ((p >= a) & (p <= b)).all(dim=0)               # AABB::contains
+                q = p[:, inside].to(torch.float64)
+                return int(inside.sum()), q.sum(dim=1).cpu().numpy(), (q * q).sum(dim=1).cpu().numpy()
+
+            splits = t.split_leaves(self.split_threshold, child_stats, on_split)
+            if splits:
+                src = [s[0] for s in splits]
+                dst = [s[2] for s in splits]                              # child 0 keeps the parent's slot
+                self.cells.copy_cells(src, dst)
+                init_h = self.initialized.cpu().numpy()
+                for a_, b_ in zip(src, dst):        # sequential: a fresh child can itself be split in the same pass
+                    init_h[b_] = init_h[a_]
+                    self.has_mixture[b_] = self.has_mixture[a_]
+                self.initialized.copy_(torch.as_tensor(init_h, device=self.dev))
+                self.cells.set_tree(t.flatten())
+                # keep find(key) consistent with the re-bucketing: move the key of a sample whose key now resolves to
+                # a different leaf to the centre of the leaf that owns it
+                found = self._pool_cells()
+                centre = np.zeros((self.cells.max_cells, 3), np.float32)
+                for node in t.leaves():
+                    centre[t.slot[node]] = 0.5 * (t.amin[node] + t.amax[node])
+                bad = (found != cell_of) & (cell_of >= 0)
+                if bool(bad.any()):
+                    self.pool[10:13, :n][:, bad] = torch.as_tensor(centre, device=self.dev)[cell_of[bad]].t()
+                dropped = cell_of < 0
+                if bool(dropped.any()):
+                    keepm = ~dropped
+                    kept0 = self.pool[:, :n][:, keepm]
+                    n = int(kept0.shape[1])
+                    self.pool[:, :n] = kept0
+                    self.pool_count = n
+                    cell_of = cell_of[keepm]
+        # canBeOptimized (volpath_sdmm.cpp:140-149)
+        cells_all = cell_of
+        data_size = torch.bincount(cells_all, minlength=self.cells.max_cells).cpu().numpy()
+        stats_size = np.zeros(self.cells.max_cells, np.int64)
+        diag = np.zeros(self.cells.max_cells, np.float32)
+        for node in t.leaves():
+            stats_size[t.slot[node]] = t.st_size[node]
+            diag[t.slot[node]] = float((t.amax[node] - t.amin[node]).max())
+        can = ((self.total_spp > 12) | (data_size > 1000)) & (stats_size >= 64) & (data_size >= 8)
+        if not can.any():
+            return dict(trained=0, leaves=t.n_leaves)
+        can_t = torch.as_tensor(can, device=self.dev)
+        sel = can_t[cells_all]
+        order = torch.argsort(cells_all[sel], stable=True)
+        idx = torch.nonzero(sel).squeeze(1)[order]
+        train = self.pool[:, :n].index_select(1, idx).contiguous()       # sorted by cell: the swapped training_data
+        counts = np.where(can, data_size, 0)
+        off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+        point6, normal3, weight = train[0:6].contiguous(), train[6:9].contiguous(), train[9].contiguous()
+        # sdmm::initialize for cells without a mixture (volpath_sdmm.cpp:292-294)
+        fresh = np.nonzero(can & ~self.has_mixture)[0]
+        if fresh.size:
+            runs = np.split(fresh, np.nonzero(np.diff(fresh) != 1)[0] + 1)
+            for run in runs:
+                a, b = int(run[0]), int(run[-1]) + 1
+                sd = (3.0 * diag[a:b] / (self.K // 8)).astype(np.float32)
+                base = int(off[a])
+                sub_off = (off[a:b + 1] - off[a]).astype(np.uint32)
+                self.cells.initialize(point6[:, base:base + int(sub_off[-1])].contiguous(),
+                                      normal3[:, base:base + int(sub_off[-1])].contiguous(),
+                                      weight[base:base + int(sub_off[-1])].contiguous(), sub_off, sd, first_cell=a)
+            self.has_mixture[fresh] = True
+        # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305)
+        _, _, scal = self.cells.download(want_em=False)
+        iters_run = scal[:, 1].astype(np.int64)
+        self.cells.set_samples(point6, weight, off)
+        self.cells.em_step(1, with_conditioner=True)
+        twice = can & (iters_run < 4)
+        if twice.any():
+            sel2 = torch.as_tensor(twice, device=self.dev)[cells_all[idx]]
+            p2 = train[:, sel2].contiguous()
+            counts2 = np.where(twice, data_size, 0)
+            off2 = np.concatenate([[0], np.cumsum(counts2)]).astype(np.uint32)
+            self.cells.set_samples(p2[0:6].contiguous(), p2[9].contiguous(), off2)
+            self.cells.em_step(1, with_conditioner=True)
+        self.initialized[can_t] = 1
+        # data.clear() for the optimised cells; everything else stays in the pool
+        keep = ~sel
+        kept = self.pool[:, :n][:, keep]
+        self.pool_count = int(kept.shape[1])
+        self.pool[:, :self.pool_count] = kept
+        return dict(trained=int(can.sum()), leaves=t.n_leaves, fresh=int(fresh.size), train_samples=int(off[-1]))
+
+    # ---- render() ---------------------------------------------------------------------------------
+    def render(self, sample_count, train_fraction=0.25, log=None):
+        """The reference's schedule: iterations of samples_per_iteration spp; sample collection + training
+        while samplesRendered < sampleCount * train_fraction (1/4 in the reference, volpath_sdmm.cpp:416)."""
+        rendered = 0
+        while rendered < sample_count:
+            still_training = rendered < sample_count * train_fraction
+            st, new = self.render_pass(self.spi, collect=still_training)
+            info = dict(iteration=self.iteration, spp=self.spi, guided_queries=int(st.guided_queries),
+                        mis_queries=int(st.mis_queries), pool=self.pool_count, overflow=int(st.pool_overflow))
+            if still_training:
+                info.update(self.optimize(new))
+            self.stats.append(info)
+            if log:
+                log(info)
+            self.iteration += 1
+            self.total_spp += self.spi
+            rendered += self.spi
+        return self.image()
+
+    def image(self):
+        img = (self.image_sum / max(1, self.total_spp)).reshape(3, self.height, self.width)
+        return img.cpu().numpy()

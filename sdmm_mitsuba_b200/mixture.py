@@ -209,6 +209,13 @@ class SDMMCells:
         nodes = np.ascontiguousarray(nodes, dtype=TREE_NODE_DTYPE)
         check(self._L.sdmmb_set_tree(self._h, nodes.shape[0], C.c_void_p(nodes.ctypes.data)), "sdmmb_set_tree", self._h)
 
+    def copy_cells(self, src, dst):
+        """Child cells inherit the parent's complete state on a split (spatial_tree.h:187-196)."""
+        src = _np(np.asarray(src), np.int32)
+        dst = _np(np.asarray(dst), np.int32)
+        assert src.shape == dst.shape
+        check(self._L.sdmmb_copy_cells(self._h, src.shape[0], _hp(src), _hp(dst), None), "sdmmb_copy_cells", self._h)
+
     def find_cells(self, pos3):
         """STree::find for a batch of points: pos3 [3,n] -> cell slot per point (0xffffffff = none)."""
         if _is_torch(pos3):

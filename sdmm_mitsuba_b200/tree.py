@@ -33,3 +33,146 @@ def flatten(is_leaf, axis, child0, child1, aabb_min, leaf_slot=None):
     nodes["child1"][inner] = child1[inner]
     nodes["split"][inner] = aabb_min[child0[inner], axis[inner]]
     return nodes, leaf_slot
+
+
+class HostTree:
+    """Host restatement of the reference's STree bookkeeping (sdmm/include/sdmm/accelerators/spatial_tree.h):
+    node table, split_to_depth (:216-252), data-driven split_leaf_recurse (:254-292) with the split position at
+    the mean of the leaf's SpatialStats along the axis of largest variance (get_split_location, :133-167).
+    Leaves own a device cell slot; the samples themselves stay on the device (they are re-bucketed there with
+    find), so a split only needs the children's SpatialStats, which the caller supplies through `child_stats`.
+    The reference's limits (10000 nodes, uint16 indices, :96, 311-312) are lifted."""
+
+    def __init__(self, aabb_min, aabb_max, max_cells):
+        self.is_leaf = [True]
+        self.axis = [0]
+        self.children = [(0, 0)]
+        self.amin = [np.asarray(aabb_min, np.float32).copy()]
+        self.amax = [np.asarray(aabb_max, np.float32).copy()]
+        self.depth = [0]
+        self.slot = [0]
+        # SpatialStats (accelerators/spatial_stats.h): size, sum of points, sum of squared points (double)
+        self.st_size = [0]
+        self.st_sum = [np.zeros(3)]
+        self.st_sqr = [np.zeros(3)]
+        self.max_cells = int(max_cells)
+        self.free_slots = list(range(self.max_cells - 1, 0, -1))
+        self.n_leaves = 1
+
+    def size(self):
+        return len(self.is_leaf)
+
+    def leaves(self):
+        return [i for i in range(self.size()) if self.is_leaf[i]]
+
+    def _create_child(self, node, child_i, loc):
+        """create_child (:169-214): child 0 is the UPPER part (min raised), child 1 the lower part."""
+        ax = self.axis[node]
+        amin, amax = self.amin[node].copy(), self.amax[node].copy()
+        diag = np.float32(amax[ax] - amin[ax])
+        if child_i == 0:
+            amin[ax] = np.float32(amin[ax] + np.float32(loc) * diag)
+        else:
+            amax[ax] = np.float32(amax[ax] - np.float32(np.float32(1.0) - np.float32(loc)) * diag)
+        self.is_leaf.append(True)
+        self.axis.append((ax + 1) % 3)
+        self.children.append((0, 0))
+        self.amin.append(amin)
+        self.amax.append(amax)
+        self.depth.append(self.depth[node] + 1)
+        self.slot.append(-1)
+        self.st_size.append(0)
+        self.st_sum.append(np.zeros(3))
+        self.st_sqr.append(np.zeros(3))
+        return self.size() - 1
+
+    def _split(self, node, loc):
+        """Returns (child0, child1); child 0 keeps the parent's slot, child 1 takes a fresh one."""
+        if not self.free_slots:
+            return None
+        self.is_leaf[node] = False
+        c0 = self._create_child(node, 0, loc)
+        c1 = self._create_child(node, 1, loc)
+        self.children[node] = (c0, c1)
+        self.slot[c0] = self.slot[node]
+        self.slot[c1] = self.free_slots.pop()
+        self.slot[node] = -1
+        self.n_leaves += 1
+        return c0, c1
+
+    def split_to_depth(self, max_depth):
+        def rec(node, depth):
+            max_axis = 3
+            next_depth = depth + 1 if self.axis[node] == max_axis - 1 else depth
+            if not self.is_leaf[node]:
+                for c in self.children[node]:
+                    rec(c, next_depth)
+                return
+            if depth >= max_depth:
+                return
+            ch = self._split(node, 0.5)
+            if ch is None:
+                return
+            for c in ch:
+                rec(c, next_depth)
+        rec(0, 0)
+
+    def split_location(self, node):
+        """get_split_location (:133-167), in double like SpatialStats."""
+        n = float(self.st_size[node])
+        mean, sqr = self.st_sum[node], self.st_sqr[node]
+        var = (sqr - (mean / n) ** 2 * n) / (n - 1.0)
+        ax = 0
+        for i in range(3):
+            if var[i] > var[ax]:
+                ax = i
+        loc = np.float32((mean[ax] / n - float(self.amin[node][ax])) / float(self.amax[node][ax] - self.amin[node][ax]))
+        return ax, loc
+
+    def split_leaves(self, threshold, child_stats, on_split=None):
+        """split_leaf_recurse over every node (volpath_sdmm.cpp:253-259).  child_stats(parent_slot, amin, amax) ->
+        (size, sum[3], sqr[3]) of the parent's CURRENT data samples inside the child's box (create_child :204-206).
+        on_split(parent_slot, slot0, slot1, axis, child0_min, child1_max) is called right after a split so the caller
+        can re-bucket the parent's data the way create_child does (:190-203: by the sample POSITION along the split axis).
+        Returns the list of (parent_slot, child0_slot, child1_slot) splits performed, in order."""
+        done = []
+
+        def rec(node):
+            if not self.is_leaf[node] or self.st_size[node] <= threshold:
+                return
+            ax, loc = self.split_location(node)
+            if not (0.0 < loc < 1.0):
+                return
+            parent_slot = self.slot[node]
+            self.axis[node] = ax
+            ch = self._split(node, loc)
+            if ch is None:
+                return
+            if on_split is not None:
+                on_split(parent_slot, self.slot[ch[0]], self.slot[ch[1]], ax, float(self.amin[ch[0]][ax]),
+                         float(self.amax[ch[1]][ax]))
+            for c in ch:
+                self.st_size[c], self.st_sum[c], self.st_sqr[c] = child_stats(self.slot[c], self.amin[c], self.amax[c])
+            self.st_size[node] = 0
+            done.append((parent_slot, self.slot[ch[0]], self.slot[ch[1]]))
+            for c in ch:
+                rec(c)
+
+        for node in range(self.size()):
+            rec(node)
+        return done
+
+    def find(self, p):
+        node = 0
+        while not self.is_leaf[node]:
+            c0, c1 = self.children[node]
+            ax = self.axis[node]
+            node = c0 if self.amin[c0][ax] < p[ax] else c1
+        return node
+
+    def flatten(self):
+        n = self.size()
+        ch = np.array(self.children, np.int64).reshape(n, 2)
+        nodes, _ = flatten(np.array(self.is_leaf), np.array(self.axis), ch[:, 0], ch[:, 1], np.array(self.amin),
+                           leaf_slot=np.array(self.slot, np.int64))
+        return nodes

@@ -8,9 +8,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _declared():
-    src = open(os.path.join(ROOT, "include", "sdmm_b200.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(sdmmb_[a-z0-9_]+)\s*\(", src)))
+    names = set()
+    for hdr in ("sdmm_b200.h", "sdmm_b200_render.h"):
+        src = open(os.path.join(ROOT, "include", hdr)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names |= set(re.findall(r"\b(sdmmb_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_header_declares_what_capi_binds():
