@@ -228,6 +228,13 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
             from bench import cpu_query_baseline
             queries["cpu_baseline"] = cpu_query_baseline(K, n_threads=cb["cores"])   # all host threads again
 
+    render = None
+    if rank == 0 and world == 1 and not getattr(args, "no_render", False):
+        from bench_render import run_render
+        del point6, weight
+        torch.cuda.empty_cache()
+        render = run_render(torch, cpu=not args.no_cpu_baseline)
+
     if rank == 0:
         line = dict(
             metric="EM sample-component updates/s", value=value, unit="updates/s", n_gpus=world,
@@ -244,7 +251,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                                   % (32.0 * n_local / 1e6),
                         model_state="EM state carries over between steps (same work per step)"),
             clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cb,
-            queries=queries)
+            queries=queries, progressive_render=render)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -1,0 +1,70 @@
+"""bench.py's third leg: the progressive training loop on the Cornell box (BASELINE.json configs[0] / [3])
+through sdmm_mitsuba_b200.integrator, with the CPU restatement of the reference integrator (oracle/ref_render.inc,
+the reference's own sdmm code on the host cores) timed beside it on a bounded sample.  Reported, not the headline."""
+import time
+
+
+def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_count=512, cpu=True):
+    from sdmm_mitsuba_b200 import scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    quads, cam = scenes.cornell_box(width, height)
+    out = dict(workload="Cornell box (test-suite/scenes/cornell-box), %dx%d, K=%d, maxDepth=%d, %d spp per iteration, "
+                        "%d spp, training while spp < 1/4 (the reference's schedule)" % (width, height, K, max_depth, spi, sample_count))
+
+    def loop():
+        g = SDMMIntegrator(quads, cam, K=K, max_depth=max_depth, samples_per_iteration=spi, seed=11)
+        t_r = t_o = 0.0
+        rendered, q = 0, 0
+        while rendered < sample_count:
+            train = rendered < sample_count / 4
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            st, new = g.render_pass(spi, collect=train)
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            if train:
+                g.optimize(new)
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            t_r += t1 - t0
+            t_o += t2 - t1
+            q += int(st.guided_queries) + int(st.mis_queries)
+            g.iteration += 1
+            g.total_spp += spi
+            rendered += spi
+        launches = g.cells.launch_count()
+        leaves, trained = g.tree.n_leaves, int(g.initialized.sum())
+        g.close()
+        return t_r, t_o, q, launches, leaves, trained
+
+    loop()                                   # warm-up (allocations, first-launch costs)
+    t_r, t_o, q, launches, leaves, trained = loop()
+    paths = width * height * sample_count
+    out.update(paths=paths, seconds=t_r + t_o, render_seconds=t_r, optimize_seconds=t_o,
+               paths_per_s=paths / (t_r + t_o), mixture_queries=q, gpu_launches=int(launches), leaves=leaves,
+               guided_cells=trained)
+    if cpu:
+        try:
+            from oracle import refbind
+            if refbind.available():
+                w2, h2 = width // 4, height // 4
+                quads2, cam2 = scenes.cornell_box(w2, h2)
+                lo, hi, norm = scenes.scene_bounds(quads2)
+                rmin, rmax = scenes.root_aabb(lo, hi, norm)
+                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=150000)
+                t0 = time.perf_counter()
+                rendered = 0
+                it = 0
+                while rendered < sample_count:
+                    r.iteration(spi, 1000 + it, rendered < sample_count / 4)
+                    rendered += spi
+                    it += 1
+                secs = time.perf_counter() - t0
+                p2 = w2 * h2 * sample_count
+                out["cpu_baseline"] = dict(value=p2 / secs, unit="paths/s", cores=int(refbind.lib().sdmm_ref_max_threads()),
+                                           kind="reference",
+                                           sample="same loop at %dx%d (1/16 of the pixels), %.1f s; mixture, tree and EM code is the "
+                                                  "reference's own, the ray caster a restatement" % (w2, h2, secs))
+        except Exception as e:   # the CPU leg is informative only
+            out["cpu_baseline"] = dict(error=str(e))
+    return out
