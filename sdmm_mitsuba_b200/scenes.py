@@ -25,11 +25,8 @@ def _quad(p0, e1, e2, facing, refl, emis=(0, 0, 0)):
 
 def rectangle(to_world, refl, flip=False, emis=(0, 0, 0)):
     m = _mat(to_world) if isinstance(to_world, str) else np.asarray(to_world, np.float64)
-    c0, c1, c2, o = m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3]
-    facing = np.cross(c0, c1) if np.linalg.norm(c2) < 1e-12 else c2
-    if np.dot(np.cross(c0, c1), facing) < 0:
-        facing = -facing
-    facing = np.cross(c0, c1)            # Mitsuba: normal = normalize(toWorld(0,0,1)) = dpdu x dpdv direction
+    c0, c1, o = m[:3, 0], m[:3, 1], m[:3, 3]
+    facing = np.cross(c0, c1)            # Mitsuba: n = normalize(dpdu x dpdv), negated by flipNormals
     if flip:
         facing = -facing
     return [_quad(o - c0 - c1, 2 * c0, 2 * c1, facing, refl, emis)]
