@@ -76,6 +76,31 @@ def lib():
     return _lib
 
 
+PRODUCT_LIB_PATH = os.path.join(os.path.dirname(LIB_PATH), "libsdmm_ref_product.so")
+_plib = None
+
+
+def product_available():
+    return os.path.exists(PRODUCT_LIB_PATH)
+
+
+def product_lib():
+    """sdmm::product entry points; a separate shared object (see oracle/ref_product.cpp) that takes the RefCell
+    handles created by lib()."""
+    global _plib
+    if _plib is None:
+        if not product_available():
+            raise RuntimeError("oracle/_ref/libsdmm_ref_product.so missing: run `make -C oracle ref`")
+        L = C.CDLL(PRODUCT_LIB_PATH)
+        fp, up, bp = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)
+        L.sdmm_ref_product_sample_pdf.restype = C.c_double
+        L.sdmm_ref_product_sample_pdf.argtypes = [C.POINTER(C.c_void_p), C.c_long, up, fp, fp, fp, fp, C.c_int, fp,
+                                                  fp, fp, fp, up, bp, C.c_int]
+        L.sdmm_ref_product_components.argtypes = [C.c_void_p, fp, fp, C.c_int, fp, fp, C.c_int]
+        _plib = L
+    return _plib
+
+
 def _f(a):
     assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
     return a.ctypes.data_as(C.POINTER(C.c_float))
@@ -209,6 +234,34 @@ class RefCells:
         secs = L.sdmm_ref_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx), _f(pos3),
                               _f(dir3), _f(out_pdf), _b(out_valid), None, None, n_threads)
         return out_pdf, out_valid, secs
+
+    def product_sample_pdf(self, cell_idx, pos3, bsdf, u3=None, dir3=None, normal3=None, n_threads=0):
+        """sampleSurface's product branch (sdmm_proc.cpp:327-339, 375-381): bsdf [M,7] rows (pmf, mean3, c00, c10,
+        c11); u3 by role (sample + pdf) or dir3 (pdf only); normal3 re-centres BSDF component 0."""
+        L = product_lib()
+        n = pos3.shape[1]
+        bsdf = np.ascontiguousarray(bsdf, np.float32).reshape(-1, 7)
+        out_dir = np.zeros((3, n), np.float32)
+        out_pdf = np.zeros(n, np.float32)
+        out_ij = np.zeros(n, np.float32)
+        out_comp = np.zeros(n, np.uint32)
+        out_valid = np.zeros(n, np.uint8)
+        opt = lambda a: _f(a) if a is not None else None
+        secs = L.sdmm_ref_product_sample_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx), _f(pos3),
+                                             opt(u3), opt(dir3), opt(normal3), bsdf.shape[0], _f(bsdf), _f(out_dir),
+                                             _f(out_pdf), _f(out_ij), _u(out_comp), _b(out_valid), n_threads)
+        return dict(dir=out_dir, pdf=out_pdf, inv_jac=out_ij, comp=out_comp, valid=out_valid), secs
+
+    def product_components(self, cell, x, bsdf, normal=None):
+        """The product mixture at one vertex: [P,7] rows (pmf, tangent_mean2, cov00, cov10, cov11, cdf)."""
+        L = product_lib()
+        bsdf = np.ascontiguousarray(bsdf, np.float32).reshape(-1, 7)
+        out = np.zeros((self.K * bsdf.shape[0], 7), np.float32)
+        xx = np.ascontiguousarray(x, np.float32)
+        nn = np.ascontiguousarray(normal, np.float32) if normal is not None else None
+        P = L.sdmm_ref_product_components(self.handles[cell], _f(xx), _f(nn) if nn is not None else None,
+                                          bsdf.shape[0], _f(bsdf), _f(out), out.shape[0])
+        return out[:P]
 
     def conditional_weights(self, cell, x):
         """Normalised conditional pmf/cdf at one vertex (for tie analysis)."""

@@ -8,8 +8,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libsdmm_b200.so")
-SOURCES = ["capi.cu", "em_kernels.cu", "query_kernels.cu", "tree_kernels.cu", "init_kernels.cu", "render_kernels.cu", "peaks.cu"]
-HEADERS = ["kernels.h", "sdmm_math.cuh", "capi_part2.inc", "capi_part3.inc", "capi_part4.inc", "render.h", os.path.join("..", "..", "include", "sdmm_b200_render.h"), os.path.join("..", "..", "include", "sdmm_b200.h")]
+SOURCES = ["capi.cu", "em_kernels.cu", "query_kernels.cu", "tree_kernels.cu", "init_kernels.cu", "render_kernels.cu", "product_kernels.cu", "peaks.cu"]
+HEADERS = ["kernels.h", "sdmm_math.cuh", "capi_part2.inc", "capi_part3.inc", "capi_part4.inc", "capi_part5.inc", "render.h", os.path.join("..", "..", "include", "sdmm_b200_render.h"), os.path.join("..", "..", "include", "sdmm_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

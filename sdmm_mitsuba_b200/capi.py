@@ -30,7 +30,7 @@ SYMBOLS = [
     "sdmmb_sample_pdf_host", "sdmmb_pdf_host", "sdmmb_set_tree", "sdmmb_find_cells", "sdmmb_find_cells_host", "sdmmb_collect_samples",
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
-    "sdmmb_copy_cells", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
+    "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
 ]
 
 
@@ -121,6 +121,8 @@ def lib():
     L.sdmmb_pt_create.argtypes = [vp, C.POINTER(vp), C.POINTER(Quad), i, C.POINTER(Camera), C.POINTER(PtConfig)]
     L.sdmmb_pt_destroy.argtypes = [vp]
     L.sdmmb_copy_cells.argtypes = [vp, i, vp, vp, vp]
+    L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
+    L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, i, fp, vp, vp, vp]
     L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):

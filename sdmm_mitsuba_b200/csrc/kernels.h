@@ -138,6 +138,33 @@ cudaError_t launch_derived_readout(const float* joint, const float* cdf, int fir
 cudaError_t launch_conditioner_readout(const float* joint, const float* qrec, int first_cell, int n_cells,
                                        int K, float* out, cudaStream_t st);
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st);
+// counting sort of vertices by cell (query_kernels.cu); scratch: 2 * (max_cells + 1) + 9 * n + 4 words
+cudaError_t launch_bin_vertices(const uint32_t* cell_idx, size_t n, int max_cells, const float* pos3,
+                                const float* in3, uint32_t* scratch, float4** out_qin, uint32_t** out_invperm,
+                                cudaStream_t st);
+
+// product guiding (product_kernels.cu): conditional x learned-BSDF mixture, one thread per vertex
+constexpr int SDMMB_PRODUCT_MAX_BSDF = 16;
+struct ProductLaunch {
+    int K, K_user;
+    int max_cells;
+    size_t n;
+    const float* qrec;
+    const uint32_t* cell_idx;
+    const float* pos3;     // 3 planes of n
+    const float* u3;       // sample mode, or nullptr
+    const float* dir3;     // pdf-only mode, or nullptr
+    const float* normal3;  // nullable: BSDF component 0 is re-centred on it (diffuse surfaces)
+    int M;
+    const float* bsdf;     // device, [M][7]: pmf, mean3, c00, c10, c11
+    uint32_t* scratch;     // binning scratch: 2 * (max_cells + 1) + 9 * n + 4 words
+    float* out_dir3;
+    float* out_pdf;
+    float* out_inv_jac;
+    uint32_t* out_comp;
+    uint8_t* out_valid;
+};
+cudaError_t launch_product_query(const ProductLaunch& q, cudaStream_t st);
 cudaError_t measure_peaks(float* out4);
 
 }  // namespace sdmmb

@@ -499,6 +499,46 @@ __global__ void query_unpermute_kernel(QueryLaunch q, const uint32_t* __restrict
 
 }  // namespace
 
+// Counting sort of n vertices by cell into the caller-provided scratch (words):
+//   count[B] | cursor[B] | invperm[n] | pad to 16 B | qin[8 n]      (B = max_cells + 1; the caller may append more)
+// qin holds, per sorted position, (x, y, z, in0) (in1, in2, original index, cell).
+cudaError_t launch_bin_vertices(const uint32_t* cell_idx, size_t n, int max_cells, const float* pos3,
+                                const float* in3, uint32_t* scratch, float4** out_qin, uint32_t** out_invperm,
+                                cudaStream_t st) {
+    cudaError_t e;
+    const uint32_t B = (uint32_t)max_cells + 1;
+    uint32_t* count = scratch;
+    uint32_t* cursor = count + B;
+    uint32_t* invperm = cursor + B;
+    size_t off = (size_t)2 * B + n;
+    off = (off + 3) & ~(size_t)3;
+    float4* qin = reinterpret_cast<float4*>(scratch + off);
+    BinPayload pl{pos3, in3, qin, invperm};
+    if ((e = cudaMemsetAsync(count, 0, (size_t)B * 4, st)) != cudaSuccess) return e;
+    const size_t hist_smem = (size_t)2 * B * sizeof(uint32_t);
+    if (hist_smem <= 160 * 1024) {
+        static bool configured = false;
+        if (!configured) {
+            if ((e = cudaFuncSetAttribute(bin_count_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
+            if ((e = cudaFuncSetAttribute(bin_scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
+            configured = true;
+        }
+        // one chunk per CTA; few, fat CTAs keep the per-bucket global atomics rare
+        const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((n + 8191) / 8192, 148 * 2));
+        bin_count_smem_kernel<<<grid, 512, hist_smem / 2, st>>>(cell_idx, n, B, count);
+        bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
+        bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(cell_idx, n, B, cursor, pl);
+    } else {
+        const unsigned grid = (unsigned)std::min<size_t>((n + 255) / 256, 148 * 16);
+        bin_count_kernel<<<grid, 256, 0, st>>>(cell_idx, n, B, count);
+        bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
+        bin_scatter_kernel<<<grid, 256, 0, st>>>(cell_idx, n, B, cursor, pl);
+    }
+    *out_qin = qin;
+    *out_invperm = invperm;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     if (q.n == 0) return cudaSuccess;
     const bool sample = q.u3 != nullptr;
@@ -507,37 +547,9 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     float4* qout = nullptr;
     uint32_t* invperm = nullptr;
     if (!q.binned) {
-        // counting sort by cell into the caller-provided scratch (words):
-        //   count[B] | cursor[B] | invperm[n] | pad to 16 B | qin[8 n] | qout[8 n]
-        const uint32_t B = (uint32_t)q.max_cells + 1;
-        uint32_t* count = q.scratch;
-        uint32_t* cursor = count + B;
-        invperm = cursor + B;
-        size_t off = (size_t)2 * B + q.n;
-        off = (off + 3) & ~(size_t)3;
-        qin = reinterpret_cast<float4*>(q.scratch + off);
+        if ((e = launch_bin_vertices(q.cell_idx, q.n, q.max_cells, q.pos3, sample ? q.u3 : q.dir3, q.scratch, &qin,
+                                     &invperm, st)) != cudaSuccess) return e;
         qout = qin + 2 * q.n;
-        BinPayload pl{q.pos3, sample ? q.u3 : q.dir3, qin, invperm};
-        if ((e = cudaMemsetAsync(count, 0, (size_t)B * 4, st)) != cudaSuccess) return e;
-        const size_t hist_smem = (size_t)2 * B * sizeof(uint32_t);
-        if (hist_smem <= 160 * 1024) {
-            static bool configured = false;
-            if (!configured) {
-                if ((e = cudaFuncSetAttribute(bin_count_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
-                if ((e = cudaFuncSetAttribute(bin_scatter_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)) != cudaSuccess) return e;
-                configured = true;
-            }
-            // one chunk per CTA; few, fat CTAs keep the per-bucket global atomics rare
-            const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((q.n + 8191) / 8192, 148 * 2));
-            bin_count_smem_kernel<<<grid, 512, hist_smem / 2, st>>>(q.cell_idx, q.n, B, count);
-            bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
-            bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(q.cell_idx, q.n, B, cursor, pl);
-        } else {
-            const unsigned grid = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
-            bin_count_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, count);
-            bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
-            bin_scatter_kernel<<<grid, 256, 0, st>>>(q.cell_idx, q.n, B, cursor, pl);
-        }
     }
     // tile: multiple of 2 * QTHREADS; short enough that the last wave's tail is small, long enough that
     // the per-run record staging (K * 128 B) stays negligible
