@@ -37,12 +37,29 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         g.close()
         return t_r, t_o, q, launches, leaves, trained
 
+    def whole(optimize_async):
+        # the whole loop through SDMMIntegrator.render(), no synchronisation between the phases
+        g = SDMMIntegrator(quads, cam, K=K, max_depth=max_depth, samples_per_iteration=spi, seed=11,
+                           optimize_async=optimize_async)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        g.render(sample_count)
+        torch.cuda.synchronize()
+        secs = time.perf_counter() - t0
+        g.close()
+        return secs
+
     loop()                                   # warm-up (allocations, first-launch costs)
     t_r, t_o, q, launches, leaves, trained = loop()
     paths = width * height * sample_count
     out.update(paths=paths, seconds=t_r + t_o, render_seconds=t_r, optimize_seconds=t_o,
                paths_per_s=paths / (t_r + t_o), mixture_queries=q, gpu_launches=int(launches), leaves=leaves,
                guided_cells=trained)
+    whole(True)
+    out["schedules"] = dict(
+        note="whole render() call, wall clock: optimize() as volpath_sdmm.cpp:244-312 vs the optimizeAsync schedule "
+             "(:180-242: fits on a second stream, visible one pass later, one em_step per fit)",
+        synchronous_seconds=min(whole(False) for _ in range(2)), async_seconds=min(whole(True) for _ in range(2)))
     if cpu:
         try:
             from oracle import refbind

@@ -385,6 +385,7 @@ class RefRenderer:
         L.sdmm_ref_renderer_destroy.argtypes = [C.c_void_p]
         L.sdmm_ref_renderer_iteration.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.sdmm_ref_renderer_image.argtypes = [C.c_void_p, fp]
+        L.sdmm_ref_renderer_set_async.argtypes = [C.c_void_p, C.c_int]
         L.sdmm_ref_renderer_tree_size.argtypes = [C.c_void_p]
         L.sdmm_ref_renderer_tree_export.argtypes = [C.c_void_p, fp]
         L.sdmm_ref_renderer_leaf_joint.argtypes = [C.c_void_p, C.c_int, fp, C.POINTER(C.c_uint32)]
@@ -405,6 +406,10 @@ class RefRenderer:
             lib().sdmm_ref_renderer_destroy(self._h)
         except Exception:
             pass
+
+    def set_async(self, enabled=True):
+        """optimizeAsync schedule (volpath_sdmm.cpp:180-242): fits become visible one pass later."""
+        lib().sdmm_ref_renderer_set_async(self._h, 1 if enabled else 0)
 
     def iteration(self, spp, pass_seed, still_training, force_unguided=False):
         st = (C.c_double * 7)()

@@ -11,6 +11,7 @@ The render pass itself (Li, sampleSurface, sample collection) runs on the device
 (include/sdmm_b200_render.h).  Everything numeric runs in the CUDA library; torch is used here for device
 buffers and for index glue (sorting the sample pool by cell, per-cell counts and SpatialStats sums).
 Synchronous schedule (optimizeAsync = false, as scripts/run_tests.sh:29 runs the reference)."""
+import contextlib
 import ctypes as C
 
 import numpy as np
@@ -27,7 +28,7 @@ POOL_PLANES = 15
 
 class SDMMIntegrator:
     def __init__(self, quads, camera, K=16, max_depth=5, samples_per_iteration=4, saved_per_path=8, max_cells=4096,
-                 pool_capacity=8_000_000, device=0, seed=1234, split_threshold=SPLIT_THRESHOLD):
+                 pool_capacity=8_000_000, device=0, seed=1234, split_threshold=SPLIT_THRESHOLD, optimize_async=False):
         import torch
         self.torch = torch
         self.dev = torch.device("cuda", device)
@@ -36,6 +37,15 @@ class SDMMIntegrator:
         self.split_threshold = int(split_threshold)
         self.cells = SDMMCells(max_cells, K, device=device)
         self.cells.set_min_samples(1)
+        # optimizeAsync (the reference's default, volpath_sdmm.cpp:65, 180-242): a fit's records and `initialized`
+        # flags become visible to the renderer one pass later; the records are double-buffered on the device
+        self.optimize_async = bool(optimize_async)
+        self._pending = None
+        self._em_stream = None
+        self._pending_keep = None
+        if self.optimize_async:
+            self.cells.set_async_records(True)
+            self._em_stream = torch.cuda.Stream(device=self.dev)   # the fit overlaps the next render pass
         lo, hi, norm = scenes.scene_bounds(quads)
         rmin, rmax = scenes.root_aabb(lo, hi, norm)
         self.tree = HostTree(rmin, rmax, max_cells)
@@ -200,39 +210,61 @@ class SDMMIntegrator:
         counts = np.where(can, data_size, 0)
         off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
         point6, normal3, weight = train[0:6].contiguous(), train[6:9].contiguous(), train[9].contiguous()
-        # sdmm::initialize for cells without a mixture (volpath_sdmm.cpp:292-294)
-        fresh = np.nonzero(can & ~self.has_mixture)[0]
-        if fresh.size:
-            runs = np.split(fresh, np.nonzero(np.diff(fresh) != 1)[0] + 1)
-            for run in runs:
-                a, b = int(run[0]), int(run[-1]) + 1
-                sd = (3.0 * diag[a:b] / (self.K // 8)).astype(np.float32)
-                base = int(off[a])
-                sub_off = (off[a:b + 1] - off[a]).astype(np.uint32)
-                self.cells.initialize(point6[:, base:base + int(sub_off[-1])].contiguous(),
-                                      normal3[:, base:base + int(sub_off[-1])].contiguous(),
-                                      weight[base:base + int(sub_off[-1])].contiguous(), sub_off, sd, first_cell=a)
-            self.has_mixture[fresh] = True
-        # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305)
-        _, _, scal = self.cells.download(want_em=False)
-        iters_run = scal[:, 1].astype(np.int64)
-        self.cells.set_samples(point6, weight, off)
-        self.cells.em_step(1, with_conditioner=True)
-        twice = can & (iters_run < 4)
-        if twice.any():
-            sel2 = torch.as_tensor(twice, device=self.dev)[cells_all[idx]]
-            p2 = train[:, sel2].contiguous()
-            counts2 = np.where(twice, data_size, 0)
-            off2 = np.concatenate([[0], np.cumsum(counts2)]).astype(np.uint32)
-            self.cells.set_samples(p2[0:6].contiguous(), p2[9].contiguous(), off2)
+        # async schedule: the fit runs on its own stream, ordered after everything queued so far, and is joined in
+        # publish_pending() after the next pass; the training copies must outlive it
+        if self.optimize_async:
+            self._em_stream.wait_stream(torch.cuda.current_stream(self.dev))
+            self._pending_keep = (train, point6, normal3, weight)
+        with (torch.cuda.stream(self._em_stream) if self.optimize_async else contextlib.nullcontext()):
+            # sdmm::initialize for cells without a mixture (volpath_sdmm.cpp:292-294)
+            fresh = np.nonzero(can & ~self.has_mixture)[0]
+            if fresh.size:
+                runs = np.split(fresh, np.nonzero(np.diff(fresh) != 1)[0] + 1)
+                for run in runs:
+                    a, b = int(run[0]), int(run[-1]) + 1
+                    # optimize_async_run seeds from 0.1 x the leaf diagonal (volpath_sdmm.cpp:215), optimize from all of it
+                    sd = (3.0 * (0.1 if self.optimize_async else 1.0) * diag[a:b] / (self.K // 8)).astype(np.float32)
+                    base = int(off[a])
+                    sub_off = (off[a:b + 1] - off[a]).astype(np.uint32)
+                    self.cells.initialize(point6[:, base:base + int(sub_off[-1])].contiguous(),
+                                          normal3[:, base:base + int(sub_off[-1])].contiguous(),
+                                          weight[base:base + int(sub_off[-1])].contiguous(), sub_off, sd, first_cell=a)
+                self.has_mixture[fresh] = True
+            # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305); optimize_async_run: always 1 (:217)
+            if self.optimize_async:
+                iters_run = np.full(self.cells.max_cells, 4, np.int64)       # one em_step per fit, no read-back
+            else:
+                _, _, scal = self.cells.download(want_em=False)
+                iters_run = scal[:, 1].astype(np.int64)
+            self.cells.set_samples(point6, weight, off)
             self.cells.em_step(1, with_conditioner=True)
-        self.initialized[can_t] = 1
+            twice = can & (iters_run < 4)
+            if twice.any():
+                sel2 = torch.as_tensor(twice, device=self.dev)[cells_all[idx]]
+                p2 = train[:, sel2].contiguous()
+                counts2 = np.where(twice, data_size, 0)
+                off2 = np.concatenate([[0], np.cumsum(counts2)]).astype(np.uint32)
+                self.cells.set_samples(p2[0:6].contiguous(), p2[9].contiguous(), off2)
+                self.cells.em_step(1, with_conditioner=True)
+        if self.optimize_async:
+            self._pending = can_t          # published by publish_pending() after the next pass
+        else:
+            self.initialized[can_t] = 1
         # data.clear() for the optimised cells; everything else stays in the pool
         keep = ~sel
         kept = self.pool[:, :n][:, keep]
         self.pool_count = int(kept.shape[1])
         self.pool[:, :self.pool_count] = kept
         return dict(trained=int(can.sum()), leaves=t.n_leaves, fresh=int(fresh.size), train_samples=int(off[-1]))
+
+    def publish_pending(self):
+        """optimize_async_wait_and_update (volpath_sdmm.cpp:227-242): make the last fit visible to the renderer."""
+        if self._pending is not None:
+            self.torch.cuda.current_stream(self.dev).wait_stream(self._em_stream)
+            self._pending_keep = None
+            self.cells.publish_records()
+            self.initialized[self._pending] = 1
+            self._pending = None
 
     # ---- render() ---------------------------------------------------------------------------------
     def render(self, sample_count, train_fraction=0.25, log=None):
@@ -242,6 +274,7 @@ class SDMMIntegrator:
         while rendered < sample_count:
             still_training = rendered < sample_count * train_fraction
             st, new = self.render_pass(self.spi, collect=still_training)
+            self.publish_pending()                                    # volpath_sdmm.cpp:446-448
             info = dict(iteration=self.iteration, spp=self.spi, guided_queries=int(st.guided_queries),
                         mis_queries=int(st.mis_queries), pool=self.pool_count, overflow=int(st.pool_overflow))
             if still_training:

@@ -129,6 +129,61 @@ def test_progressive_loop_matches_cpu_restatement(oracle_ref):
 
 
 @pytest.mark.gpu
+def test_async_schedule_matches_cpu_restatement(oracle_ref):
+    """optimizeAsync, the reference's default schedule (volpath_sdmm.cpp:65, 180-242): fits become visible one pass
+    later (double-buffered records + deferred `initialized` flags), one em_step per fit, seeds spaced from 0.1 x the
+    leaf diagonal."""
+    from sdmm_mitsuba_b200 import scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    W, H, K, MD, SPI = 320, 180, 16, 5, 64
+    quads, cam = scenes.cornell_box(W, H)
+    lo, hi, norm = scenes.scene_bounds(quads)
+    rmin, rmax = scenes.root_aabb(lo, hi, norm)
+    g = SDMMIntegrator(quads, cam, K=K, max_depth=MD, samples_per_iteration=SPI, seed=11, pool_capacity=4_000_000,
+                       optimize_async=True)
+    r = oracle_ref.RefRenderer(quads, cam, lo, norm, rmin, rmax, K=K, max_depth=MD, capacity=150000)
+    r.set_async(True)
+    infos = []
+    for it in range(4):
+        seed = (g.seed * 0x9E3779B97F4A7C15 + g.iteration) & 0xFFFFFFFFFFFFFFFF
+        st, new = g.render_pass(SPI, collect=True)
+        g.publish_pending()
+        n_init = int(g.initialized.sum())
+        info = g.optimize(new)
+        g.iteration += 1
+        g.total_spp += SPI
+        rs = r.iteration(SPI, seed, True)
+        infos.append((info, rs, int(st.guided_queries), n_init))
+        ig, ir = g.image(), r.image()
+        assert abs(ig.mean() - ir.mean()) <= 2e-3 * ir.mean(), (it, ig.mean(), ir.mean())
+        if it < 3:
+            assert np.abs(ig - ir).mean() <= 1e-5 * ir.mean(), (it, np.abs(ig - ir).mean())
+    # the lag: the fit started after pass 1 is first used in pass 3 (pass 2 still ran unguided)
+    assert infos[1][0]["trained"] == infos[1][1]["trained"] > 10
+    assert infos[1][3] == 0 and infos[2][2] == 0 and infos[2][3] > 10 and infos[3][2] > 100000
+    assert abs(infos[3][2] - infos[3][1]["guided_queries"]) <= 1e-3 * infos[3][2]
+    for it, (a, b, _, _) in enumerate(infos):
+        assert a["trained"] == b["trained"], (it, a, b)
+        # passes 0-2 are unguided: identical paths, identical samples; a guided pass may differ in a few paths
+        tol = 0 if it < 3 else 2e-3 * b["train_samples"]
+        assert abs(a.get("train_samples", 0) - b["train_samples"]) <= tol, (it, a, b)
+    nr, t = r.nodes(), g.tree
+    assert t.size() == nr.shape[0]
+    assert all(bool(nr[i, 0] > 0) == t.is_leaf[i] for i in range(t.size()))
+    j_gpu, _, s_gpu = g.cells.download(want_em=False)
+    n_mix = n_ok = 0
+    for node in t.leaves():
+        jr, sr = r.leaf_joint(node)
+        if jr is None:
+            continue
+        n_mix += 1
+        e = joint_param_errs(j_gpu[t.slot[node]][None], jr[None])
+        assert int(s_gpu[t.slot[node], 1]) == int(sr[1])
+        n_ok += all(v <= PARAM_RTOL for v in e.values())
+    assert n_mix > 10 and n_ok >= 0.9 * n_mix, (n_mix, n_ok)
+
+
+@pytest.mark.gpu
 def test_guiding_is_unbiased_and_reduces_variance():
     """MIS-combined guided sampling must converge to the same image as BSDF sampling (sdmm_proc.cpp:383-393,
     587-589) and, on this scene (tiny light, no next-event estimation), with a much smaller error per sample."""
