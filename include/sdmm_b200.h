@@ -191,20 +191,25 @@ int sdmmb_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const f
  * h_bsdf: n_bsdf x 7 floats (pmf, mean x y z, cov00, cov10, cov11) -- the BSDF::DMM of
  * mitsuba/include/mitsuba/render/bsdf.h:301-304 in world space; components with pmf == 0 are skipped as
  * the reference does.  d_normal3 (nullable, 3 planes of n): component 0 is re-centred on the shading normal
- * (the diffuse branch, sdmm_proc.cpp:335-339).  The glossy branch (rotate_to_wo + shading frame, :340-355)
- * changes the BSDF mixture per vertex and is not covered.
+ * (the diffuse branch, sdmm_proc.cpp:335-339).  d_frame9 + d_wi3 (both or neither; 9 planes: the shading
+ * frame's to-world matrix [s t n] row-major; 3 planes: the incident direction in that frame): the glossy
+ * branch (:340-355) -- the first packet of the BSDF mixture (components 0..7), given in the local frame, is
+ * rotated about the local z axis by -atan2(wi.y, wi.x) (DirectionalTangentSpace::rotate_to_wo,
+ * sdmm/spaces/directional.h:202-218) and taken to world space; it takes precedence over d_normal3.
  * out_comp is the index in the product mixture: (k / 8 * n_nonzero_bsdf + m) * 8 + k % 8 for conditional
  * component k and the m-th non-zero BSDF component.  out_valid = 0: invalid conditional or product
  * (prepare_vectorized failed); all outputs zero.  n_bsdf <= 16; the context's K must be a multiple of 8.
  * Synchronous on `stream`. */
 int sdmmb_sample_pdf_product(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
-                             const float* d_u3, const float* d_normal3, int n_bsdf, const float* h_bsdf,
-                             float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
-                             uint32_t* d_out_comp, uint8_t* d_out_valid, void* stream);
+                             const float* d_u3, const float* d_normal3, const float* d_frame9,
+                             const float* d_wi3, int n_bsdf, const float* h_bsdf, float* d_out_dir3,
+                             float* d_out_pdf, float* d_out_inv_jac, uint32_t* d_out_comp,
+                             uint8_t* d_out_valid, void* stream);
 /* pdfSurface with the product mixture for a caller-supplied direction (sdmm_proc.cpp:476-487). */
 int sdmmb_pdf_product(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
-                      const float* d_dir3, const float* d_normal3, int n_bsdf, const float* h_bsdf,
-                      float* d_out_pdf, uint8_t* d_out_valid, void* stream);
+                      const float* d_dir3, const float* d_normal3, const float* d_frame9,
+                      const float* d_wi3, int n_bsdf, const float* h_bsdf, float* d_out_pdf,
+                      uint8_t* d_out_valid, void* stream);
 
 /* ---- spatial cell structure on the device ------------------------------------
  * The STree (sdmm/accelerators/spatial_tree.h:83-349) is built and split on the host by the reference's

@@ -94,7 +94,7 @@ def product_lib():
         L = C.CDLL(PRODUCT_LIB_PATH)
         fp, up, bp = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)
         L.sdmm_ref_product_sample_pdf.restype = C.c_double
-        L.sdmm_ref_product_sample_pdf.argtypes = [C.POINTER(C.c_void_p), C.c_long, up, fp, fp, fp, fp, C.c_int, fp,
+        L.sdmm_ref_product_sample_pdf.argtypes = [C.POINTER(C.c_void_p), C.c_long, up, fp, fp, fp, fp, fp, fp, C.c_int, fp,
                                                   fp, fp, fp, up, bp, C.c_int]
         L.sdmm_ref_product_components.argtypes = [C.c_void_p, fp, fp, C.c_int, fp, fp, C.c_int]
         _plib = L
@@ -235,9 +235,11 @@ class RefCells:
                               _f(dir3), _f(out_pdf), _b(out_valid), None, None, n_threads)
         return out_pdf, out_valid, secs
 
-    def product_sample_pdf(self, cell_idx, pos3, bsdf, u3=None, dir3=None, normal3=None, n_threads=0):
+    def product_sample_pdf(self, cell_idx, pos3, bsdf, u3=None, dir3=None, normal3=None, frame9=None, wi3=None,
+                           n_threads=0):
         """sampleSurface's product branch (sdmm_proc.cpp:327-339, 375-381): bsdf [M,7] rows (pmf, mean3, c00, c10,
-        c11); u3 by role (sample + pdf) or dir3 (pdf only); normal3 re-centres BSDF component 0."""
+        c11); u3 by role (sample + pdf) or dir3 (pdf only); normal3 re-centres BSDF component 0 (diffuse branch);
+        frame9 + wi3: the glossy branch (sdmm_proc.cpp:340-355)."""
         L = product_lib()
         n = pos3.shape[1]
         bsdf = np.ascontiguousarray(bsdf, np.float32).reshape(-1, 7)
@@ -248,7 +250,8 @@ class RefCells:
         out_valid = np.zeros(n, np.uint8)
         opt = lambda a: _f(a) if a is not None else None
         secs = L.sdmm_ref_product_sample_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx), _f(pos3),
-                                             opt(u3), opt(dir3), opt(normal3), bsdf.shape[0], _f(bsdf), _f(out_dir),
+                                             opt(u3), opt(dir3), opt(normal3), opt(frame9), opt(wi3), bsdf.shape[0],
+                                             _f(bsdf), _f(out_dir),
                                              _f(out_pdf), _f(out_ij), _u(out_comp), _b(out_valid), n_threads)
         return dict(dir=out_dir, pdf=out_pdf, inv_jac=out_ij, comp=out_comp, valid=out_valid), secs
 

@@ -121,8 +121,8 @@ def lib():
     L.sdmmb_pt_create.argtypes = [vp, C.POINTER(vp), C.POINTER(Quad), i, C.POINTER(Camera), C.POINTER(PtConfig)]
     L.sdmmb_pt_destroy.argtypes = [vp]
     L.sdmmb_copy_cells.argtypes = [vp, i, vp, vp, vp]
-    L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
-    L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, i, fp, vp, vp, vp]
+    L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
+    L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp]
     L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):

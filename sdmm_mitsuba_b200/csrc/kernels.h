@@ -155,6 +155,8 @@ struct ProductLaunch {
     const float* u3;       // sample mode, or nullptr
     const float* dir3;     // pdf-only mode, or nullptr
     const float* normal3;  // nullable: BSDF component 0 is re-centred on it (diffuse surfaces)
+    const float* frame9;   // nullable, 9 planes of n: shading frame to-world matrix row-major (glossy surfaces)
+    const float* wi3;      // nullable, 3 planes of n: incident direction in the local shading frame
     int M;
     const float* bsdf;     // device, [M][7]: pmf, mean3, c00, c10, c11
     uint32_t* scratch;     // binning scratch: 2 * (max_cells + 1) + 9 * n + 4 words

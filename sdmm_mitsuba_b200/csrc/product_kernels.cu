@@ -149,6 +149,22 @@ __device__ __forceinline__ void make_bsdf(float w, const float mean_in[3], float
     b.c00 = c00; b.c10 = c10; b.c11 = c11;
 }
 
+// glossy surfaces: the BSDF mixture lives in the local shading frame relative to the incident direction; its first
+// packet (components 0..7) is rotated about the local z axis by -phi(wi) and taken to world space through the
+// shading frame: mean, s, t -> W R^T (mean, s, t)            (rotate_to_wo + to_world_space, sdmm_proc.cpp:340-355,
+// R: spaces/directional.h:202-218)
+__device__ __forceinline__ void xform_bsdf(const float T[9], BsdfM& b) {
+    float m[3], s[3], t[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        m[r] = T[3 * r] * b.mean[0] + T[3 * r + 1] * b.mean[1] + T[3 * r + 2] * b.mean[2];
+        s[r] = T[3 * r] * b.s[0] + T[3 * r + 1] * b.s[1] + T[3 * r + 2] * b.s[2];
+        t[r] = T[3 * r] * b.t[0] + T[3 * r + 1] * b.t[1] + T[3 * r + 2] * b.t[2];
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) { b.mean[r] = m[r]; b.s[r] = s[r]; b.t[r] = t[r]; }
+}
+
 constexpr int PROD_THREADS = 128;
 
 // One thread per vertex.  Passes: (1) conditional total, (2) product total + PSD mask, (3) component select and
@@ -179,10 +195,32 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
 
     // diffuse surfaces: component 0 is re-centred on the shading normal       (sdmm_proc.cpp:335-339)
     BsdfM b0 = s_b[0];
-    if (q.normal3 != nullptr) {
+    if (q.normal3 != nullptr && !(q.frame9 != nullptr && q.wi3 != nullptr)) {
         const float nn[3] = {q.normal3[i], q.normal3[n + i], q.normal3[2 * n + i]};
         make_bsdf(b0.w, nn, b0.c00, b0.c10, b0.c11, b0);
     }
+
+    // glossy surfaces: T = W R^T from the shading frame (columns s, t, n) and the local incident direction
+    const bool glossy = (q.frame9 != nullptr) && (q.wi3 != nullptr);
+    float T[9];
+    if (glossy) {
+        const float neg_phi = -atan2f(q.wi3[n + i], q.wi3[i]);
+        float sn, cs;
+        sincosf(neg_phi, &sn, &cs);
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const float w0 = q.frame9[(3 * r) * n + i], w1 = q.frame9[(3 * r + 1) * n + i], w2 = q.frame9[(3 * r + 2) * n + i];
+            // R^T = [[c, s, 0], [-s, c, 0], [0, 0, 1]]
+            T[3 * r] = w0 * cs - w1 * sn;
+            T[3 * r + 1] = w0 * sn + w1 * cs;
+            T[3 * r + 2] = w2;
+        }
+    }
+    auto fetch = [&](int m) -> BsdfM {
+        BsdfM b = (m == 0) ? b0 : s_b[m];
+        if (glossy && m < 8) xform_bsdf(T, b);
+        return b;
+    };
 
     // ---- pass 1: the conditional's normalisation                               R: categorical.h:97-101
     float total1 = 0.f;
@@ -199,7 +237,7 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
     bool all_psd = true, first = true;
     for (int kp = 0; kp < K; kp += 8)
         for (int m = 0; m < M; ++m) {
-            const BsdfM& b = (m == 0) ? b0 : s_b[m];
+            const BsdfM b = fetch(m);
             if (b.w == 0.f) continue;
             for (int k = kp; k < kp + 8; ++k) {
                 load_cond(rec + k * QREC_FLOATS, x, y, z, c);
@@ -223,7 +261,7 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
             uint32_t sel_i = 0, best_i = 0, idx = 0;
             for (int kp = 0; kp < K && !found; kp += 8)
                 for (int m = 0; m < M && !found; ++m) {
-                    const BsdfM& b = (m == 0) ? b0 : s_b[m];
+                    const BsdfM b = fetch(m);
                     if (b.w == 0.f) continue;
                     for (int k = kp; k < kp + 8; ++k, ++idx) {
                         load_cond(rec + k * QREC_FLOATS, x, y, z, c);
@@ -268,7 +306,7 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
         float pdf = 0.f;
         for (int kp = 0; kp < K; kp += 8)
             for (int m = 0; m < M; ++m) {
-                const BsdfM& b = (m == 0) ? b0 : s_b[m];
+                const BsdfM b = fetch(m);
                 if (b.w == 0.f) continue;
                 for (int k = kp; k < kp + 8; ++k) {
                     load_cond(rec + k * QREC_FLOATS, x, y, z, c);

@@ -153,7 +153,7 @@ __global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, P
 // ------------------------------------------------------------------------------------------------
 // one bounce of every live path
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
+__global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
                                                         int first, size_t nA, size_t nB) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
@@ -354,7 +354,7 @@ __device__ void pool_push(const PtLists& L, const PtFrame& F, const float* vp, s
 }
 
 // end of every path: film accumulation + the sample collection of Li's tail (R: 862-965)
-__global__ void pt_finish_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F) {
+__global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n) return;
     const PtScene& sc = *scp;

@@ -306,10 +306,11 @@ class SDMMCells:
                                      1 if binned else 0, None), "sdmmb_pdf_host", self._h)
         return out_pdf, out_valid
 
-    def sample_pdf_product(self, cell_idx, pos3, u3, bsdf, normal3=None, dir3=None):
+    def sample_pdf_product(self, cell_idx, pos3, u3, bsdf, normal3=None, dir3=None, frame9=None, wi3=None):
         """Product guiding per vertex (sdmm_proc.cpp:327-339, 375-381; sdmm_product.h:62-203): conditional x
         learned-BSDF mixture.  `bsdf`: [M][7] rows (pmf, mean3, cov00, cov10, cov11) in world space; `normal3`
-        re-centres component 0 on the shading normal (diffuse surfaces).  With `dir3` instead of `u3` only the
+        re-centres component 0 on the shading normal (diffuse surfaces); `frame9` [9,n] (shading frame to-world
+        matrix, row-major) + `wi3` [3,n] (local incident direction) select the glossy branch.  With `dir3` instead of `u3` only the
         pdf at the given directions is evaluated.  Inputs: host arrays or torch device tensors."""
         import torch
         dev = torch.device("cuda", self.device)
@@ -325,6 +326,7 @@ class SDMMCells:
         else:
             cell_t = torch.from_numpy(np.ascontiguousarray(cell_idx, np.uint32).view(np.int32)).to(dev)
         pos_t, u_t, n_t, d_t = dv(pos3, np.float32), dv(u3, np.float32), dv(normal3, np.float32), dv(dir3, np.float32)
+        f_t, w_t = dv(frame9, np.float32), dv(wi3, np.float32)
         bsdf = np.ascontiguousarray(bsdf, np.float32).reshape(-1, 7)
         n = pos_t.shape[1]
         ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
@@ -335,11 +337,12 @@ class SDMMCells:
                        inv_jac=torch.zeros(n, dtype=torch.float32, device=dev),
                        comp=torch.zeros(n, dtype=torch.int32, device=dev))
             check(self._L.sdmmb_sample_pdf_product(self._h, n, ptr(cell_t), ptr(pos_t), ptr(u_t), ptr(n_t),
-                                                   bsdf.shape[0], _hp(bsdf), ptr(out["dir"]), ptr(out["pdf"]),
+                                                   ptr(f_t), ptr(w_t), bsdf.shape[0], _hp(bsdf), ptr(out["dir"]), ptr(out["pdf"]),
                                                    ptr(out["inv_jac"]), ptr(out["comp"]), ptr(out["valid"]),
                                                    _stream(self.device)), "sdmmb_sample_pdf_product", self._h)
         else:
-            check(self._L.sdmmb_pdf_product(self._h, n, ptr(cell_t), ptr(pos_t), ptr(d_t), ptr(n_t), bsdf.shape[0],
+            check(self._L.sdmmb_pdf_product(self._h, n, ptr(cell_t), ptr(pos_t), ptr(d_t), ptr(n_t), ptr(f_t), ptr(w_t),
+                                            bsdf.shape[0],
                                             _hp(bsdf), ptr(out["pdf"]), ptr(out["valid"]), _stream(self.device)),
                   "sdmmb_pdf_product", self._h)
         if not as_torch:

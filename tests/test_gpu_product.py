@@ -98,6 +98,47 @@ def test_product_components_match_reference():
     assert np.quantile(rel, 0.99) < PDF_RTOL and rel.max() < PDF_RTOL_MAX and np.median(rel) < 1e-4, np.quantile(rel, [0.5, 0.99, 1.0])
 
 
+def _shading_frames(n, seed):
+    """Random orthonormal shading frames (to-world matrix [s t n], row-major planes) and local incident directions."""
+    rng = np.random.default_rng(seed)
+    nn = rng.normal(size=(n, 3))
+    nn /= np.linalg.norm(nn, axis=1, keepdims=True)
+    a = rng.normal(size=(n, 3))
+    ss = a - (a * nn).sum(axis=1, keepdims=True) * nn
+    ss /= np.linalg.norm(ss, axis=1, keepdims=True)
+    tt = np.cross(nn, ss)
+    W = np.stack([ss, tt, nn], axis=2)                      # [n, row, col]: columns s, t, n
+    frame9 = np.ascontiguousarray(W.reshape(n, 9).T.astype(np.float32))
+    wi = rng.normal(size=(n, 3))
+    wi[:, 2] = np.abs(wi[:, 2]) + 0.1
+    wi /= np.linalg.norm(wi, axis=1, keepdims=True)
+    return frame9, np.ascontiguousarray(wi.T.astype(np.float32))
+
+
+@pytest.mark.parametrize("K", [16, 64])
+def test_product_glossy_branch_parity(K):
+    """sdmm_proc.cpp:340-355: the BSDF mixture is given in the local shading frame; per vertex it is rotated to the
+    incident direction (rotate_to_wo) and taken to world space before the product."""
+    C, n = 4, 6000
+    cells, ref, cell, pos3, u3, _ = _setup(C, K, n, seed=80 + K)
+    frame9, wi3 = _shading_frames(n, seed=K)
+    bsdf = _bsdf()
+    g = cells.sample_pdf_product(cell, pos3, u3, bsdf, frame9=frame9, wi3=wi3)
+    r, _ = ref.product_sample_pdf(cell, pos3, bsdf, u3=u3, frame9=frame9, wi3=wi3)
+    np.testing.assert_array_equal(g["valid"], r["valid"])
+    v = r["valid"].astype(bool)
+    same = v & (g["comp"] == r["comp"])
+    assert v.sum() > 0.5 * n and same.sum() >= 0.998 * v.sum(), (v.sum(), same.sum())
+    ang = np.arccos(np.clip((g["dir"][:, same] * r["dir"][:, same]).sum(axis=0), -1, 1))
+    assert np.quantile(ang, 0.999) < 2e-3 and ang.max() < 2e-2, np.quantile(ang, [0.5, 0.999, 1.0])
+    big = same & (r["pdf"] > 1e-6)
+    rel = np.abs(g["pdf"][big] - r["pdf"][big]) / r["pdf"][big]
+    assert rel.max() < PDF_RTOL_MAX and np.quantile(rel, 0.99) < PDF_RTOL and np.median(rel) < 1e-4, np.quantile(rel, [0.5, 0.99, 1.0])
+    # the transform matters: without it the result is a different distribution
+    plain = cells.sample_pdf_product(cell, pos3, u3, bsdf)
+    assert np.abs(plain["pdf"][big] - g["pdf"][big]).max() > 0.1
+
+
 def test_product_samples_follow_the_product_pdf():
     """Size-independent self-consistency: the fraction of the product's own samples falling in a region equals
     the integral of the product pdf over that region (uniform quadrature through the pdf-only entry point), and
@@ -138,6 +179,8 @@ def test_product_argument_errors():
         cells.sample_pdf_product(cell, pos3, u3, bad)
     with pytest.raises(capi.SdmmError):
         cells.sample_pdf_product(cell, pos3, u3, np.zeros((17, 7), np.float32) + 1)
+    with pytest.raises(capi.SdmmError):   # frame without wi
+        cells.sample_pdf_product(cell, pos3, u3, _bsdf(), frame9=np.zeros((9, cell.size), np.float32))
     # cells outside the context come back invalid, not out-of-bounds reads
     far = cell.copy()
     far[::2] = 1000
