@@ -44,6 +44,7 @@ struct ProdC {      // one prepared product component
     float w;        // unnormalised weight
     float tm0, tm1;
     float L00, L10, L11;
+    float r0, r1;   // 1 / L00, 1 / L11
     float inv_det;
     bool psd;
 };
@@ -66,7 +67,10 @@ __device__ __forceinline__ void load_cond(const float* __restrict__ rec, float x
     c.c11 = L11 * L11 + L10 * L10 - 1e-5f;
 }
 
-// R: sdmm_product.h:110-199 for one (first, second) pair, then prepare_cov of the result
+// R: sdmm_product.h:110-199 for one (first, second) pair, then prepare_cov of the result.
+// Every 1/sqrt(x) pair of the reference (Cholesky pivot, then division by it) is one rsqrt here and the divisions
+// become multiplications by it: the kernel is issue-bound on exactly these chains (ncu: 34 % XU pipe, 69 % issue
+// slots busy at 25 % occupancy), and 2 ulp on a pivot is far below the conditioning of the weights.
 __device__ __forceinline__ ProdC product_component(const CondK& c, float pmf1, const BsdfM& b) {
     ProdC o;
     // first_ts.to_jacobian(second mean)                                  R: offset_directional.h:126-170
@@ -75,11 +79,11 @@ __device__ __forceinline__ ProdC product_component(const CondK& c, float pmf1, c
     const float lz = c.R[6] * b.mean[0] + c.R[7] * b.mean[1] + c.R[8] * b.mean[2];
     const float angle = acosf(fminf(1.f, fmaxf(-1.f, lz)));
     const float sin2 = 1.f - lz * lz;
-    const float sn = sqrtf(fmaxf(sin2, 0.f));
-    const bool small = (sn < 1e-2f) || (lz < -0.99f);
-    const float rcp = small ? 1.f : angle / sn;
+    const bool small = (sin2 < 1e-4f) || (lz < -0.99f);     // sin < 1e-2
+    const float rsin = rsqrtf(small ? 1.f : sin2);
+    const float rcp = small ? 1.f : angle * rsin;
     const float inv_jac = (lz <= -0.99f) ? 0.f : rcp;
-    const float temp = (lz * rcp - 1.f) * (small ? 0.f : 1.f / sin2);
+    const float temp = small ? 0.f : (lz * rcp - 1.f) * (rsin * rsin);
     const float jl02 = lx * temp, jl12 = ly * temp;
     float Jto[6];   // (Jl * to): 2x3
 #pragma unroll
@@ -100,10 +104,11 @@ __device__ __forceinline__ ProdC product_component(const CondK& c, float pmf1, c
     const float s10 = a10 * J00 + a11 * J01, s11 = a10 * J10 + a11 * J11;
     // cov_sum = first + second; Cholesky with the +1e-5 pivots; inverse
     const float q00 = c.c00 + s00, q10 = c.c10 + s10, q11 = c.c11 + s11;
-    const float L00 = sqrtf(q00 + 1e-5f);
-    const float L10 = q10 / L00;
-    const float L11 = sqrtf(q11 - L10 * L10 + 1e-5f);
-    const float i00 = 1.f / L00, i11 = 1.f / L11;
+    const float x0 = q00 + 1e-5f;
+    const float i00 = rsqrtf(x0);                  // 1 / L00
+    const float L10 = q10 * i00;
+    const float x1 = q11 - L10 * L10 + 1e-5f;
+    const float i11 = rsqrtf(x1);                  // 1 / L11
     const float i10 = -L10 * i00 * i11;
     // premultiplied covariances (inv_cov_sum_sqrt * cov), 2x2 each; first is symmetric
     const float f00 = i00 * c.c00, f01 = i00 * c.c10;
@@ -119,22 +124,22 @@ __device__ __forceinline__ ProdC product_component(const CondK& c, float pmf1, c
     o.tm0 = c.tm0 + (f00 * p0 + f10 * p1);                                 // R: sdmm_product.h:57-58
     o.tm1 = c.tm1 + (f01 * p0 + f11 * p1);
     // weight                                                               R: sdmm_product.h:180-198
-    const float cov_det = L00 * L11;
-    const float st0 = m0 / L00, st1 = (m1 - L10 * st0) / L11;
+    const float st0 = p0, st1 = (m1 - L10 * st0) * i11;                    // solve(L, second_mean)
     const float sq = st0 * st0 + st1 * st1;
-    const float wgt = pmf1 * b.w * (1.f / cov_det) * inv_jac * kInv2Pi * expf(-0.5f * sq);
-    o.w = (cov_det == 0.f) ? 0.f : wgt;
+    const float wgt = pmf1 * b.w * (i00 * i11) * inv_jac * kInv2Pi * expf(-0.5f * sq);
+    o.w = (x0 == 0.f || x1 == 0.f) ? 0.f : wgt;                            // cov_det == 0
     // prepare_cov of the product component                                 R: distributions/sdmm.h:186-197
     const float v0 = n00 + 1e-5f;
-    o.L00 = sqrtf(v0);
-    o.L10 = n10 / o.L00;
+    o.r0 = rsqrtf(v0);
+    o.L00 = v0 * o.r0;
+    o.L10 = n10 * o.r0;
     const float v1 = n11 - o.L10 * o.L10 + 1e-5f;
-    o.L11 = sqrtf(v1);
+    o.r1 = rsqrtf(v1);
+    o.L11 = v1 * o.r1;
     o.psd = (v0 > 0.f) && (v1 > 0.f);
-    o.inv_det = 1.f / (o.L00 * o.L11);
+    o.inv_det = o.r0 * o.r1;
     return o;
 }
-
 
 // world-space BSDF component from (pmf, mean, cov): frame from the normalised mean (DirectionalTangentSpace::set_mean,
 // R: spaces/directional.h:197-200)
@@ -166,12 +171,14 @@ __device__ __forceinline__ void xform_bsdf(const float T[9], BsdfM& b) {
 }
 
 constexpr int PROD_THREADS = 128;
+constexpr int PROD_MAX_GROUPS = 48;   // (K / 8) * non-zero BSDF components whose running sums fit in shared memory
 
 // One thread per vertex.  Passes: (1) conditional total, (2) product total + PSD mask, (3) component select and
 // sample, (4) product pdf at omega.  Every pass recomputes its components from the conditioner records.
 template <bool SAMPLE>
-__global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaunch q, const float4* __restrict__ qin) {
+__global__ void __launch_bounds__(PROD_THREADS, 6) product_query_kernel(ProductLaunch q, const float4* __restrict__ qin) {
     __shared__ BsdfM s_b[SDMMB_PRODUCT_MAX_BSDF];
+    __shared__ float s_pref[SAMPLE ? PROD_MAX_GROUPS * PROD_THREADS : 1];   // running sum at the end of each group
     if ((int)threadIdx.x < q.M) {
         const float* src = q.bsdf + threadIdx.x * 7;   // pmf, mean3, c00, c10, c11
         make_bsdf(src[0], src + 1, src[4], src[5], src[6], s_b[threadIdx.x]);
@@ -232,21 +239,33 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
     valid = valid && (total1 > 1e-20f);
     const float inv1 = 1.f / total1;
 
-    // ---- pass 2: product total (sequential, in the reference's packet order) and the PSD mask
+    // ---- pass 2: product total (sequential, in the reference's packet order) and the PSD mask.  A "group" is one
+    // (packet of 8 conditional components) x (one non-zero BSDF component); the running sum at the end of every
+    // group is kept so that pass 3 only has to redo the group the CDF crosses u0 in.
+    int M_nz = 0;
+    for (int m = 0; m < M; ++m) M_nz += (s_b[m].w != 0.f) ? 1 : 0;
+    const int G = (K / 8) * M_nz;
+    const bool use_pref = SAMPLE && G <= PROD_MAX_GROUPS;
+    float* pref = s_pref + threadIdx.x;
     float total = 0.f;
     bool all_psd = true, first = true;
-    for (int kp = 0; kp < K; kp += 8)
-        for (int m = 0; m < M; ++m) {
-            const BsdfM b = fetch(m);
-            if (b.w == 0.f) continue;
-            for (int k = kp; k < kp + 8; ++k) {
-                load_cond(rec + k * QREC_FLOATS, x, y, z, c);
-                const ProdC pc = product_component(c, c.w * inv1, b);
-                total = first ? pc.w : total + pc.w;
-                first = false;
-                all_psd = all_psd && pc.psd;
+    {
+        int gi = 0;
+        for (int kp = 0; kp < K; kp += 8)
+            for (int m = 0; m < M; ++m) {
+                if (s_b[m].w == 0.f) continue;
+                const BsdfM b = fetch(m);
+                for (int k = kp; k < kp + 8; ++k) {
+                    load_cond(rec + k * QREC_FLOATS, x, y, z, c);
+                    const ProdC pc = product_component(c, c.w * inv1, b);
+                    total = first ? pc.w : total + pc.w;
+                    first = false;
+                    all_psd = all_psd && pc.psd;
+                }
+                if (use_pref) pref[gi * PROD_THREADS] = total;
+                ++gi;
             }
-        }
+    }
     valid = valid && !first && (total > 1e-20f) && all_psd;   // R: sdmm.h:163-173 prepare_vectorized
     const float inv = 1.f / total;
 
@@ -254,33 +273,47 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
         if (SAMPLE) {
             // ---- pass 3: first component with cdf >= u0, backing off over zero-pmf ones  R: sdmm.h:220-233
             const float u0 = ra.w, u1 = rb.x, u2 = rb.y;
-            float run = 0.f;
-            bool found = false, have_best = false, started = false;
             ProdC sel, best;
             int sel_k = 0, best_k = 0;
-            uint32_t sel_i = 0, best_i = 0, idx = 0;
-            for (int kp = 0; kp < K && !found; kp += 8)
-                for (int m = 0; m < M && !found; ++m) {
-                    const BsdfM b = fetch(m);
-                    if (b.w == 0.f) continue;
-                    for (int k = kp; k < kp + 8; ++k, ++idx) {
-                        load_cond(rec + k * QREC_FLOATS, x, y, z, c);
-                        const ProdC pc = product_component(c, c.w * inv1, b);
-                        run = started ? run + pc.w : pc.w;
-                        started = true;
-                        const bool nz = pc.w * inv != 0.f;
-                        if (nz || !have_best) {   // index 0 is where the back-off stops even at pmf 0
-                            if (nz || idx == 0) { best = pc; best_k = k; best_i = idx; have_best = true; }
-                        }
-                        if (!(run * inv < u0)) {
-                            found = true;
-                            if (nz) { sel = pc; sel_k = k; sel_i = idx; }
-                            else { sel = best; sel_k = best_k; sel_i = best_i; }
-                            break;
+            uint32_t sel_i = 0, best_i = 0;
+            // the group the crossing lies in: the same comparisons on the same floats as the full scan
+            int g_start = 0;
+            if (use_pref)
+                while (g_start < G - 1 && pref[g_start * PROD_THREADS] * inv < u0) ++g_start;
+            for (int attempt = 0; attempt < 2; ++attempt) {
+                float run = (g_start > 0) ? pref[(g_start - 1) * PROD_THREADS] : 0.f;
+                bool found = false, have_best = false, nz_hit = false;
+                uint32_t idx = (uint32_t)g_start * 8u;
+                int gi = 0;
+                for (int kp = 0; kp < K && !found; kp += 8)
+                    for (int m = 0; m < M && !found; ++m) {
+                        if (s_b[m].w == 0.f) continue;
+                        if (gi++ < g_start) continue;
+                        const BsdfM b = fetch(m);
+                        for (int k = kp; k < kp + 8; ++k, ++idx) {
+                            load_cond(rec + k * QREC_FLOATS, x, y, z, c);
+                            const ProdC pc = product_component(c, c.w * inv1, b);
+                            run = (idx == 0) ? pc.w : run + pc.w;
+                            const bool nz = pc.w * inv != 0.f;
+                            if (nz || idx == 0) {   // index 0 is where the back-off stops even at pmf 0
+                                best = pc; best_k = k; best_i = idx; have_best = true;
+                            }
+                            if (!(run * inv < u0)) {
+                                found = true;
+                                nz_hit = nz;
+                                if (nz) { sel = pc; sel_k = k; sel_i = idx; }
+                                break;
+                            }
                         }
                     }
+                // crossing on a zero-pmf component, or no crossing at all (binary_search clamps to the last index):
+                // back off to the last non-zero one
+                if (!(found && nz_hit)) {
+                    if (!have_best && g_start > 0) { g_start = 0; continue; }   // it lies before this group: full scan
+                    sel = best; sel_k = best_k; sel_i = best_i;
                 }
-            if (!found) { sel = best; sel_k = best_k; sel_i = best_i; }   // binary_search clamps to the last index
+                break;
+            }
             out_comp = sel_i;
             // Box-Muller + offset exp map about the conditional component's frame   R: sdmm.h:234-273
             const float radius = sqrtf(-2.f * logf(1.f - u1));
@@ -315,11 +348,12 @@ __global__ void __launch_bounds__(PROD_THREADS) product_query_kernel(ProductLaun
                     const float ly = c.R[3] * wo[0] + c.R[4] * wo[1] + c.R[5] * wo[2];
                     const float lz = c.R[6] * wo[0] + c.R[7] * wo[1] + c.R[8] * wo[2];
                     const float ang = acosf(fminf(1.f, fmaxf(-1.f, lz)));
-                    const float sa = sqrtf(fmaxf(1.f - lz * lz, 0.f));
-                    const float rs = (sa < 1e-4f) ? 1.f : ang / sa;          // R: offset_directional.h:40-60
+                    const float s2 = 1.f - lz * lz;
+                    const bool tiny = !(s2 >= 1e-8f);                        // sin < 1e-4
+                    const float rs = tiny ? 1.f : ang * rsqrtf(s2);          // R: offset_directional.h:40-60
                     const float ij = (lz < -0.98f) ? 0.f : rs;
                     const float t0 = lx * rs - pc.tm0, t1 = ly * rs - pc.tm1;
-                    const float z0 = t0 / pc.L00, z1 = (t1 - pc.L10 * z0) / pc.L11;
+                    const float z0 = t0 * pc.r0, z1 = (t1 - pc.L10 * z0) * pc.r1;
                     const float g = pc.inv_det * kInv2Pi * expf(-0.5f * (z0 * z0 + z1 * z1));
                     pdf = fmaf(ij * g, pc.w * inv, pdf);
                 }
