@@ -60,6 +60,7 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         note="whole render() call, wall clock: optimize() as volpath_sdmm.cpp:244-312 vs the optimizeAsync schedule "
              "(:180-242: fits on a second stream, visible one pass later, one em_step per fit)",
         synchronous_seconds=min(whole(False) for _ in range(2)), async_seconds=min(whole(True) for _ in range(2)))
+    out["interior_doubling"] = run_interior(torch, cpu=cpu)
     if cpu:
         try:
             from oracle import refbind
@@ -83,5 +84,60 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
                                            sample="same loop at %dx%d (1/16 of the pixels), %.1f s; mixture, tree and EM code is the "
                                                   "reference's own, the ray caster a restatement" % (w2, h2, secs))
         except Exception as e:   # the CPU leg is informative only
+            out["cpu_baseline"] = dict(error=str(e))
+    return out
+
+
+def run_interior(torch, width=640, height=360, K=16, max_depth=6, first_spp=8, sample_count=504, cpu=True):
+    """BASELINE.json configs[3]: progressive loop with the doubling schedule and a refit after every iteration on the
+    procedurally generated three-room interior (scenes.interior; every test-suite mesh is an LFS pointer)."""
+    from sdmm_mitsuba_b200 import scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    quads, cam = scenes.interior(width, height)
+    out = dict(workload="three-room interior of analytic boxes (scenes.interior, %d quads), %dx%d, K=%d, maxDepth=%d, "
+                        "doubling schedule from %d spp to %d spp in total, stepwise EM refit after every iteration"
+                        % (len(quads), width, height, K, max_depth, first_spp, sample_count))
+
+    def whole():
+        g = SDMMIntegrator(quads, cam, K=K, max_depth=max_depth, samples_per_iteration=first_spp, seed=5,
+                           pool_capacity=96_000_000)   # 5.8 GB: every sample of the largest pass is kept
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        g.render(sample_count, train_fraction=1.0, schedule="doubling")
+        torch.cuda.synchronize()
+        secs = time.perf_counter() - t0
+        info = dict(iterations=len(g.stats), leaves=g.tree.n_leaves, guided_cells=int(g.initialized.sum()),
+                    samples_dropped=int(sum(s["overflow"] for s in g.stats)),
+                    train_samples=int(sum(s.get("train_samples", 0) for s in g.stats)),
+                    mixture_queries=int(sum(s["guided_queries"] + s["mis_queries"] for s in g.stats)))
+        g.close()
+        return secs, info
+
+    whole()
+    secs, info = min((whole() for _ in range(2)), key=lambda r: r[0])
+    paths = width * height * sample_count
+    out.update(paths=paths, seconds=secs, paths_per_s=paths / secs, **info)
+    if cpu:
+        try:
+            from oracle import refbind
+            if refbind.available():
+                w2, h2 = width // 4, height // 4
+                quads2, cam2 = scenes.interior(w2, h2)
+                lo, hi, norm = scenes.scene_bounds(quads2)
+                rmin, rmax = scenes.root_aabb(lo, hi, norm)
+                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=400000)
+                t0 = time.perf_counter()
+                rendered, spp, it = 0, first_spp, 0
+                while rendered < sample_count:
+                    spp = min(spp, sample_count - rendered)
+                    r.iteration(spp, 2000 + it, True)
+                    rendered += spp
+                    spp *= 2
+                    it += 1
+                secs2 = time.perf_counter() - t0
+                p2 = w2 * h2 * sample_count
+                out["cpu_baseline"] = dict(value=p2 / secs2, unit="paths/s", cores=int(refbind.lib().sdmm_ref_max_threads()),
+                                           kind="reference", sample="same loop at %dx%d (1/16 of the pixels), %.1f s" % (w2, h2, secs2))
+        except Exception as e:
             out["cpu_baseline"] = dict(error=str(e))
     return out

@@ -144,26 +144,52 @@ class SDMMIntegrator:
         # data-driven splits (volpath_sdmm.cpp:253-259); children inherit the parent's state
         if t.n_leaves <= MAX_LEAF_NODES:
             ppos = self.pool[0:3, :n]
+            # Level-synchronous: the host decides which leaves split (HostTree, the reference's rule) and the device
+            # re-buckets the samples of ALL leaves of a recursion level and reduces their children's SpatialStats in
+            # one pass; HostTree then renumbers the new nodes into the reference's depth-first creation order.
+            C = self.cells.max_cells
 
-            def on_split(parent_slot, slot0, slot1, axis, c0_min, c1_max):
-                # create_child (spatial_tree.h:190-203): the parent's data is re-bucketed by the sample POSITION along
-                # the split axis: child 0 takes min < p, child 1 takes max >= p
-                m = cell_of == parent_slot
-                upper = ppos[axis] > c0_min
-                lower = ppos[axis] <= c1_max
-                cell_of[m & upper] = slot0
-                cell_of[m & ~upper & lower] = slot1
-                cell_of[m & ~upper & ~lower] = -1          # falls between the two boxes (rounding gap): dropped
+            def rebucket(level):
+                tab_i = np.full((3, C), -1, np.int64)             # per parent slot: axis, slot0, slot1
+                tab_f = np.zeros((2, C), np.float32)              # c0_min, c1_max
+                box = np.zeros((2, 3, C), np.float32)             # per CHILD slot: aabb min / max
+                for e in level:
+                    ps = e["parent_slot"]
+                    tab_i[:, ps] = (e["axis"], e["slot0"], e["slot1"])
+                    tab_f[:, ps] = (e["c0_min"], e["c1_max"])
+                    box[0, :, e["slot0"]], box[1, :, e["slot0"]] = e["amin0"], e["amax0"]
+                    box[0, :, e["slot1"]], box[1, :, e["slot1"]] = e["amin1"], e["amax1"]
+                tab_i_t = torch.as_tensor(tab_i, device=self.dev)
+                tab_f_t = torch.as_tensor(tab_f, device=self.dev)
+                box_t = torch.as_tensor(box, device=self.dev)
+                ok = (cell_of >= 0) & (cell_of < C)
+                safe = torch.where(ok, cell_of, torch.zeros_like(cell_of))
+                idx = torch.nonzero(ok & (tab_i_t[0][safe] >= 0)).squeeze(1)
+                c = cell_of[idx]
+                p = ppos[:, idx]
+                pa = p.gather(0, tab_i_t[0][c][None])[0]
+                upper = pa > tab_f_t[0][c]                        # create_child (spatial_tree.h:190-203): child 0 takes
+                lower = pa <= tab_f_t[1][c]                       # min < p, child 1 takes max >= p
+                newc = torch.where(upper, tab_i_t[1][c], torch.where(lower, tab_i_t[2][c], torch.full_like(c, -1)))
+                cell_of[idx] = newc                               # -1: fell between the two boxes (rounding gap)
+                keep = newc >= 0
+                cc, pp = newc[keep], p[:, keep]
+                inside = ((pp >= box_t[0][:, cc]) & (pp <= box_t[1][:, cc])).all(dim=0)      # AABB::contains (:204-206)
+                ci, q = cc[inside], pp[:, inside].to(torch.float64)
+                size = torch.bincount(ci, minlength=C).cpu().numpy()
+                s1 = torch.zeros((3, C), dtype=torch.float64, device=self.dev).index_add_(1, ci, q).cpu().numpy()
+                s2 = torch.zeros((3, C), dtype=torch.float64, device=self.dev).index_add_(1, ci, q * q).cpu().numpy()
+                return [tuple((int(size[sl]), s1[:, sl].copy(), s2[:, sl].copy()) for sl in (e["slot0"], e["slot1"]))
+                        for e in level]
 
-            def child_stats(slot, amin, amax):
-                p = ppos[:, cell_of == slot]
-                a = torch.as_tensor(amin, device=self.dev)[:, None]
-                b = torch.as_tensor(amax, device=self.dev)[:, None]
-                inside = ((p >= a) & (p <= b)).all(dim=0)               # AABB::contains
-                q = p[:, inside].to(torch.float64)
-                return int(inside.sum()), q.sum(dim=1).cpu().numpy(), (q * q).sum(dim=1).cpu().numpy()
-
-            splits = t.split_leaves(self.split_threshold, child_stats, on_split)
+            splits, slot_map = t.split_leaves_levels(self.split_threshold, rebucket)
+            if slot_map:
+                lut = np.arange(C, dtype=np.int64)
+                for a_, b_ in slot_map.items():
+                    lut[a_] = b_
+                ok = cell_of >= 0
+                cell_of = torch.where(ok, torch.as_tensor(lut, device=self.dev)[torch.where(ok, cell_of, torch.zeros_like(cell_of))],
+                                      cell_of)
             if splits:
                 src = [s[0] for s in splits]
                 dst = [s[2] for s in splits]                              # child 0 keeps the parent's slot
@@ -267,24 +293,29 @@ class SDMMIntegrator:
             self._pending = None
 
     # ---- render() ---------------------------------------------------------------------------------
-    def render(self, sample_count, train_fraction=0.25, log=None):
-        """The reference's schedule: iterations of samples_per_iteration spp; sample collection + training
-        while samplesRendered < sampleCount * train_fraction (1/4 in the reference, volpath_sdmm.cpp:416)."""
-        rendered = 0
+    def render(self, sample_count, train_fraction=0.25, log=None, schedule="fixed"):
+        """The reference's schedule ("fixed"): iterations of samples_per_iteration spp; sample collection + training
+        while samplesRendered < sampleCount * train_fraction (1/4 in the reference, volpath_sdmm.cpp:411-416).
+        "doubling" (BASELINE.json configs[3]; PPG's schedule, test-suite/scenes/_integrators/ppg.xml): iteration i
+        renders samples_per_iteration * 2^i spp, with a refit after every iteration when train_fraction = 1."""
+        rendered, spp = 0, self.spi
         while rendered < sample_count:
+            spp = min(spp, sample_count - rendered)
             still_training = rendered < sample_count * train_fraction
-            st, new = self.render_pass(self.spi, collect=still_training)
+            st, new = self.render_pass(spp, collect=still_training)
             self.publish_pending()                                    # volpath_sdmm.cpp:446-448
-            info = dict(iteration=self.iteration, spp=self.spi, guided_queries=int(st.guided_queries),
+            info = dict(iteration=self.iteration, spp=spp, guided_queries=int(st.guided_queries),
                         mis_queries=int(st.mis_queries), pool=self.pool_count, overflow=int(st.pool_overflow))
             if still_training:
-                info.update(self.optimize(new))
+                info.update(self.optimize(new))        # before m_totalSpp advances (volpath_sdmm.cpp:494-503)
             self.stats.append(info)
             if log:
                 log(info)
             self.iteration += 1
-            self.total_spp += self.spi
-            rendered += self.spi
+            self.total_spp += spp
+            rendered += spp
+            if schedule == "doubling":
+                spp *= 2
         return self.image()
 
     def image(self):

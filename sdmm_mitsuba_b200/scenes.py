@@ -85,3 +85,58 @@ def root_aabb(lo, hi, norm):
     """getAABB (mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:314-332): normalised box padded by 1e-5."""
     eps = np.float32(1e-5)
     return (np.zeros(3, np.float32) - eps), ((hi - lo) / np.float32(norm)).astype(np.float32) + eps
+
+
+def _box(lo, hi, refl):
+    """Axis-aligned box [lo, hi] as six outward-facing quads."""
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    quads = []
+    for a in range(3):
+        b, c = (a + 1) % 3, (a + 2) % 3
+        eb, ec = np.zeros(3), np.zeros(3)
+        eb[b], ec[c] = hi[b] - lo[b], hi[c] - lo[c]
+        for side, sgn in ((lo, -1.0), (hi, 1.0)):
+            p0 = lo.copy()
+            p0[a] = side[a]
+            n = np.zeros(3)
+            n[a] = sgn
+            quads.append(_quad(p0, eb, ec, n, refl))
+    return quads
+
+
+def interior(width=640, height=360):
+    """A procedurally generated three-room interior of analytic boxes (BASELINE.json configs[3] asks for a complex
+    test-suite interior; every mesh under test-suite/scenes is a git-LFS pointer, so SURVEY.md section 8 F1 allows
+    this instead).  Rooms of 2 x 2 x 2 in a row along x, joined by door openings in 0.1-thick dividing walls; the
+    camera stands in the first room and looks down the row, the only light is a small ceiling panel in the LAST
+    room, so the first room is lit by light that passed two doorways -- the case path guiding is for.
+    61 quads: shell 6, dividing walls 2 x 3 boxes, three furniture boxes, one light."""
+    white, warm, blue, green = (0.725, 0.71, 0.68), (0.7, 0.45, 0.25), (0.2, 0.3, 0.65), (0.14, 0.45, 0.091)
+    q = []
+    # shell [-3, 3] x [0, 2] x [-1, 1], normals facing inwards
+    q.append(_quad((-3, 0, -1), (6, 0, 0), (0, 0, 2), (0, 1, 0), white))      # floor
+    q.append(_quad((-3, 2, -1), (6, 0, 0), (0, 0, 2), (0, -1, 0), white))     # ceiling
+    q.append(_quad((-3, 0, -1), (6, 0, 0), (0, 2, 0), (0, 0, 1), warm))       # back wall z = -1
+    q.append(_quad((-3, 0, 1), (6, 0, 0), (0, 2, 0), (0, 0, -1), blue))       # front wall z = +1
+    q.append(_quad((-3, 0, -1), (0, 0, 2), (0, 2, 0), (1, 0, 0), white))      # end wall x = -3
+    q.append(_quad((3, 0, -1), (0, 0, 2), (0, 2, 0), (-1, 0, 0), green))      # end wall x = +3
+    # dividing walls at x = -1 and x = +1 with a door (z in [-0.4, 0.4], y in [0, 1.5]); the second door is offset
+    for xc, z0 in ((-1.0, -0.4), (1.0, 0.0)):
+        z1 = z0 + 0.8
+        q += _box((xc - 0.05, 0, -1), (xc + 0.05, 2, z0), white)
+        q += _box((xc - 0.05, 0, z1), (xc + 0.05, 2, 1), white)
+        q += _box((xc - 0.05, 1.5, z0), (xc + 0.05, 2, z1), white)
+    # furniture
+    q += _box((-2.2, 0, -0.8), (-1.6, 0.7, -0.3), white)
+    q += _box((-0.5, 0, 0.3), (0.2, 1.1, 0.8), warm)
+    q += _box((1.8, 0, -0.7), (2.5, 0.5, 0.0), white)
+    # ceiling light in the last room, facing down
+    q.append(_quad((1.9, 1.98, -0.25), (0.5, 0, 0), (0, 0, 0.5), (0, -1, 0), (0, 0, 0), emis=(400.0, 380.0, 330.0)))
+    fwd, up = np.array([1.0, 0.0, 0.05]), np.array([0.0, 1.0, 0.0])
+    fwd /= np.linalg.norm(fwd)
+    right = np.cross(up, fwd)
+    right /= np.linalg.norm(right)
+    up = np.cross(fwd, right)
+    camera = dict(origin=np.array([-2.9, 1.0, 0.0], np.float32), right=right.astype(np.float32),
+                  up=up.astype(np.float32), forward=fwd.astype(np.float32), fov_x_degrees=70.0, width=width, height=height)
+    return q, camera

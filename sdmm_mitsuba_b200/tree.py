@@ -162,6 +162,79 @@ class HostTree:
             rec(node)
         return done
 
+    def split_leaves_levels(self, threshold, rebucket):
+        """split_leaves with the data work batched per recursion level (the device does it for all leaves of a level
+        at once), then the nodes and slots created in this pass are renumbered into the order the reference's
+        depth-first split_leaf_recurse would have created them in, so the node table is identical.
+        rebucket(level) with level = list of dicts (parent_slot, slot0, slot1, axis, c0_min, c1_max, amin0, amax0,
+        amin1, amax1) re-buckets the parents' samples (create_child, :190-203) and returns, per entry, the two
+        children's SpatialStats ((size, sum, sqr), (size, sum, sqr)) over the samples inside their boxes (:204-206).
+        Returns (splits, slot_map): splits = [(parent_slot, child0_slot, child1_slot)] in depth-first order with
+        the FINAL slots; slot_map = {temporary slot used during the pass: final slot}."""
+        S0 = self.size()
+        created, created_slots, popped = {}, {}, []
+        frontier = [n for n in range(S0) if self.is_leaf[n] and self.st_size[n] > threshold]
+        while frontier:
+            level, nodes = [], []
+            for node in frontier:
+                if self.st_size[node] <= threshold:
+                    continue
+                ax, loc = self.split_location(node)
+                if not (0.0 < loc < 1.0):
+                    continue
+                parent_slot = self.slot[node]
+                self.axis[node] = ax
+                ch = self._split(node, loc)
+                if ch is None:
+                    continue
+                popped.append(self.slot[ch[1]])
+                created[node] = ch
+                created_slots[node] = (self.slot[ch[0]], self.slot[ch[1]])   # a later split clears slot[child]
+                nodes.append((node, ch))
+                level.append(dict(parent_slot=parent_slot, slot0=self.slot[ch[0]], slot1=self.slot[ch[1]], axis=ax,
+                                  c0_min=float(self.amin[ch[0]][ax]), c1_max=float(self.amax[ch[1]][ax]),
+                                  amin0=self.amin[ch[0]], amax0=self.amax[ch[0]], amin1=self.amin[ch[1]],
+                                  amax1=self.amax[ch[1]]))
+            if not level:
+                break
+            stats = rebucket(level)
+            frontier = []
+            for (node, ch), st in zip(nodes, stats):
+                for c, (size, ssum, ssqr) in zip(ch, st):
+                    self.st_size[c], self.st_sum[c], self.st_sqr[c] = int(size), np.asarray(ssum, np.float64), np.asarray(ssqr, np.float64)
+                    frontier.append(c)
+                self.st_size[node] = 0
+        if not created:
+            return [], {}
+        # depth-first creation order of the new nodes and of the new slots
+        order, split_seq = [], []
+
+        def visit(node):
+            if node in created:
+                c0, c1 = created[node]
+                order.extend((c0, c1))
+                split_seq.append(node)
+                visit(c0)
+                visit(c1)
+
+        for node in range(S0):
+            visit(node)
+        new_id = {b: S0 + i for i, b in enumerate(order)}
+        ident = lambda b: new_id.get(b, b)
+        slot_map = {created_slots[node][1]: popped[j] for j, node in enumerate(split_seq)}
+        smap = lambda sl: slot_map.get(sl, sl)
+        splits = []
+        for node in split_seq:     # child 0 carries the slot its parent had
+            s0, s1 = created_slots[node]
+            splits.append((smap(s0), smap(s0), smap(s1)))
+        perm = list(range(S0)) + order
+        for name in ("is_leaf", "axis", "children", "amin", "amax", "depth", "slot", "st_size", "st_sum", "st_sqr"):
+            old = getattr(self, name)
+            setattr(self, name, [old[b] for b in perm])
+        self.children = [(ident(a), ident(b)) for a, b in self.children]
+        self.slot = [smap(sl) if sl >= 0 else sl for sl in self.slot]
+        return splits, slot_map
+
     def find(self, p):
         node = 0
         while not self.is_leaf[node]:

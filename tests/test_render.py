@@ -184,6 +184,37 @@ def test_async_schedule_matches_cpu_restatement(oracle_ref):
 
 
 @pytest.mark.gpu
+def test_interior_doubling_schedule_matches_cpu_restatement(oracle_ref):
+    """BASELINE.json configs[3]: the progressive loop on the three-room interior with the doubling schedule
+    (8, 16, 32, 64 spp) and a refit after every iteration, against the CPU restatement on the same schedule."""
+    from sdmm_mitsuba_b200 import scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    W, H, K, MD = 160, 90, 16, 6
+    quads, cam = scenes.interior(W, H)
+    assert len(quads) <= 64
+    lo, hi, norm = scenes.scene_bounds(quads)
+    rmin, rmax = scenes.root_aabb(lo, hi, norm)
+    g = SDMMIntegrator(quads, cam, K=K, max_depth=MD, samples_per_iteration=8, seed=3, pool_capacity=4_000_000)
+    r = oracle_ref.RefRenderer(quads, cam, lo, norm, rmin, rmax, K=K, max_depth=MD, capacity=200000)
+    seeds = []
+    g.render(120, train_fraction=1.0, schedule="doubling",
+             log=lambda info: seeds.append(((g.seed * 0x9E3779B97F4A7C15 + info["iteration"]) & 0xFFFFFFFFFFFFFFFF, info["spp"])))
+    assert [s[1] for s in seeds] == [8, 16, 32, 64]
+    rstats = [r.iteration(spp, seed, True) for seed, spp in seeds]
+    ig, ir = g.image(), r.image()
+    assert ir.mean() > 0 and abs(ig.mean() - ir.mean()) <= 5e-3 * ir.mean(), (ig.mean(), ir.mean())
+    for it, (a, b) in enumerate(zip(g.stats, rstats)):
+        assert a["trained"] == b["trained"], (it, a, b)
+        tol = 0 if a["guided_queries"] == 0 else 5e-3 * b["train_samples"]
+        assert abs(a.get("train_samples", 0) - b["train_samples"]) <= tol, (it, a, b)
+    assert g.stats[-1]["guided_queries"] > 10000 and g.stats[2]["trained"] > 4
+    assert abs(g.stats[-1]["guided_queries"] - rstats[-1]["guided_queries"]) <= 5e-3 * rstats[-1]["guided_queries"]
+    nr, t = r.nodes(), g.tree
+    assert t.size() == nr.shape[0]
+    assert all(bool(nr[i, 0] > 0) == t.is_leaf[i] for i in range(t.size()))
+
+
+@pytest.mark.gpu
 def test_guiding_is_unbiased_and_reduces_variance():
     """MIS-combined guided sampling must converge to the same image as BSDF sampling (sdmm_proc.cpp:383-393,
     587-589) and, on this scene (tiny light, no next-event estimation), with a much smaller error per sample."""
