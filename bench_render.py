@@ -65,11 +65,11 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         try:
             from oracle import refbind
             if refbind.available():
-                w2, h2 = width // 4, height // 4
+                w2, h2 = width, height
                 quads2, cam2 = scenes.cornell_box(w2, h2)
                 lo, hi, norm = scenes.scene_bounds(quads2)
                 rmin, rmax = scenes.root_aabb(lo, hi, norm)
-                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=150000)
+                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=2000000)
                 t0 = time.perf_counter()
                 rendered = 0
                 it = 0
@@ -81,7 +81,7 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
                 p2 = w2 * h2 * sample_count
                 out["cpu_baseline"] = dict(value=p2 / secs, unit="paths/s", cores=int(refbind.lib().sdmm_ref_max_threads()),
                                            kind="reference",
-                                           sample="same loop at %dx%d (1/16 of the pixels), %.1f s; mixture, tree and EM code is the "
+                                           sample="the same loop at %dx%d (the whole workload), %.1f s; mixture, tree and EM code is the "
                                                   "reference's own, the ray caster a restatement" % (w2, h2, secs))
         except Exception as e:   # the CPU leg is informative only
             out["cpu_baseline"] = dict(error=str(e))

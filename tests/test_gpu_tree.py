@@ -101,3 +101,30 @@ def test_collect_samples_bins_like_push_back(oracle_ref, oracle_port):
     small = expect_counts < 64
     assert (sa[small, 1] == 0).all() and (sa[~small, 1] == 2).all()
     np.testing.assert_array_equal(ja[small][:, 1:], joint[small][:, 1:])   # means and covariances as uploaded
+
+
+def test_find_cells_in_a_65536_leaf_tree():
+    """The reference caps the tree at 10000 nodes with uint16 child indices (spatial_tree.h:96, 311-312); BASELINE.json
+    configs[4] needs 65536 cells.  131071 nodes, 65536 leaves: device find == host find, every slot reachable."""
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    from sdmm_mitsuba_b200.tree import HostTree
+    eps = np.float32(1e-5)
+    t = HostTree(np.zeros(3, np.float32) - eps, np.ones(3, np.float32) + eps, 65536)
+    t.split_to_depth(5)                      # 8^5 = 32768 leaves
+    for node in t.leaves():
+        assert t._split(node, 0.5) is not None
+    assert t.n_leaves == 65536 and t.size() == 131071
+    flat = t.flatten()
+    assert int(flat["child1"].max()) > 65535          # indices beyond uint16
+    cells = SDMMCells(65536, 16)
+    cells.set_tree(flat)
+    rng = np.random.default_rng(4)
+    q = rng.uniform(0, 1, (3, 40000)).astype(np.float32)
+    got = cells.find_cells(q).astype(np.int64)
+    want = np.array([t.slot[t.find(q[:, i])] for i in range(q.shape[1])], np.int64)
+    np.testing.assert_array_equal(got, want)
+    assert sorted(t.slot[n] for n in t.leaves()) == list(range(65536))
+    # leaf centres hit every slot exactly once
+    centres = np.array([0.5 * (t.amin[n] + t.amax[n]) for n in t.leaves()], np.float32).T.copy()
+    hit = cells.find_cells(centres).astype(np.int64)
+    np.testing.assert_array_equal(hit, np.array([t.slot[n] for n in t.leaves()]))
