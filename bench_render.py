@@ -14,7 +14,7 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
     def loop():
         g = SDMMIntegrator(quads, cam, K=K, max_depth=max_depth, samples_per_iteration=spi, seed=11)
         t_r = t_o = 0.0
-        rendered, q = 0, 0
+        rendered, q, dropped, trained_on = 0, 0, 0, 0
         while rendered < sample_count:
             train = rendered < sample_count / 4
             torch.cuda.synchronize()
@@ -23,7 +23,8 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
             torch.cuda.synchronize()
             t1 = time.perf_counter()
             if train:
-                g.optimize(new)
+                trained_on += g.optimize(new).get("train_samples", 0)
+            dropped += int(st.pool_overflow)
             torch.cuda.synchronize()
             t2 = time.perf_counter()
             t_r += t1 - t0
@@ -35,7 +36,7 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         launches = g.cells.launch_count()
         leaves, trained = g.tree.n_leaves, int(g.initialized.sum())
         g.close()
-        return t_r, t_o, q, launches, leaves, trained
+        return t_r, t_o, q, launches, leaves, trained, dropped, trained_on
 
     def whole(optimize_async):
         # the whole loop through SDMMIntegrator.render(), no synchronisation between the phases
@@ -50,11 +51,11 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         return secs
 
     loop()                                   # warm-up (allocations, first-launch costs)
-    t_r, t_o, q, launches, leaves, trained = loop()
+    t_r, t_o, q, launches, leaves, trained, dropped, trained_on = loop()
     paths = width * height * sample_count
     out.update(paths=paths, seconds=t_r + t_o, render_seconds=t_r, optimize_seconds=t_o,
                paths_per_s=paths / (t_r + t_o), mixture_queries=q, gpu_launches=int(launches), leaves=leaves,
-               guided_cells=trained)
+               guided_cells=trained, train_samples=int(trained_on), samples_dropped=int(dropped))
     whole(True)
     out["schedules"] = dict(
         note="whole render() call, wall clock: optimize() as volpath_sdmm.cpp:244-312 vs the optimizeAsync schedule "
@@ -65,11 +66,11 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
         try:
             from oracle import refbind
             if refbind.available():
-                w2, h2 = width, height
+                w2, h2 = width // 2, height // 2
                 quads2, cam2 = scenes.cornell_box(w2, h2)
                 lo, hi, norm = scenes.scene_bounds(quads2)
                 rmin, rmax = scenes.root_aabb(lo, hi, norm)
-                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=2000000)
+                r = refbind.RefRenderer(quads2, cam2, lo, norm, rmin, rmax, K=K, max_depth=max_depth, capacity=700000)
                 t0 = time.perf_counter()
                 rendered = 0
                 it = 0
@@ -81,7 +82,7 @@ def run_render(torch, width=640, height=360, K=16, max_depth=5, spi=64, sample_c
                 p2 = w2 * h2 * sample_count
                 out["cpu_baseline"] = dict(value=p2 / secs, unit="paths/s", cores=int(refbind.lib().sdmm_ref_max_threads()),
                                            kind="reference",
-                                           sample="the same loop at %dx%d (the whole workload), %.1f s; mixture, tree and EM code is the "
+                                           sample="the same loop at %dx%d (1/4 of the pixels), %.1f s; mixture, tree and EM code is the "
                                                   "reference's own, the ray caster a restatement" % (w2, h2, secs))
         except Exception as e:   # the CPU leg is informative only
             out["cpu_baseline"] = dict(error=str(e))
