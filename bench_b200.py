@@ -1,6 +1,7 @@
 """Second half of bench.py: the B200 arm (one process per GPU; torchrun provides RANK/WORLD_SIZE)."""
 import json
 import os
+import sys
 import time
 
 import numpy as np
@@ -31,7 +32,19 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line (no "NCCL version" banner)
-        dist.init_process_group("nccl", device_id=device)
+        # NCCL prints its version banner on stdout when the communicator comes up (whatever the box's
+        # NCCL_DEBUG says): point fd 1 at stderr meanwhile so that stdout stays the one JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=device)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     K, N, iters = cfg["K"], cfg["N"], cfg["iters"]
     strong = args.config == "cfg5"
@@ -55,10 +68,32 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     off = (np.arange(C_local + 1, dtype=np.uint64) * N).astype(np.uint32)
     torch.cuda.synchronize()
 
+    # record exchange after the fit: "peer" = stores into every peer's record array fused into the
+    # kernel that writes the records (NVLink peer memory, no collective call); "nccl" = all-gather
+    exchange = "none"
+    if world > 1:
+        exchange = args.exchange
+        ok = 1
+        if exchange == "peer":
+            try:
+                cells.attach_peers()
+            except Exception as e:  # no P2P / IPC between the ranks: say so, use the collective
+                print("bench: peer attach failed on rank %d (%s); falling back to the NCCL all-gather" % (rank, e),
+                      file=sys.stderr, flush=True)
+                ok = 0
+        flag = torch.tensor([ok], device=device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if exchange == "peer" and int(flag.item()) == 0:
+            if ok:
+                cells.detach_peers()
+            exchange = "nccl"
+
     def step():
         cells.set_samples(point6, weight, off, first_cell=first)
         cells.em_step(iters, with_conditioner=True)
-        if world > 1:
+        if exchange == "peer":
+            cells.wait_peers()
+        elif exchange == "nccl":
             cells.allgather_records(C_local)
 
     for _ in range(args.warmup):
@@ -80,6 +115,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     if world > 1:
         dist.barrier()
     ms_local = e0.elapsed_time(e1)
+    peer_timeouts = cells.peer_status()[1] if exchange == "peer" else None
     estep_ms, estep_n = cells.last_estep_ms()
     clocks = sampler.stop() if rank == 0 else None
     launches = cells.launch_count() - l0
@@ -243,8 +279,10 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
             config=dict(workload="%s: batched StepwiseTangentEM (sdmm::em_step), %d cells x %d components x %d "
                                  "5-D samples/cell, %d EM iterations per step%s" %
                                  (args.config, C_total, K, N, iters,
-                                  (" (%d cells per GPU, cell-sharded, NCCL all-gather of query records per step)"
-                                   % C_local) if world > 1 else ""),
+                                  (" (%d cells per GPU, cell-sharded, query records exchanged every step: %s)"
+                                   % (C_local, "peer-memory stores fused into the M-step kernel" if exchange == "peer"
+                                      else "NCCL all-gather")) if world > 1 else ""),
+                        exchange=exchange, peer_timeouts=peer_timeouts,
                         cells=C_total, components=K, samples_per_cell=N, em_iterations=iters,
                         parallelism="cells sharded over %d GPU(s)" % world,
                         l2_policy="inputs larger than L2 (%.0f MB of packed samples per GPU per iteration)"

@@ -259,6 +259,31 @@ int sdmmb_query_records(sdmmb_ctx* ctx, float** d_records, size_t* floats_per_ce
  * resolved at run time (dlopen), so the library has no link-time NCCL dependency. */
 int sdmmb_allgather_records(sdmmb_ctx* ctx, void* nccl_comm, int cells_per_rank, void* stream);
 
+/* The same exchange WITHOUT a collective call: fused into the kernel that writes the records.
+ * After sdmmb_peer_attach the last M-step of sdmmb_em_step(with_conditioner = 1) and
+ * sdmmb_prepare_conditioner store every freshly written record straight into the record arrays of
+ * all peers (NVLink / NVSwitch peer memory, CTA by CTA as the cells finish) and raise an arrival flag
+ * there; sdmmb_peer_wait enqueues a device-side wait for the flags of all peers, after which queries
+ * on that stream see every cell.  Protocol (SPMD): every rank issues the same sequence of pushing
+ * calls; a rank's records are only overwritten once it has entered the same step (its ready flag is
+ * raised stream-ordered at the start of its own pushing call), so queries of the previous step that
+ * precede that call on the stream are safe.  Waits are bounded (SDMMB_PEER_TIMEOUT_MS, default
+ * 10000): a timeout skips the stores, is counted, and shows in sdmmb_peer_status.
+ * With async records enabled (sdmmb_set_async_records) nothing is pushed.
+ *   h_handle : SDMMB_PEER_HANDLE_BYTES, opaque (CUDA IPC handles + same-process pointers);
+ *   h_handles: world * SDMMB_PEER_HANDLE_BYTES, rank r's handle at r (exchange them with any
+ *              host-side all-gather: torch.distributed, MPI, a pipe).
+ * This replaces the reference's conditioner swap loop for the multi-GPU case
+ * (mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:227-242 publishes refitted conditioners to the
+ * render threads; here the "render threads" are the other GPUs). */
+#define SDMMB_PEER_HANDLE_BYTES 192
+#define SDMMB_E_PEER (-9)      /* peer memory not reachable (no P2P / IPC open failed) */
+int sdmmb_peer_export(sdmmb_ctx* ctx, unsigned char* h_handle);
+int sdmmb_peer_attach(sdmmb_ctx* ctx, int rank, int world, const unsigned char* h_handles);
+int sdmmb_peer_detach(sdmmb_ctx* ctx);
+int sdmmb_peer_wait(sdmmb_ctx* ctx, void* stream);
+int sdmmb_peer_status(sdmmb_ctx* ctx, uint32_t* out_epoch, uint32_t* out_timeouts, void* stream);
+
 /* Introspection used by bench.py */
 int sdmmb_launch_count(sdmmb_ctx* ctx, uint64_t* out);           /* kernels launched by this ctx */
 int sdmmb_last_estep_ms(sdmmb_ctx* ctx, float* total_ms, int* n_launches); /* CUDA-event time of

@@ -31,7 +31,10 @@ SYMBOLS = [
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
+    "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
 ]
+PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
+E_PEER = -9
 
 
 
@@ -113,6 +116,11 @@ def lib():
     L.sdmmb_publish_records.argtypes = [vp, i, i, vp]
     L.sdmmb_query_records.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     L.sdmmb_allgather_records.argtypes = [vp, vp, i, vp]
+    L.sdmmb_peer_export.argtypes = [vp, vp]
+    L.sdmmb_peer_attach.argtypes = [vp, i, i, vp]
+    L.sdmmb_peer_detach.argtypes = [vp]
+    L.sdmmb_peer_wait.argtypes = [vp, vp]
+    L.sdmmb_peer_status.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), vp]
     L.sdmmb_launch_count.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.sdmmb_last_estep_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i)]
     L.sdmmb_measure_peaks.argtypes = [i, C.POINTER(C.c_float)]

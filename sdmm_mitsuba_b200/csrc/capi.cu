@@ -2,6 +2,7 @@
 // the flat host layouts and the device layouts, work-item construction, kernel launches.
 // No CPU fallback anywhere: every entry point drives the CUDA kernels of this library.
 #include <dlfcn.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstdlib>
@@ -68,6 +69,11 @@ struct sdmmb_ctx {
     void* nccl_handle = nullptr;
     int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     int (*nccl_user_rank)(void*, int*) = nullptr;
+    // peer-memory record exchange (capi_part6.inc)
+    uint32_t* d_peer_flags = nullptr;   // PEER_FLAG_WORDS words, exported to the peers
+    PeerPush peer{};                    // world == 0 until sdmmb_peer_attach
+    uint32_t peer_epoch = 0;            // pushing launches issued so far
+    std::vector<void*> peer_ipc_opened; // mappings to close on detach
 };
 
 namespace {
@@ -130,6 +136,7 @@ MStepArgs base_mstep_args(sdmmb_ctx* ctx, int first_cell, int n_cells, int mode)
     a.erec = ctx->d_erec;
     a.qrec = ctx->d_qrec_back ? ctx->d_qrec_back : ctx->d_qrec;
     a.min_samples = ctx->min_samples;
+    a.peer.world = 0;
     return a;
 }
 
@@ -166,6 +173,7 @@ const char* sdmmb_get_error_string(int code) {
         case SDMMB_E_STATE: return "call order: samples not bound for this cell range";
         case SDMMB_E_NCCL: return "NCCL missing or returned an error";
         case SDMMB_E_DATA_FULL: return "Data full.";
+        case SDMMB_E_PEER: return "peer memory not reachable (no P2P between the devices or CUDA IPC open failed)";
         default: return "unknown error";
     }
 }
@@ -226,6 +234,8 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_qrec_back); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch); cudaFree(ctx->d_tree);
+    for (void* m : ctx->peer_ipc_opened) cudaIpcCloseMemHandle(m);
+    cudaFree(ctx->d_peer_flags);
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     if (ctx->copy_stream) {
         cudaStreamDestroy(ctx->copy_stream);

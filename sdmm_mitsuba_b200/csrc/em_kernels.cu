@@ -681,6 +681,106 @@ __device__ inline bool categorical_prepare_seq(float* pmf, float* cdf, int K) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// K3 epilogue: record exchange over peer memory (replaces the all-gather that would follow).
+// Called by every thread of every CTA after the CTA's records are in local memory (and after a
+// __syncthreads()).  The CTA's records are one contiguous run of MSTEP_THREADS * 128 bytes: read
+// once (L2-hot), stored coalesced to the same offset of every peer's array, peers visited in
+// rotated order so that the ranks do not all hit the same destination at once.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// spin until *flag >= epoch (epochs only grow); false on timeout
+__device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, uint32_t timeout_ms) {
+    if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+    const unsigned long long t0 = globaltimer_ns(), limit = (unsigned long long)timeout_ms * 1000000ull;
+    while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+        __nanosleep(200);
+        if (globaltimer_ns() - t0 > limit) return false;
+    }
+    return true;
+}
+
+__device__ __forceinline__ void peer_push_records(const MStepArgs& a) {
+    const PeerPush& P = a.peer;
+    const int K = a.K;
+    const int cells_per_cta = MSTEP_THREADS / K;
+    const int c0 = blockIdx.x * cells_per_cta;
+    const int nc = min(cells_per_cta, a.n_cells - c0);
+    uint32_t* lf = P.flags[P.rank];
+    __shared__ int s_go;
+    if (threadIdx.x == 0) s_go = 1;
+    __syncthreads();
+    // a peer's records may only be overwritten once it has entered this training step
+    if (threadIdx.x < P.world && (int)threadIdx.x != P.rank) {
+        if (!wait_flag(lf + PEER_READY + threadIdx.x, P.epoch, P.timeout_ms)) {
+            atomicAdd(lf + PEER_ERROR, 1u);
+            s_go = 0;
+        }
+    }
+    __syncthreads();
+    if (s_go && nc > 0) {
+        constexpr int V = QREC_FLOATS / 4;  // float4 per record = per thread
+        const size_t off = ((size_t)(a.first_cell + c0) * K) * V;
+        const int n4 = nc * K * V;
+        // the local array the records were written to may be the async back copy; peers always
+        // receive into their published array
+        const float4* src = reinterpret_cast<const float4*>(a.qrec) + off;
+        float4 v[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            const int idx = j * MSTEP_THREADS + threadIdx.x;
+            v[j] = (idx < n4) ? __ldcg(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int pp = 1; pp < P.world; ++pp) {
+            const int p = (P.rank + pp) % P.world;
+            float4* dst = reinterpret_cast<float4*>(P.qrec[p]) + off;
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                const int idx = j * MSTEP_THREADS + threadIdx.x;
+                if (idx < n4) dst[idx] = v[j];
+            }
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t done = atomicAdd(lf + PEER_COUNTER, 1u);
+        if (done == gridDim.x - 1) {   // every CTA's stores are fenced: publish this rank's arrival
+            lf[PEER_COUNTER] = 0;
+            __threadfence_system();
+            for (int pp = 1; pp < P.world; ++pp) {
+                const int p = (P.rank + pp) % P.world;
+                st_release_sys(P.flags[p] + PEER_ARRIVED + P.rank, P.epoch);
+            }
+        }
+    }
+}
+
+__global__ void peer_signal_kernel(PeerPush P) {
+    const int p = threadIdx.x;
+    if (p < P.world && p != P.rank) st_release_sys(P.flags[p] + PEER_READY + P.rank, P.epoch);
+}
+
+__global__ void peer_wait_kernel(PeerPush P) {
+    const int p = threadIdx.x;
+    uint32_t* lf = P.flags[P.rank];
+    if (p < P.world && p != P.rank) {
+        if (!wait_flag(lf + PEER_ARRIVED + p, P.epoch, P.timeout_ms)) atomicAdd(lf + PEER_ERROR, 1u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // K2 (+K3): M-step.  One thread per (cell, component); MSTEP_THREADS / K cells per CTA.
 // mode bit 0: run the EM update (else only prepare from the stored model)
 // mode bit 1: also write the conditioner's query records
@@ -895,6 +995,7 @@ em_mstep_kernel(MStepArgs a) {
         if (!s_psd[local]) status |= ST_NON_PSD;
         scal[7] = status;
     }
+    if ((a.mode & 2) && a.peer.world > 1) peer_push_records(a);  // uniform over the grid
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -999,6 +1100,16 @@ cudaError_t launch_mstep(const MStepArgs& a, cudaStream_t st) {
     const int cells_per_cta = MSTEP_THREADS / a.K;
     const int grid = (a.n_cells + cells_per_cta - 1) / cells_per_cta;
     em_mstep_kernel<<<grid, MSTEP_THREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_peer_signal(const PeerPush& p, cudaStream_t st) {
+    peer_signal_kernel<<<1, 32, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_peer_wait(const PeerPush& p, cudaStream_t st) {
+    peer_wait_kernel<<<1, 32, 0, st>>>(p);
     return cudaGetLastError();
 }
 

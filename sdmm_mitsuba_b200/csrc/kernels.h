@@ -58,6 +58,25 @@ struct EStepLaunch {
     float* out_loglik; // nullable, indexed by absolute sample index
 };
 
+// Multi-GPU record exchange fused into K3 (sdmmb_peer_attach): the CTA that wrote the query records
+// of its cells stores them straight into every peer's record array over NVLink, then the launch's
+// last CTA raises this rank's arrival flag on every peer.  Flag words of one context (uint32):
+//   [0 .. 7]  ready[r]   : rank r has entered training step `epoch` (its queries of the previous
+//                          step are done, so its records may be overwritten)        -- written by r
+//   [8 .. 15] arrived[r] : rank r's records of step `epoch` are complete here       -- written by r
+//   [16] CTA counter of the pushing launch, [17] timeout error count
+constexpr int PEER_MAX = 8;
+constexpr int PEER_FLAG_WORDS = 32;
+constexpr int PEER_READY = 0, PEER_ARRIVED = 8, PEER_COUNTER = 16, PEER_ERROR = 17;
+struct PeerPush {
+    int world;                       // 0 = disabled
+    int rank;
+    uint32_t epoch;                  // this launch's training step (1, 2, ...)
+    uint32_t timeout_ms;
+    float* qrec[PEER_MAX];           // every rank's record array (entry `rank` = the local one)
+    uint32_t* flags[PEER_MAX];       // every rank's flag words
+};
+
 struct MStepArgs {
     int K;
     int first_cell, n_cells;
@@ -74,6 +93,7 @@ struct MStepArgs {
     uint32_t item_base;                 // item index that `partials` / `item_scal` start at
     const uint32_t* cell_sample_count;  // [n_cells]
     uint32_t min_samples;               // cells with fewer bound samples are left untouched by the EM update
+    PeerPush peer;                      // world == 0: no peer stores
 };
 
 struct QueryLaunch {
@@ -133,6 +153,10 @@ cudaError_t launch_pack(const float* point6, size_t stride, const float* weight,
                         cudaStream_t st);
 cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st);
 cudaError_t launch_mstep(const MStepArgs& a, cudaStream_t st);
+// raises ready[rank] = epoch on every peer (stream-ordered after this rank's earlier work)
+cudaError_t launch_peer_signal(const PeerPush& p, cudaStream_t st);
+// device-side wait until arrived[r] >= epoch for every peer r (bounded by timeout_ms)
+cudaError_t launch_peer_wait(const PeerPush& p, cudaStream_t st);
 cudaError_t launch_derived_readout(const float* joint, const float* cdf, int first_cell, int n_cells, int K,
                                    float* out, cudaStream_t st);
 cudaError_t launch_conditioner_readout(const float* joint, const float* qrec, int first_cell, int n_cells,

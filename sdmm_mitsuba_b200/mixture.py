@@ -200,7 +200,11 @@ class SDMMCells:
     def prepare(self, first_cell=0, n_cells=None):
         """sdmm::prepare(conditioner, sdmm) for a cell range."""
         n = self.max_cells - first_cell if n_cells is None else n_cells
-        check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, None), "sdmmb_prepare_conditioner", self._h)
+        try:
+            st = _stream(self.device)
+        except Exception:
+            st = None
+        check(self._L.sdmmb_prepare_conditioner(self._h, first_cell, n, st), "sdmmb_prepare_conditioner", self._h)
 
     # ---- spatial cell structure ---------------------------------------------------------------
     def set_tree(self, nodes):
@@ -373,6 +377,45 @@ class SDMMCells:
         (rank r owns cells [r*cells_per_rank, (r+1)*cells_per_rank)).  NCCL all-gather, in place."""
         from . import sharding
         sharding.allgather_records(self.query_records(), cells_per_rank, group)
+
+    # ---- record exchange over peer memory, fused into the kernel that writes the records ----------
+    def peer_export(self):
+        """This context's opaque peer handle (bytes) for sdmmb_peer_attach on the other ranks."""
+        buf = (C.c_ubyte * capi.PEER_HANDLE_BYTES)()
+        check(self._L.sdmmb_peer_export(self._h, C.cast(buf, C.c_void_p)), "sdmmb_peer_export", self._h)
+        return bytes(buf)
+
+    def peer_attach(self, rank, handles):
+        """handles: list of every rank's peer_export() bytes, rank r's at index r."""
+        blob = b"".join(handles)
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(self._L.sdmmb_peer_attach(self._h, int(rank), len(handles), C.cast(buf, C.c_void_p)),
+              "sdmmb_peer_attach", self._h)
+
+    def attach_peers(self, group=None):
+        """One process per GPU: exchange the handles over torch.distributed (any backend) and attach.
+        Afterwards em_step(with_conditioner=True) / prepare() store the records they write straight into
+        every peer's record array; finish a step with wait_peers() instead of allgather_records()."""
+        import torch.distributed as dist
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        mine = self.peer_export()
+        handles = [None] * world
+        dist.all_gather_object(handles, mine, group=group)
+        self.peer_attach(rank, handles)
+
+    def detach_peers(self):
+        check(self._L.sdmmb_peer_detach(self._h), "sdmmb_peer_detach", self._h)
+
+    def wait_peers(self):
+        """Stream-ordered device-side wait until every peer's records of the current step arrived."""
+        check(self._L.sdmmb_peer_wait(self._h, _stream(self.device)), "sdmmb_peer_wait", self._h)
+
+    def peer_status(self):
+        """(exchange epochs issued, bounded waits that timed out)."""
+        ep, to = C.c_uint32(), C.c_uint32()
+        check(self._L.sdmmb_peer_status(self._h, C.byref(ep), C.byref(to), _stream(self.device)),
+              "sdmmb_peer_status", self._h)
+        return int(ep.value), int(to.value)
 
     def launch_count(self):
         v = C.c_uint64()

@@ -44,11 +44,31 @@ def main():
     pdf0 = pdf.clone()
     dist.broadcast(pdf0, src=0)
     same_q = bool((pdf == pdf0).all().item()) and bool((out["valid"].float().mean() > 0.9).item())
-    flags = torch.tensor([int(same), int(same_q)], device="cuda")
+    # the same exchange without the collective: peer-memory stores fused into the M-step kernel
+    # (CUDA IPC across the rank processes); restart from the same model -> must reproduce `rec` bit for bit
+    same_p, timeouts = False, -1
+    try:
+        cells.attach_peers()
+        cells.query_records().zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        for rep in range(2):   # two epochs: handshake reuse
+            cells.upload(joint[first:first + n], em[first:first + n], scal[first:first + n], first_cell=first)
+            cells.em_step(3, with_conditioner=True)
+            cells.wait_peers()
+        torch.cuda.synchronize()
+        ep, timeouts = cells.peer_status()
+        same_p = bool(torch.equal(cells.query_records(), rec)) and ep == 2 and timeouts == 0
+        dist.barrier()
+        cells.detach_peers()
+    except Exception as e:  # noqa: BLE001
+        print("rank %d: peer exchange failed: %s" % (rank, e), flush=True)
+    flags = torch.tensor([int(same), int(same_q), int(same_p)], device="cuda")
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print("mgpu_check world=%d records_identical=%d queries_identical=%d nonzero_records=%d" %
-              (world, flags[0].item(), flags[1].item(), int((rec[:C_total] != 0).any(dim=(1, 2)).sum().item())), flush=True)
+        print("mgpu_check world=%d records_identical=%d queries_identical=%d peer_push_identical=%d nonzero_records=%d" %
+              (world, flags[0].item(), flags[1].item(), flags[2].item(),
+               int((rec[:C_total] != 0).any(dim=(1, 2)).sum().item())), flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if flags.min().item() == 1 else 1)
