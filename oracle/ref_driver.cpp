@@ -738,5 +738,119 @@ void sdmm_ref_tree_find(void* h, long n, const float* pos3, int32_t* out_node) {
     }
 }
 
+#ifdef SDMM_REF_WITH_JSON
+// (compiled only by ref_checkpoint.cpp: needs nlohmann_json >= 3.9 for NLOHMANN_DEFINE_TYPE_INTRUSIVE; the json.hpp
+// vendored with the reference's legacy jmm tree is 3.7.3 and the macro is stubbed out for the other drivers)
+// ---- .asdmm checkpoints: the reference's own save_json of the accelerator (volpath_sdmm.cpp:120-130,
+// core/utils.h:130-147) and the from_json NLOHMANN_DEFINE_TYPE_INTRUSIVE generates (spatial_tree.h:314).
+// STree has no default constructor, so loading goes into an existing tree (m_nodes and m_aabb are
+// replaced; the reference does not restore m_nodes_end, callers walk from the root).
+int sdmm_ref_tree_save_json(void* h, const char* path) {
+    // save_json's body (core/utils.h:130-137) with the two-member object NLOHMANN_DEFINE_TYPE_INTRUSIVE(STree,
+    // m_nodes, m_aabb) (spatial_tree.h:314) written out by hand: json 3.11's conversion traits probe
+    // STree::end(), whose body does not compile (spatial_tree.h:113-115; the reference's pinned 3.9.1 never
+    // looks at it).  m_aabb is private; the constructor copies it to the root node (:91).  Nodes, mixtures,
+    // tangent spaces, matrices and boxes go through the reference's own serializers.
+    try {
+        auto& tree = *static_cast<RefTree*>(h)->tree;
+        nlohmann::json j;
+        j["m_nodes"] = tree.data();
+        j["m_aabb"] = tree.data()[0].aabb;
+        std::ofstream file(path);
+        file << std::setw(4) << j << std::endl;
+    } catch (...) { return -1; }
+    return 0;
+}
+
+int sdmm_ref_tree_load_json(void* h, const char* path) {
+    try {
+        auto& tree = *static_cast<RefTree*>(h)->tree;
+        std::ifstream file(path);
+        nlohmann::json j;
+        file >> j;
+        auto nodes = j.at("m_nodes").get<std::vector<Tree::Node>>();
+        (void)j.at("m_aabb").get<Tree::AABB>();
+        const_cast<std::vector<Tree::Node>&>(tree.data()) = std::move(nodes);
+    } catch (...) { return -1; }
+    return 0;
+}
+
+// Install / read back a leaf's joint mixture (planes: pmf, mean[6], cov[25] row-major, K floats each).
+int sdmm_ref_tree_set_leaf_model(void* h, int node, int K, const float* joint) {
+    auto& nodes = const_cast<std::vector<Tree::Node>&>(static_cast<RefTree*>(h)->tree->data());
+    if (node < 0 || node >= (int)nodes.size() || !nodes[node].value) return -1;
+    auto& m = nodes[node].value->sdmm;
+    m = enoki::zero<JointSDMM>(K);
+    enoki::set_slices(m, K);
+    for (int k = 0; k < K; ++k) m.weight.pmf.coeff(k) = joint[k];
+    sdmm::embedded_t<JointSDMM> mean;
+    enoki::set_slices(mean, K);
+    for (int d = 0; d < 6; ++d)
+        for (int k = 0; k < K; ++k) mean.coeff(d).coeff(k) = joint[(1 + d) * K + k];
+    m.tangent_space.set_mean(mean);
+    for (int r = 0; r < 5; ++r)
+        for (int col = 0; col < 5; ++col)
+            for (int k = 0; k < K; ++k) m.cov(r, col).coeff(k) = joint[(7 + 5 * r + col) * K + k];
+    return sdmm::prepare_vectorized(m) ? 1 : 0;
+}
+
+// returns K (0: leaf without a mixture, -1: not a node with a value); joint may be null to query K.
+// frame (nullable): coordinate_system.to then .from, 9 planes each, row-major.
+int sdmm_ref_tree_get_leaf_model(void* h, int node, int K_cap, float* joint, float* frame) {
+    const auto& nodes = static_cast<RefTree*>(h)->tree->data();
+    if (node < 0 || node >= (int)nodes.size() || !nodes[node].value) return -1;
+    const auto& m = nodes[node].value->sdmm;
+    const int K = (int)enoki::slices(m.weight.pmf);
+    if (!joint || K > K_cap) return K;
+    for (int k = 0; k < K; ++k) joint[k] = m.weight.pmf.coeff(k);
+    for (int d = 0; d < 6; ++d)
+        for (int k = 0; k < K; ++k) joint[(1 + d) * K + k] = m.tangent_space.mean.coeff(d).coeff(k);
+    for (int r = 0; r < 5; ++r)
+        for (int col = 0; col < 5; ++col)
+            for (int k = 0; k < K; ++k) joint[(7 + 5 * r + col) * K + k] = m.cov(r, col).coeff(k);
+    if (frame)
+        for (int r = 0; r < 3; ++r)
+            for (int col = 0; col < 3; ++col)
+                for (int k = 0; k < K; ++k) {
+                    frame[(3 * r + col) * K + k] = m.tangent_space.coordinate_system.to(r, col).coeff(k);
+                    frame[(9 + 3 * r + col) * K + k] = m.tangent_space.coordinate_system.from(r, col).coeff(k);
+                }
+    return K;
+}
+
+// all stored nodes (the reference keeps 10000): per node 13 values: is_leaf, axis, child0, child1, has value,
+// aabb.min[3], aabb.max[3], idx, depth
+int sdmm_ref_tree_stored_nodes(void* h) { return (int)static_cast<RefTree*>(h)->tree->data().size(); }
+void sdmm_ref_tree_export_stored(void* h, int first, int n, double* out) {
+    const auto& nodes = static_cast<RefTree*>(h)->tree->data();
+    for (int i = 0; i < n; ++i) {
+        const auto& nd = nodes[first + i];
+        double* o = out + 13 * (size_t)i;
+        o[0] = nd.is_leaf ? 1 : 0;
+        o[1] = nd.axis;
+        o[2] = nd.children[0];
+        o[3] = nd.children[1];
+        o[4] = nd.value ? 1 : 0;
+        for (int d = 0; d < 3; ++d) { o[5 + d] = nd.aabb.min.coeff(d); o[8 + d] = nd.aabb.max.coeff(d); }
+        o[11] = nd.idx;
+        o[12] = nd.depth;
+    }
+}
+// STree::find on a LOADED tree (size() is not restored by from_json): leaf's node index over all stored nodes
+void sdmm_ref_tree_find_stored(void* h, long n, const float* pos3, int32_t* out_node) {
+    auto& tree = *static_cast<RefTree*>(h)->tree;
+    const auto& nodes = tree.data();
+    for (long i = 0; i < n; ++i) {
+        Tree::Point key(pos3[i], pos3[n + i], pos3[2 * n + i]);
+        auto* ctx = tree.find(key);
+        int found = -1;
+        if (ctx)
+            for (int j = 0; j < (int)nodes.size(); ++j)
+                if (nodes[j].is_leaf && nodes[j].value.get() == ctx) { found = j; break; }
+        out_node[i] = found;
+    }
+}
+#endif  // SDMM_REF_WITH_JSON
+
 }  // extern "C"
 #include "ref_render.inc"

@@ -318,6 +318,29 @@ class SDMMIntegrator:
                 spp *= 2
         return self.image()
 
+    def save_checkpoint(self, experiment_path):
+        """saveCheckpoint (volpath_sdmm.cpp:121-130, called at the end of render(), :513): the accelerator -- node
+        table + every leaf's joint mixture -- as `<experiment_path>/checkpoints/model_%05i.asdmm` in the reference's
+        JSON layout (checkpoint.py); leaves that never received a mixture are written with value = null like the
+        reference's empty contexts would be with size 0.  Also stores the EM statistics (extra keys)."""
+        import os
+        from . import checkpoint
+        d = os.path.join(str(experiment_path), "checkpoints")
+        os.makedirs(d, exist_ok=True)
+        path = os.path.join(d, "model_%05i.asdmm" % self.iteration)
+        self.publish_pending()
+        joint, em, scal = self.cells.download()
+        slots = [self.tree.slot[i] for i in range(self.tree.size()) if self.tree.is_leaf[i]]
+        keep = np.zeros(joint.shape[0], bool)
+        keep[[s for s in slots if self.has_mixture[s]]] = True
+        tree = self.tree
+        if not keep[slots].all():       # hide the slots of mixture-less leaves from the writer
+            import copy
+            tree = copy.copy(self.tree)
+            tree.slot = [(-1 if (s >= 0 and not keep[s]) else s) for s in self.tree.slot]
+        checkpoint.save_asdmm(path, tree, joint, K=self.K, em_by_slot=em, scal_by_slot=scal)
+        return path
+
     def image(self):
         img = (self.image_sum / max(1, self.total_spp)).reshape(3, self.height, self.width)
         return img.cpu().numpy()

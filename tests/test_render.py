@@ -241,3 +241,45 @@ def test_guiding_is_unbiased_and_reduces_variance():
     mse_b, mse_g = ((img_b - img_ref) ** 2).mean(), ((img_g - img_ref) ** 2).mean()
     assert mse_g < 0.8 * mse_b, (mse_g, mse_b)
     assert int(gi.initialized.sum()) > 5
+
+
+@pytest.mark.gpu
+def test_render_writes_a_reference_layout_checkpoint(tmp_path):
+    """saveCheckpoint (volpath_sdmm.cpp:121-130, 513): after render() the accelerator is written as
+    checkpoints/model_%05i.asdmm; reading it back gives the same tree and, uploaded into a fresh context, the same
+    query records for every trained leaf."""
+    import torch
+    from sdmm_mitsuba_b200 import checkpoint, scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    quads, cam = scenes.cornell_box(320, 180)
+    gi = SDMMIntegrator(quads, cam, K=16, max_depth=5, samples_per_iteration=32, seed=5, max_cells=256)
+    gi.render(256)
+    path = gi.save_checkpoint(str(tmp_path))
+    assert path.endswith("checkpoints/model_%05i.asdmm" % gi.iteration)
+    tree, joint, ex = checkpoint.load_asdmm(path, max_cells=256)
+    assert tree.size() == gi.tree.size() and tree.n_leaves == gi.tree.n_leaves
+    assert tree.is_leaf == gi.tree.is_leaf and tree.children == gi.tree.children
+    trained = [i for i in range(tree.size()) if tree.is_leaf[i] and gi.has_mixture[gi.tree.slot[i]]]
+    assert len(trained) > 5 and ex["K"] == 16
+    assert sorted(ex["empty_slots"]) == sorted(tree.slot[i] for i in range(tree.size())
+                                               if tree.is_leaf[i] and i not in trained)
+    fresh = SDMMCells(256, 16)
+    n = joint.shape[0]
+    em = np.zeros((n, 81, 16), np.float32)
+    sc = np.zeros((n, 8), np.uint32)
+    for s in ex["em"]:
+        em[s], sc[s] = ex["em"][s], ex["scalars"][s]
+    # untrained leaves: any valid mixture (not compared)
+    for s in ex["empty_slots"]:
+        joint[s, 0] = 1.0 / 16
+        joint[s, 6] = 1.0
+        for d in range(5):
+            joint[s, 7 + 6 * d] = 1.0
+    fresh.upload(joint, em, sc)
+    fresh.prepare(0, n)
+    torch.cuda.synchronize()
+    r_old, r_new = gi.cells.query_records(), fresh.query_records()
+    for i in trained:
+        # upload normalises the (already normalised) weights once more, like the reference's from_json -> prepare
+        assert torch.allclose(r_old[gi.tree.slot[i]], r_new[tree.slot[i]], rtol=2e-5, atol=2e-6), i

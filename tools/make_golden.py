@@ -120,7 +120,41 @@ def make_init(name, C, K, N):
     print(path, "%.0f KB" % (os.path.getsize(path) / 1e3))
 
 
+def make_checkpoint():
+    """A `.asdmm` checkpoint written by the reference's own serializers (oracle/ref_checkpoint.cpp): an STree
+    split to depth 1 (8 leaves) whose leaves hold the mixtures of tests/test_checkpoint.py::_models; gzip'd
+    (the reference always stores 10000 nodes)."""
+    import gzip
+    import json
+    import shutil
+    import tempfile
+    from oracle import ckptbind
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_checkpoint as tc
+    rt = ckptbind.RefCheckpointTree(tc.AABB[0], tc.AABB[1], 16)
+    rt.split_to_depth(1)
+    nodes = rt.stored_nodes(rt.size())
+    leaves = [i for i in range(rt.size()) if nodes[i, 4]]
+    seed = 11
+    joint = tc._models(len(leaves), tc.K, seed=seed)
+    for c, i in enumerate(leaves):
+        assert rt.set_leaf_model(i, joint[c]) == 1
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "model_00000.asdmm")
+        rt.save(p)
+        out = os.path.join(ROOT, "tests", "golden", "ref_tree.asdmm.gz")
+        with open(p, "rb") as fi, gzip.GzipFile(out, "wb", mtime=0) as fo:
+            shutil.copyfileobj(fi, fo)
+    with open(out.replace(".asdmm.gz", ".meta.json"), "w") as f:
+        json.dump(dict(nodes=rt.size(), leaves=len(leaves), K=tc.K, seed=seed,
+                       written_by="sdmm::save_json layout via oracle/_ref/libsdmm_ref_ckpt.so (tools/make_golden.py --checkpoint)"), f)
+    print(out, "%.0f KB" % (os.path.getsize(out) / 1e3))
+
+
 if __name__ == "__main__":
+    if "--checkpoint" in sys.argv:
+        make_checkpoint()
+        sys.exit(0)
     assert refbind.available(), "build oracle/_ref first (make -C oracle ref)"
     for name, cfg in INIT_CASES.items():
         make_init(name, *cfg)
