@@ -1087,6 +1087,8 @@ cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st) {
                 case 5: return launch_estep_t<1, 32, 2, 6>(L, st);
                 case 6: return launch_estep_t<1, 32, 4, 3, 1>(L, st);
                 case 7: return launch_estep_t<1, 32, 4, 4, 1>(L, st);
+                case 8: return launch_estep_t<1, 32, 4, 2>(L, st);   // 2 warps per sub-partition, 255 registers
+                case 9: return launch_estep_t<1, 32, 2, 4>(L, st);
                 default: return launch_estep_t<1, 32, 4, 3>(L, st);
             }
         }
