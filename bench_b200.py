@@ -88,8 +88,12 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                 cells.detach_peers()
             exchange = "nccl"
 
+    borrowed = args.binding == "borrowed"
+
     def step():
-        cells.set_samples(point6, weight, off, first_cell=first)
+        # the step's batch of samples: bound zero-copy (the E-step reads the SoA planes in place, like the
+        # reference trains on the swapped-in training_data) or packed into records first (--binding packed)
+        cells.set_samples(point6, weight, off, first_cell=first, borrowed=borrowed)
         cells.em_step(iters, with_conditioner=True)
         if exchange == "peer":
             cells.wait_peers()
@@ -137,7 +141,8 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
         pass
     hbm_src = "MEASURED_PEAKS.json" if hbm_peak else "fallback (B200_PROFILING.md)"
     hbm_peak = hbm_peak or 6650.0
-    hbm_gbs = 32.0 * C_local * N / (est_ms * 1e-3) / 1e9
+    bytes_per_sample = 28.0 if borrowed else 32.0   # SoA planes vs packed records
+    hbm_gbs = bytes_per_sample * C_local * N / (est_ms * 1e-3) / 1e9
     traffic, traffic_src = None, None
     try:
         with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_estep_traffic.json")) as f:
@@ -155,7 +160,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
         share_of_step=estep_ms / ms_per_step if world == 1 else None,
         sfu=dict(achieved_gops=SFU_PER_UPDATE * upd_per_launch / (est_ms * 1e-3) / 1e9, peak_gops=peaks["mufu_gops"]),
         hbm=dict(achieved=hbm_gbs, peak=hbm_peak, unit="GB/s", frac=hbm_gbs / hbm_peak, peak_source=hbm_src,
-                 algorithmic_bytes_per_sample=32),
+                 algorithmic_bytes_per_sample=bytes_per_sample),
         measured_peaks=peaks,
         note="no tensor cores: the contraction is 5-D; flop-based fraction is capped at ~71% by the "
              "instruction mix (72 FP32-pipe lane-ops per 102 algorithmic flop)")
@@ -283,10 +288,12 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                                    % (C_local, "peer-memory stores fused into the M-step kernel" if exchange == "peer"
                                       else "NCCL all-gather")) if world > 1 else ""),
                         exchange=exchange, peer_timeouts=peer_timeouts,
+                        sample_binding="borrowed SoA planes read in place by the E-step (sdmmb_set_samples_borrowed)"
+                        if borrowed else "packed 32-byte records (sdmmb_set_samples: one packing pass per step)",
                         cells=C_total, components=K, samples_per_cell=N, em_iterations=iters,
                         parallelism="cells sharded over %d GPU(s)" % world,
-                        l2_policy="inputs larger than L2 (%.0f MB of packed samples per GPU per iteration)"
-                                  % (32.0 * n_local / 1e6),
+                        l2_policy="inputs larger than L2 (%.0f MB of samples per GPU per iteration)"
+                                  % (bytes_per_sample * n_local / 1e6),
                         model_state="EM state carries over between steps (same work per step)"),
             clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cb,
             queries=queries, progressive_render=render)

@@ -89,6 +89,15 @@ int sdmmb_download_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_j
  * 35 cdf, 36 pmf, 37 psd. */
 int sdmmb_download_derived(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, void* stream);
 
+/* Zero-copy form of sdmmb_set_samples: the E-step reads the caller's planes in place (7 coalesced loads
+ * per sample per EM iteration instead of a packing pass + a second copy), as the reference trains on the
+ * `data` it swapped into `training_data` without copying (volpath_sdmm.cpp:290).  The planes are BORROWED:
+ * they must stay valid and unchanged until the next set_samples* / collect call on this context.  Same
+ * arguments and weight rule (opt/data.h:20-23) as sdmmb_set_samples. */
+int sdmmb_set_samples_borrowed(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d_point6,
+                               size_t plane_stride, const float* d_weight,
+                               const uint32_t* h_cell_offsets, void* stream);
+
 /* Bind the training samples of cells [first_cell, first_cell+n_cells): replaces Data::push_back /
  * the data <-> training_data swap (sdmm/opt/data.h:59-102; volpath_sdmm.cpp:290).  The device
  * variant reads SoA planes already resident in HBM; the host variant copies them first (that copy

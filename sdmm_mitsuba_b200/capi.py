@@ -31,7 +31,7 @@ SYMBOLS = [
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
-    "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
+    "sdmmb_set_samples_borrowed", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
 ]
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
 E_PEER = -9
@@ -98,6 +98,7 @@ def lib():
     L.sdmmb_download_cells.argtypes = [vp, i, i, fp, fp, up, vp]
     L.sdmmb_download_derived.argtypes = [vp, i, i, fp, vp]
     L.sdmmb_set_samples.argtypes = [vp, i, i, fp, sz, fp, up, vp]
+    L.sdmmb_set_samples_borrowed.argtypes = [vp, i, i, fp, sz, fp, up, vp]
     L.sdmmb_set_samples_host.argtypes = [vp, i, i, fp, sz, fp, up, vp]
     L.sdmmb_em_step.argtypes = [vp, i, i, i, i, fp, vp]
     L.sdmmb_optimize_host.argtypes = [vp, i, i, fp, sz, fp, up, i, i, fp, fp, up, vp]

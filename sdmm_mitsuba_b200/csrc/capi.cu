@@ -35,6 +35,10 @@ struct sdmmb_ctx {
     // bound samples
     float4* d_samples = nullptr;
     size_t samples_cap = 0, n_samples = 0;
+    // sdmmb_set_samples_borrowed: the caller's planes, read in place by the E-step (null = packed records)
+    const float* soa_point6 = nullptr;
+    size_t soa_stride = 0;
+    const float* soa_weight = nullptr;
     int bound_first = 0, bound_cells = 0;
     std::vector<uint32_t> h_item_begin;  // [bound_cells+1] item index per bound cell
     EItem* d_items = nullptr;

@@ -314,11 +314,31 @@ __device__ __forceinline__ StepOut<NP> estep_sample(const float2 (&prm)[NP][EREC
     return r;
 }
 
-template <int NP, int LPS, int WARPS, int MINB, bool LL, int MODE>
+// One sample as the kernel stages it: a = (x, y, z, w), b = (dx, dy, dz, w_eff).  SOA reads the caller's
+// planes directly (7 coalesced 4-byte loads per lane per 32-sample chunk) and applies pack_samples_kernel's
+// weight rule on the fly, so the borrowed binding needs no packing pass and no second copy of the samples.
+template <bool SOA>
+__device__ __forceinline__ void load_sample(const float4* __restrict__ samples, const float* __restrict__ p6,
+                                            size_t stride, const float* __restrict__ wt, uint32_t idx,
+                                            float4& a, float4& b) {
+    if constexpr (SOA) {
+        const float w = wt[idx];
+        const float w_eff = (w >= 1e-8f && w <= 3.402823466e+38f) ? w : 0.f;
+        a = make_float4(p6[idx], p6[stride + idx], p6[2 * stride + idx], w);
+        b = make_float4(p6[3 * stride + idx], p6[4 * stride + idx], p6[5 * stride + idx], w_eff);
+    } else {
+        a = samples[2 * (size_t)idx];
+        b = samples[2 * (size_t)idx + 1];
+    }
+}
+
+template <int NP, int LPS, int WARPS, int MINB, bool LL, int MODE, bool SOA = false>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
 em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ items,
                 const float* __restrict__ erec, float* __restrict__ partials,
-                float* __restrict__ item_scal, float* __restrict__ out_loglik) {
+                float* __restrict__ item_scal, float* __restrict__ out_loglik,
+                const float* __restrict__ soa_p6 = nullptr, size_t soa_stride = 0,
+                const float* __restrict__ soa_w = nullptr) {
     constexpr int K = 2 * NP * LPS;
     constexpr int SPW = 32 / LPS;      // samples a warp processes per step
     constexpr int STEPS = 32 / SPW;    // steps per 32-sample chunk
@@ -369,10 +389,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     float4 ra = make_float4(0.f, 0.f, 0.f, 0.f), rb = make_float4(0.f, 0.f, 1.f, 0.f);
     {
         uint32_t idx = item.begin + warp * 32u + lane;
-        if (idx < item.end) {
-            ra = samples[2 * (size_t)idx];
-            rb = samples[2 * (size_t)idx + 1];
-        }
+        if (idx < item.end) load_sample<SOA>(samples, soa_p6, soa_stride, soa_w, idx, ra, rb);
     }
     for (uint32_t round = 0; round < n_rounds; ++round) {
         const uint32_t cbase = item.begin + (round * WARPS + warp) * 32u;
@@ -387,10 +404,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             uint32_t nidx = cbase + WARPS * 32u + lane;
             ra = make_float4(0.f, 0.f, 0.f, 0.f);
             rb = make_float4(0.f, 0.f, 1.f, 0.f);
-            if (nidx < item.end) {
-                ra = samples[2 * (size_t)nidx];
-                rb = samples[2 * (size_t)nidx + 1];
-            }
+            if (nidx < item.end) load_sample<SOA>(samples, soa_p6, soa_stride, soa_w, nidx, ra, rb);
         }
         if constexpr (MODE == 1) {
             // phased: E-step of two samples in lockstep (shared parameter operands), both normaliser
@@ -786,7 +800,8 @@ __global__ void peer_wait_kernel(PeerPush P) {
 // mode bit 1: also write the conditioner's query records
 // mode bit 2: normalise the stored pmf (upload path: prepare_vectorized on a fresh model)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(MSTEP_THREADS)
+template <int MINB>
+__global__ void __launch_bounds__(MSTEP_THREADS, MINB)
 em_mstep_kernel(MStepArgs a) {
     const int K = a.K;
     const int cells_per_cta = MSTEP_THREADS / K;
@@ -1061,7 +1076,8 @@ static cudaError_t launch_estep_tl(const EStepLaunch& L, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    kern<<<L.n_items, WARPS * 32, smem, st>>>(L.samples, L.items, L.erec, L.partials, L.item_scal, L.out_loglik);
+    kern<<<L.n_items, WARPS * 32, smem, st>>>(L.samples, L.items, L.erec, L.partials, L.item_scal, L.out_loglik,
+                                             nullptr, (size_t)0, nullptr);
     return cudaGetLastError();
 }
 
@@ -1071,8 +1087,39 @@ static cudaError_t launch_estep_t(const EStepLaunch& L, cudaStream_t st) {
                         : launch_estep_tl<NP, LPS, WARPS, MINB, false, MODE>(L, st);
 }
 
+// borrowed SoA planes: the default shape of each K only
+template <int NP, int LPS, int WARPS, int MINB, bool LL>
+static cudaError_t launch_estep_soa_l(const EStepLaunch& L, cudaStream_t st) {
+    constexpr int K = 2 * NP * LPS;
+    const size_t smem = (size_t)WARPS * 32 * 32 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
+    auto kern = em_estep_kernel<NP, LPS, WARPS, MINB, LL, 0, true>;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    kern<<<L.n_items, WARPS * 32, smem, st>>>(nullptr, L.items, L.erec, L.partials, L.item_scal, L.out_loglik,
+                                             L.soa_point6, L.soa_stride, L.soa_weight);
+    return cudaGetLastError();
+}
+template <int NP, int LPS, int WARPS, int MINB>
+static cudaError_t launch_estep_soa(const EStepLaunch& L, cudaStream_t st) {
+    return L.out_loglik ? launch_estep_soa_l<NP, LPS, WARPS, MINB, true>(L, st)
+                        : launch_estep_soa_l<NP, LPS, WARPS, MINB, false>(L, st);
+}
+
 cudaError_t launch_estep(const EStepLaunch& L, cudaStream_t st) {
     if (L.n_items == 0) return cudaSuccess;
+    if (L.soa_point6) {
+        switch (L.K) {
+            case 16: return launch_estep_soa<1, 8, 4, 3>(L, st);
+            case 32: return launch_estep_soa<1, 16, 4, 3>(L, st);
+            case 64: return launch_estep_soa<1, 32, 4, 3>(L, st);
+            case 128: return launch_estep_soa<2, 32, 4, 2>(L, st);
+            default: return cudaErrorInvalidValue;
+        }
+    }
     switch (L.K) {
         case 16: return launch_estep_t<1, 8, 4, 3>(L, st);
         case 32: return launch_estep_t<1, 16, 4, 3>(L, st);
@@ -1101,7 +1148,11 @@ cudaError_t launch_mstep(const MStepArgs& a, cudaStream_t st) {
     if (a.n_cells == 0) return cudaSuccess;
     const int cells_per_cta = MSTEP_THREADS / a.K;
     const int grid = (a.n_cells + cells_per_cta - 1) / cells_per_cta;
-    em_mstep_kernel<<<grid, MSTEP_THREADS, 0, st>>>(a);
+    // occupancy of this latency-bound kernel: MINB resident CTAs per SM (register cap 255 / 168 / 128)
+    static const int minb = [] { const char* v = getenv("SDMMB_MSTEP_MINB"); return v ? atoi(v) : 2; }();
+    if (minb >= 4) em_mstep_kernel<4><<<grid, MSTEP_THREADS, 0, st>>>(a);
+    else if (minb == 3) em_mstep_kernel<3><<<grid, MSTEP_THREADS, 0, st>>>(a);
+    else em_mstep_kernel<2><<<grid, MSTEP_THREADS, 0, st>>>(a);
     return cudaGetLastError();
 }
 

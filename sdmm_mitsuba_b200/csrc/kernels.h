@@ -51,6 +51,11 @@ struct EStepLaunch {
     int K;
     int n_items;
     const float4* samples;  // packed records, 2 float4 per sample
+    // borrowed SoA planes instead of packed records (sdmmb_set_samples_borrowed): 6 planes of the
+    // point with `soa_stride` floats between them and the weight plane; null = use `samples`
+    const float* soa_point6;
+    size_t soa_stride;
+    const float* soa_weight;
     const EItem* items;
     const float* erec;
     float* partials;   // [n_items][21][K]

@@ -109,18 +109,23 @@ class SDMMCells:
         return out
 
     # ---- training ---------------------------------------------------------------------------
-    def set_samples(self, point6, weight, cell_offsets, first_cell=0):
-        """point6 [6,N] (x,y,z,dx,dy,dz planes), weight [N], cell_offsets [C+1] (host, u32)."""
+    def set_samples(self, point6, weight, cell_offsets, first_cell=0, borrowed=False):
+        """point6 [6,N] (x,y,z,dx,dy,dz planes), weight [N], cell_offsets [C+1] (host, u32).
+        borrowed=True (device tensors only): zero-copy, the E-step reads the planes in place; they must not
+        change until the next binding (the object keeps them alive)."""
         off = _np(np.asarray(cell_offsets), np.uint32)
         n_cells = off.shape[0] - 1
         if _is_torch(point6):
             assert point6.is_cuda and weight.is_cuda and point6.dtype.is_floating_point
             assert point6.is_contiguous() and weight.is_contiguous() and point6.shape[0] == 6
             self._keep = (point6, weight)
-            check(self._L.sdmmb_set_samples(self._h, first_cell, n_cells, C.c_void_p(point6.data_ptr()),
-                                            point6.shape[1], C.c_void_p(weight.data_ptr()), _hp(off),
-                                            _stream(self.device)), "sdmmb_set_samples", self._h)
+            fn = self._L.sdmmb_set_samples_borrowed if borrowed else self._L.sdmmb_set_samples
+            check(fn(self._h, first_cell, n_cells, C.c_void_p(point6.data_ptr()),
+                     point6.shape[1], C.c_void_p(weight.data_ptr()), _hp(off),
+                     _stream(self.device)), "sdmmb_set_samples", self._h)
         else:
+            if borrowed:
+                raise ValueError("borrowed=True needs device tensors")
             point6 = _np(point6, np.float32)
             weight = _np(weight, np.float32)
             assert point6.shape[0] == 6 and weight.shape[0] == point6.shape[1]

@@ -236,3 +236,47 @@ def test_optimize_host_pipeline_equals_stepwise_calls(K, monkeypatch):
     ja2, _, sa2 = a.download()
     np.testing.assert_array_equal(ja2, jb2)
     np.testing.assert_array_equal(sa2, sb2)
+
+
+@pytest.mark.parametrize("K", [16, 32, 64, 128])
+def test_borrowed_planes_equal_packed_records(K):
+    """sdmmb_set_samples_borrowed: the E-step reading the caller's SoA planes in place must give bit-identical
+    fits and log-likelihoods to the packed-record path, ragged cells and invalid weights (0, < 1e-8, inf, nan:
+    opt/data.h:20-23) included, also for a sub-range of a larger plane set (non-zero first offset)."""
+    import torch
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C = 7
+    sizes = np.array([1500, 0, 33, 2049, 1, 640, 1024])
+    n_pad = 100                                   # the bound range starts inside the planes
+    off = (n_pad + np.concatenate([[0], np.cumsum(sizes)])).astype(np.uint32)
+    total = int(off[-1]) + 50
+    p6, w, _ = _setup(1, K, total, seed=3)[:3]
+    w = w.copy()
+    w[n_pad + 5] = 0.0
+    w[n_pad + 6] = 1e-9
+    w[n_pad + 7] = np.inf
+    w[n_pad + 8] = np.nan
+    joint, em, scal = _setup(C, K, 8, seed=9)[3:]
+    d_p6, d_w = torch.from_numpy(p6).cuda(), torch.from_numpy(w).cuda()
+    out = []
+    for borrowed in (False, True):
+        cells = SDMMCells(C, K)
+        cells.upload(joint, em, scal)
+        cells.set_samples(d_p6, d_w, off, borrowed=borrowed)
+        ll = cells.em_step(3, with_conditioner=True, want_loglik=True)
+        torch.cuda.synchronize()
+        out.append((cells.download(), ll.cpu().numpy(), cells.query_records().clone()))
+    (ja, ea, sa), lla, ra = out[0]
+    (jb, eb, sb), llb, rb = out[1]
+    np.testing.assert_array_equal(ja, jb)
+    np.testing.assert_array_equal(ea, eb)
+    np.testing.assert_array_equal(sa, sb)
+    np.testing.assert_array_equal(lla, llb)
+    assert torch.equal(ra, rb)
+    assert np.isfinite(ja).all()
+    # a packing bind afterwards drops the borrowed planes
+    cells.set_samples(d_p6, d_w, off)
+    d_p6.zero_()
+    cells.em_step(1)
+    torch.cuda.synchronize()
+    assert np.isfinite(cells.download()[0]).all()
