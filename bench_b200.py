@@ -147,6 +147,8 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     try:
         with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_estep_traffic.json")) as f:
             tj = json.load(f)
+        if not borrowed:
+            tj = tj.get("packed", tj)
         traffic = tj["dram_bytes_per_sample"] * C_local * N
         traffic_src = tj["source"]
     except Exception:
