@@ -678,19 +678,24 @@ __device__ inline void write_qrec(float* __restrict__ q, float pmf_a, const floa
 // Sequential Categorical::prepare over the K weights of one cell held in shared memory
 // (R: distributions/categorical.h:86-114).  Called by ONE thread per cell; keeps the reference's
 // left-to-right float32 association order.  Returns validity; on success pmf and cdf are scaled.
-__device__ inline bool categorical_prepare_seq(float* pmf, float* cdf, int K) {
+// Split in two so that only the order-dependent part is serial: ONE thread per cell walks the prefix sum
+// left to right (the float32 association order decides the cdf bits), then EVERY thread scales its own
+// entry by 1/total -- element for element the same operations as the reference's loop.
+__device__ inline float categorical_prefix_seq(const float* pmf, float* cdf, int K) {
     float run = pmf[0];
     cdf[0] = run;
+#pragma unroll 8
     for (int i = 1; i < K; ++i) {
         run += pmf[i];
         cdf[i] = run;
     }
-    if (!(run > 1e-20f)) return false;
-    float inv = 1.f / run;
-    for (int i = 0; i < K; ++i) {
-        cdf[i] *= inv;
-        pmf[i] *= inv;
-    }
+    return run;
+}
+__device__ __forceinline__ bool categorical_scale_own(float* pmf_k, float* cdf_k, float total) {
+    if (!(total > 1e-20f)) return false;
+    const float inv = 1.f / total;
+    *cdf_k *= inv;
+    *pmf_k *= inv;
     return true;
 }
 
@@ -811,6 +816,7 @@ em_mstep_kernel(MStepArgs a) {
     __shared__ float s_cdf[MSTEP_THREADS];
     __shared__ int s_flag[MSTEP_THREADS / 16 + 1];
     __shared__ int s_psd[MSTEP_THREADS / 16 + 1];
+    __shared__ float s_tot[MSTEP_THREADS / 16 + 1];
     const bool active = ci < a.n_cells;
     const int cell = a.first_cell + (active ? ci : 0);
 
@@ -964,9 +970,11 @@ em_mstep_kernel(MStepArgs a) {
     const bool renorm = active && (do_update || (a.mode & 4));
     s_pmf[threadIdx.x] = pmf;
     __syncthreads();
-    if (renorm && k == 0) {
-        bool ok = categorical_prepare_seq(s_pmf + local * K, s_cdf + local * K, K);
-        s_flag[local] = ok ? 0 : 1;
+    if (renorm && k == 0) s_tot[local] = categorical_prefix_seq(s_pmf + local * K, s_cdf + local * K, K);
+    __syncthreads();
+    if (renorm) {
+        const bool ok = categorical_scale_own(&s_pmf[threadIdx.x], &s_cdf[threadIdx.x], s_tot[local]);
+        if (k == 0) s_flag[local] = ok ? 0 : 1;
     }
     __syncthreads();
     ComponentPrep cp;
@@ -993,9 +1001,11 @@ em_mstep_kernel(MStepArgs a) {
         __syncthreads();
         s_pmf[threadIdx.x] = pmf;
         __syncthreads();
-        if (active && k == 0) {
-            bool ok = categorical_prepare_seq(s_pmf + local * K, s_cdf + local * K, K);
-            if (!ok) s_flag[local] |= 2;
+        if (active && k == 0) s_tot[local] = categorical_prefix_seq(s_pmf + local * K, s_cdf + local * K, K);
+        __syncthreads();
+        if (active) {
+            const bool ok = categorical_scale_own(&s_pmf[threadIdx.x], &s_cdf[threadIdx.x], s_tot[local]);
+            if (!ok && k == 0) s_flag[local] |= 2;
         }
         __syncthreads();
         if (active) {
