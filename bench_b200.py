@@ -89,6 +89,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
             exchange = "nccl"
 
     borrowed = args.binding == "borrowed"
+    cells.set_em_overlap(not args.no_overlap)   # M-steps hidden behind the other half's E-steps
 
     def step():
         # the step's batch of samples: bound zero-copy (the E-step reads the SoA planes in place, like the
@@ -120,9 +121,19 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
         dist.barrier()
     ms_local = e0.elapsed_time(e1)
     peer_timeouts = cells.peer_status()[1] if exchange == "peer" else None
+    launches_timed = cells.launch_count() - l0
+    if not args.no_overlap:
+        # per-launch E-step durations need launches that do not queue behind each other: two more (untimed)
+        # steps with the in-order schedule, same kernels on the same data, CUDA events around every E-step
+        cells.set_em_overlap(False)
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
     estep_ms, estep_n = cells.last_estep_ms()
     clocks = sampler.stop() if rank == 0 else None
-    launches = cells.launch_count() - l0
+    launches = launches_timed
     ms_total = _maxreduce(torch, dist, world, ms_local, device)
     ms_per_step = ms_total / args.steps
     updates_per_step = float(C_total) * K * N * iters
@@ -290,6 +301,9 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                                    % (C_local, "peer-memory stores fused into the M-step kernel" if exchange == "peer"
                                       else "NCCL all-gather")) if world > 1 else ""),
                         exchange=exchange, peer_timeouts=peer_timeouts,
+                        schedule="two halves, E-steps alternating on two streams, M-steps on a high-priority stream "
+                                 "(sdmmb_set_em_overlap); roofline E-step durations from two extra in-order steps"
+                        if not args.no_overlap else "in order on one stream",
                         sample_binding="borrowed SoA planes read in place by the E-step (sdmmb_set_samples_borrowed)"
                         if borrowed else "packed 32-byte records (sdmmb_set_samples: one packing pass per step)",
                         cells=C_total, components=K, samples_per_cell=N, em_iterations=iters,

@@ -250,6 +250,14 @@ int sdmmb_collect_samples(sdmmb_ctx* ctx, size_t n, const float* d_point6, size_
  * by sdmmb_em_step (default 0 = train every cell of the range). */
 int sdmmb_set_min_samples(sdmmb_ctx* ctx, uint32_t min_samples);
 
+/* Hide the M-steps of sdmmb_em_step behind E-steps: with overlap enabled the bound range is fitted as two
+ * halves whose E-steps alternate on two internal streams while every M-step (and the peer-memory push of
+ * the last one) runs on a third, high-priority stream; the caller's stream forks into them and joins at the
+ * end, so the call is still stream-ordered for the caller and the results are bit-identical.  The reference
+ * gets the same effect from its thread pool: a cell's M-step runs while other cells are still in their
+ * E-step (volpath_sdmm.cpp:287-311).  Off by default; sdmmb_last_estep_ms reports nothing while it is on. */
+int sdmmb_set_em_overlap(sdmmb_ctx* ctx, int enabled);
+
 /* optimizeAsync (the plugin's default, volpath_sdmm.cpp:180-242, 446-448): the fit of iteration i runs
  * while iteration i+1 is rendered with the PREVIOUS conditioners, which are swapped in by
  * optimize_async_wait_and_update (:227-242).  With async records enabled the fit (sdmmb_em_step /

@@ -31,7 +31,7 @@ SYMBOLS = [
     "sdmmb_set_min_samples", "sdmmb_set_async_records", "sdmmb_publish_records", "sdmmb_query_records", "sdmmb_allgather_records",
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
-    "sdmmb_set_samples_borrowed", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
+    "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
 ]
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
 E_PEER = -9
@@ -117,6 +117,7 @@ def lib():
     L.sdmmb_publish_records.argtypes = [vp, i, i, vp]
     L.sdmmb_query_records.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     L.sdmmb_allgather_records.argtypes = [vp, vp, i, vp]
+    L.sdmmb_set_em_overlap.argtypes = [vp, i]
     L.sdmmb_peer_export.argtypes = [vp, vp]
     L.sdmmb_peer_attach.argtypes = [vp, i, i, vp]
     L.sdmmb_peer_detach.argtypes = [vp]

@@ -73,6 +73,10 @@ struct sdmmb_ctx {
     void* nccl_handle = nullptr;
     int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     int (*nccl_user_rank)(void*, int*) = nullptr;
+    // sdmmb_set_em_overlap: two E-step streams + one high-priority M-step stream, fork/E/M events
+    bool em_overlap = false;
+    cudaStream_t ov_stream[2] = {nullptr, nullptr}, ov_mstream = nullptr;
+    cudaEvent_t ov_ev[5] = {};
     // peer-memory record exchange (capi_part6.inc)
     uint32_t* d_peer_flags = nullptr;   // PEER_FLAG_WORDS words, exported to the peers
     PeerPush peer{};                    // world == 0 until sdmmb_peer_attach
@@ -240,6 +244,10 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch); cudaFree(ctx->d_tree);
     for (void* m : ctx->peer_ipc_opened) cudaIpcCloseMemHandle(m);
     cudaFree(ctx->d_peer_flags);
+    if (ctx->ov_mstream) {
+        cudaStreamDestroy(ctx->ov_stream[0]); cudaStreamDestroy(ctx->ov_stream[1]); cudaStreamDestroy(ctx->ov_mstream);
+        for (cudaEvent_t e : ctx->ov_ev) cudaEventDestroy(e);
+    }
     for (cudaEvent_t e : ctx->ev) cudaEventDestroy(e);
     if (ctx->copy_stream) {
         cudaStreamDestroy(ctx->copy_stream);

@@ -181,6 +181,10 @@ class SDMMCells:
               "sdmmb_em_step", self._h)
         return ll
 
+    def set_em_overlap(self, enabled=True):
+        """Hide em_step's M-steps behind E-steps (two halves on two streams + a high-priority M-step stream)."""
+        check(self._L.sdmmb_set_em_overlap(self._h, 1 if enabled else 0), "sdmmb_set_em_overlap", self._h)
+
     def optimize_host(self, point6, weight, cell_offsets, n_iters, first_cell=0, with_conditioner=True, out=None):
         """The integrator's per-iteration training call for a batch of cells, host buffers in and out
         (volpath_sdmm.cpp:287-311): bind samples -> n_iters x em_step -> conditioner -> fitted mixtures.

@@ -108,3 +108,25 @@ def test_peer_wait_is_bounded_when_a_rank_never_arrives():
     assert torch.equal(b.query_records(), before)
     a.detach_peers()
     assert a.peer_status() == (0, 0)
+
+
+def test_peer_push_with_overlapped_schedule():
+    """em_step's overlapped schedule pushes each half from the (single, in-order) M-step stream: two exchange
+    epochs per call, same records."""
+    import torch
+    ranks, whole = _ranks(24, 64, 700, 2)
+    _attach(ranks)
+    for cells, _ in ranks:
+        cells.set_em_overlap(True)
+    for step in range(2):
+        for cells, st in ranks:
+            with torch.cuda.stream(st):
+                cells.em_step(2, with_conditioner=True)
+        for cells, st in ranks:
+            with torch.cuda.stream(st):
+                cells.wait_peers()
+        whole.em_step(2, with_conditioner=True)
+        torch.cuda.synchronize()
+        for cells, _ in ranks:
+            assert cells.peer_status() == (2 * (step + 1), 0)
+            assert torch.equal(cells.query_records()[:24], whole.query_records()[:24])

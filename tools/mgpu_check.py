@@ -52,13 +52,15 @@ def main():
         cells.query_records().zero_()
         torch.cuda.synchronize()
         dist.barrier()
-        for rep in range(2):   # two epochs: handshake reuse
+        for rep in range(3):   # three calls: handshake reuse; the last one with the overlapped schedule (2 epochs)
+            cells.set_em_overlap(rep == 2)
             cells.upload(joint[first:first + n], em[first:first + n], scal[first:first + n], first_cell=first)
             cells.em_step(3, with_conditioner=True)
             cells.wait_peers()
+        cells.set_em_overlap(False)
         torch.cuda.synchronize()
         ep, timeouts = cells.peer_status()
-        same_p = bool(torch.equal(cells.query_records(), rec)) and ep == 2 and timeouts == 0
+        same_p = bool(torch.equal(cells.query_records(), rec)) and ep == 4 and timeouts == 0
         dist.barrier()
         cells.detach_peers()
     except Exception as e:  # noqa: BLE001
