@@ -63,9 +63,11 @@ struct sdmmb_ctx {
     std::vector<cudaEvent_t> ev;  // pairs around the E-step launches of the last em_step
     int ev_used = 0;
     uint32_t item_samples = 1024;
+    int sm_count = 0;
     // sdmmb_optimize_host pipeline: H2D copy stream, D2H stream, events
     // [0,1] chunk copied, [2,3] chunk packed (staging buffer reusable), [4] entry fence, [5] chunk fitted
     cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
+    cudaStream_t pipe_fit_stream[2] = {nullptr, nullptr};   // optimize_host: alternating chunks
     cudaEvent_t pipe_ev[8] = {};  // [6,7] query_host: chunk's results copied out (staging reusable)
     size_t pipe_chunk_samples = 2u << 20;
     size_t query_chunk = 2u << 20;  // vertices per chunk of the host-buffer query pipeline
@@ -244,6 +246,7 @@ int sdmmb_destroy(sdmmb_ctx* ctx) {
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch); cudaFree(ctx->d_tree);
     for (void* m : ctx->peer_ipc_opened) cudaIpcCloseMemHandle(m);
     cudaFree(ctx->d_peer_flags);
+    for (cudaStream_t ps : ctx->pipe_fit_stream) if (ps) cudaStreamDestroy(ps);
     if (ctx->ov_mstream) {
         cudaStreamDestroy(ctx->ov_stream[0]); cudaStreamDestroy(ctx->ov_stream[1]); cudaStreamDestroy(ctx->ov_mstream);
         for (cudaEvent_t e : ctx->ov_ev) cudaEventDestroy(e);
