@@ -100,7 +100,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-render", action="store_true", help="skip the progressive-render leg")
-    ap.add_argument("--no-overlap", action="store_true", help="run E- and M-steps in order on one stream")
+    ap.add_argument("--overlap", action="store_true",
+                    help="hide the M-steps behind E-steps (sdmmb_set_em_overlap; +0.8 %% at cfg2).  Off by default so "
+                         "that the roofline's per-launch E-step durations come from the timed region itself")
     ap.add_argument("--binding", default="borrowed", choices=["borrowed", "packed"],
                     help="how a step's device-resident samples are bound: zero-copy SoA planes or packed records")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],

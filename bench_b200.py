@@ -89,7 +89,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
             exchange = "nccl"
 
     borrowed = args.binding == "borrowed"
-    cells.set_em_overlap(not args.no_overlap)   # M-steps hidden behind the other half's E-steps
+    cells.set_em_overlap(args.overlap)   # --overlap: M-steps hidden behind the other half's E-steps
 
     def step():
         # the step's batch of samples: bound zero-copy (the E-step reads the SoA planes in place, like the
@@ -122,7 +122,7 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
     ms_local = e0.elapsed_time(e1)
     peer_timeouts = cells.peer_status()[1] if exchange == "peer" else None
     launches_timed = cells.launch_count() - l0
-    if not args.no_overlap:
+    if args.overlap:
         # per-launch E-step durations need launches that do not queue behind each other: two more (untimed)
         # steps with the in-order schedule, same kernels on the same data, CUDA events around every E-step
         cells.set_em_overlap(False)
@@ -303,7 +303,8 @@ def run_b200(args, cfg, rank, world, ClockSampler, make_device_samples, cpu_base
                         exchange=exchange, peer_timeouts=peer_timeouts,
                         schedule="two halves, E-steps alternating on two streams, M-steps on a high-priority stream "
                                  "(sdmmb_set_em_overlap); roofline E-step durations from two extra in-order steps"
-                        if not args.no_overlap else "in order on one stream",
+                        if args.overlap else "in order on one stream (E-step durations: CUDA events around every E-step "
+                                             "launch of the timed region's last step)",
                         sample_binding="borrowed SoA planes read in place by the E-step (sdmmb_set_samples_borrowed)"
                         if borrowed else "packed 32-byte records (sdmmb_set_samples: one packing pass per step)",
                         cells=C_total, components=K, samples_per_cell=N, em_iterations=iters,
