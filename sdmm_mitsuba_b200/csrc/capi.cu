@@ -67,7 +67,8 @@ struct sdmmb_ctx {
     // sdmmb_optimize_host pipeline: H2D copy stream, D2H stream, events
     // [0,1] chunk copied, [2,3] chunk packed (staging buffer reusable), [4] entry fence, [5] chunk fitted
     cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
-    cudaStream_t pipe_fit_stream[2] = {nullptr, nullptr};   // optimize_host: alternating chunks
+    cudaStream_t pipe_fit_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // optimize_host: alternating chunks
+    int pipe_fit_streams = 2;
     cudaEvent_t pipe_ev[8] = {};  // [6,7] query_host: chunk's results copied out (staging reusable)
     size_t pipe_chunk_samples = 2u << 20;
     size_t query_chunk = 2u << 20;  // vertices per chunk of the host-buffer query pipeline
