@@ -47,6 +47,11 @@ struct sdmmb_ctx {
     float* d_partials = nullptr;
     float* d_item_scal = nullptr;
     size_t items_cap = 0, cells_cap = 0, n_items = 0;
+    // layout of the item table currently on the device (build_items skips an identical rebuild)
+    std::vector<uint32_t> items_off;
+    int items_first = -1;
+    uint32_t items_target = 0;
+    bool items_valid = false;
     // staging (grow-only)
     void* d_stage = nullptr;
     size_t stage_cap = 0;

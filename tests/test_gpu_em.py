@@ -317,3 +317,37 @@ def test_overlapped_schedule_is_bit_identical(K, borrowed):
     assert torch.equal(ra, rb)
     np.testing.assert_array_equal(sta, stb)
     assert np.isfinite(ja).all()
+
+
+def test_rebinding_an_identical_layout_reuses_the_item_table():
+    """build_items skips the rebuild when the cell layout is unchanged: new sample values under the same offsets must
+    still be used, and the result must equal a context that was forced to rebuild in between."""
+    import torch
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    K, C = 32, 6
+    sizes = np.array([700, 1300, 0, 2500, 64, 999])
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    other = np.concatenate([[0], np.cumsum(sizes[::-1])]).astype(np.uint32)
+    n = int(off[-1])
+    pa, wa, _ = _setup(1, K, n, seed=21)[:3]
+    pb, wb, _ = _setup(1, K, n, seed=22)[:3]
+    joint, em, scal = _setup(C, K, 8, seed=23)[3:]
+    out = []
+    for force_rebuild in (False, True):
+        for device_tensors in (True, False):
+            cells = SDMMCells(C, K)
+            cells.upload(joint, em, scal)
+            conv = (lambda a: torch.from_numpy(a).cuda()) if device_tensors else (lambda a: a)
+            cells.set_samples(conv(pa), conv(wa), off)
+            cells.em_step(1)
+            if force_rebuild:
+                cells.set_samples(conv(pa), conv(wa), other)
+            cells.set_samples(conv(pb), conv(wb), off)
+            cells.em_step(2)
+            torch.cuda.synchronize()
+            out.append(cells.download())
+    for j, e, s in out[1:]:
+        np.testing.assert_array_equal(j, out[0][0])
+        np.testing.assert_array_equal(e, out[0][1])
+        np.testing.assert_array_equal(s, out[0][2])
+    assert np.isfinite(out[0][0]).all()
