@@ -8,8 +8,17 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libsdmm_b200.so")
-SOURCES = ["capi.cu", "em_kernels.cu", "query_kernels.cu", "tree_kernels.cu", "init_kernels.cu", "render_kernels.cu", "product_kernels.cu", "peaks.cu"]
-HEADERS = ["kernels.h", "sdmm_math.cuh", "capi_part2.inc", "capi_part3.inc", "capi_part4.inc", "capi_part5.inc", "render.h", os.path.join("..", "..", "include", "sdmm_b200_render.h"), os.path.join("..", "..", "include", "sdmm_b200.h")]
+SOURCES = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+
+
+def _deps():
+    """Every file a translation unit can include: stale() compares all of them with the library."""
+    inc = os.path.join(_HERE, "..", "include")
+    out = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".hpp", ".inc"))]
+    out += [os.path.join(inc, f) for f in os.listdir(inc) if f.endswith(".h")]
+    return out
+
+
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
@@ -25,8 +34,7 @@ def stale():
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
-    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    return any(os.path.getmtime(d) > t for d in _deps())
 
 
 def build(force=False, verbose=False):

@@ -29,7 +29,7 @@ struct sdmmb_ctx {
     float* d_em = nullptr;       // [max_cells][81][K]
     uint32_t* d_scal = nullptr;  // [max_cells][8]
     float* d_cdf = nullptr;      // [max_cells][K]
-    float* d_erec = nullptr;     // [max_cells][28][K]
+    float* d_erec = nullptr;     // [max_cells][EREC_PLANES][K]
     float* d_qrec = nullptr;     // [max_cells][K][32]  records the queries (and the all-gather) read
     float* d_qrec_back = nullptr;  // async mode: records the fit writes, published by sdmmb_publish_records
     // bound samples
