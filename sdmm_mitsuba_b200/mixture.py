@@ -93,7 +93,12 @@ class SDMMCells:
         return joint, em, scal
 
     def status(self, first_cell=0, n_cells=None):
-        return self.download(first_cell, n_cells)[2][:, 7].copy()
+        """Per-cell status words of the last training call (ST_* bits; 0 = ok): only the scalars travel."""
+        n = self.max_cells - first_cell if n_cells is None else n_cells
+        scal = np.zeros((n, SCALAR_WORDS), np.uint32)
+        check(self._L.sdmmb_download_cells(self._h, first_cell, n, None, None, _hp(scal), None),
+              "sdmmb_download_cells", self._h)
+        return scal[:, 7].copy()
 
     def derived(self, first_cell=0, n_cells=None):
         n = self.max_cells - first_cell if n_cells is None else n_cells

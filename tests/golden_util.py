@@ -7,7 +7,7 @@ import numpy as np
 from parity import LL_RTOL, PARAM_RTOL, assert_joint_close, loglik_err
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["em_k16", "em_k64", "em_k128"]
+CASES = ["em_k16", "em_k64", "em_k128", "em_k64_n4096", "em_k128_n8192"]
 TIE_DELTA = 2e-5
 
 

@@ -85,36 +85,84 @@ def test_em_step_parity_per_iteration(K, N):
             assert (sg[:, 7] == 0).all()
 
 
-@pytest.mark.parametrize("K,N", [(16, 777), (64, 2048), (128, 1500)])
-def test_em_free_running_parity(K, N):
-    """4 iterations without re-synchronising: fitted parameters within 1e-3 and log-likelihoods
-    within 1e-4 at the 99.9th percentile.  The MAXIMUM over samples is bounded by the spread that two
-    CPU builds of the reference algorithm (oracle/_ref vs oracle port) show between themselves on the
-    same stream (measured ~2e-4: EM amplifies last-bit differences of the fitted parameters at a few
-    tail samples), not by 1e-4."""
-    C, iters = 4, 4
-    point6, weight, off, joint, em, scal = _setup(C, K, N, seed=K)
+def _free_running_with_cause(C, K, N, iters, seed):
+    """`iters` iterations without re-synchronising.  Two float32 implementations of EM drift apart (the two
+    CPU builds of the reference differ by ~2e-4 between themselves at a few tail samples), so the free-running
+    log-likelihoods are held to 1e-4 at the 99.9th percentile and to 1e-3 on the final parameters -- and the
+    CAUSE of everything above 1e-4 is proven instead of assumed: at every iteration the oracle is put into the
+    GPU's OWN state entering that iteration and must reproduce the GPU's per-sample log-likelihoods to 1e-4 at
+    EVERY sample, and the state after the step to 1e-3.  What remains between the free-running trajectories is
+    therefore the parameter drift the tolerance of 1e-3 allows, not an E-step error."""
+    point6, weight, off, joint, em, scal = _setup(C, K, N, seed=seed)
     cells = _gpu_cells(C, K, joint, em, scal)
     cells.set_samples(point6, weight, off)
-    ll_gpu = cells.em_step(iters, with_conditioner=True, want_loglik=True).cpu().numpy()
-    j_gpu, em_gpu, sc_gpu = cells.download()
-    assert (sc_gpu[:, 7] == 0).all(), sc_gpu[:, 7]
-    lls = {}
+    free = {}
     for name, cls in _oracles():
         o = cls(C, K)
         o.set(joint, em, scal)
-        lls[name] = np.concatenate(o.em_step(off, point6, weight, iters, want_loglik=True), axis=1)
-        j, e, s = o.get()
-        assert_joint_close(j_gpu, j, PARAM_RTOL, name)
+        free[name] = (np.concatenate(o.em_step(off, point6, weight, iters, want_loglik=True), axis=1), o.get())
+    ll_gpu = []
+    for it in range(iters):
+        jg, eg, sg = cells.download()                      # the GPU's state entering iteration `it`
+        ll_g = cells.em_step(1, with_conditioner=(it == iters - 1), want_loglik=True).cpu().numpy()[0]
+        ll_gpu.append(ll_g)
+        jg1, eg1, sg1 = cells.download()
+        assert (sg1[:, 7] == 0).all(), sg1[:, 7]
+        for name, cls in _oracles():
+            o = cls(C, K)
+            o.set(jg, eg, sg)
+            ll_o = np.concatenate(o.em_step(off, point6, weight, 1, want_loglik=True), axis=1)[0]
+            err, mism = loglik_err(ll_g, ll_o)
+            assert mism == 0.0 and err <= LL_RTOL, "%s it %d from the GPU's own state: log-likelihood error %.3g" % (name, it, err)
+            j1, _, s1 = o.get()
+            assert_joint_close(jg1, j1, PARAM_RTOL, "%s it %d from the GPU's own state" % (name, it))
+            assert (sg1[:, 1] == s1[:, 1]).all() and (sg1[:, 2] == s1[:, 2]).all(), (name, it)
+    ll_gpu = np.stack(ll_gpu)
+    j_gpu, _, sc_gpu = cells.download()
+    out = {}
+    for name, (ll, (j, e, s)) in free.items():
+        assert_joint_close(j_gpu, j, PARAM_RTOL, name + " free-running")
         assert (sc_gpu[:, 1] == s[:, 1]).all() and (sc_gpu[:, 2] == s[:, 2]).all()
-    spread = 0.0
-    if len(lls) == 2:
-        spread = loglik_err(lls["port"], lls["ref"])[0]
-    for name, ll in lls.items():
-        rel = np.abs(ll_gpu - ll) / np.maximum(1.0, np.abs(ll))
-        assert np.quantile(rel, 0.999) <= LL_RTOL, (name, np.quantile(rel, 0.999))
+        # samples every component underflows at (log 0 = -inf: skipped by the E-step) must be the same ones
+        fin = np.isfinite(ll_gpu) & np.isfinite(ll)
+        assert (np.isfinite(ll_gpu[0]) == np.isfinite(ll[0])).all(), (name, "iteration 0 skip pattern")
+        assert np.mean(np.isfinite(ll_gpu) != np.isfinite(ll)) <= 1e-4, (name, "skip pattern")
+        rel = np.where(fin, np.abs(np.where(fin, ll_gpu, 0) - np.where(fin, ll, 0)) / np.maximum(1.0, np.abs(np.where(fin, ll, 0))), 0.0)
         assert rel[0].max() <= LL_RTOL, (name, "iteration 0", rel[0].max())
-        assert rel.max() <= max(3 * spread, 1e-3), (name, rel.max(), spread)
+        assert np.quantile(rel, 0.999) <= LL_RTOL, (name, np.quantile(rel, 0.999))
+        out[name] = float(rel.max())
+    return out
+
+
+@pytest.mark.parametrize("K,N", [(16, 777), (64, 2048), (128, 1500)])
+def test_em_free_running_parity(K, N):
+    _free_running_with_cause(4, K, N, 4, seed=K)
+
+
+@pytest.mark.parametrize("K,N,C,iters", [(64, 4096, 16, 4), (128, 8192, 8, 2)])
+def test_em_parity_at_bench_shapes(K, N, C, iters):
+    """The per-cell shapes bench.py times -- cfg2: K=64, N=4096, 4 iterations; cfg5: K=128, N=8192 -- against
+    the oracle (sdmm::em_step, sdmm/opt/em.h:218-253): strict per-iteration parity from the oracle's state, then
+    the free-running trajectory with its cause check."""
+    point6, weight, off, joint, em, scal = _setup(C, K, N, seed=100 + K)
+    for name, cls in _oracles():
+        o = cls(C, K)
+        o.set(joint, em, scal)
+        cells = _gpu_cells(C, K, joint, em, scal)
+        cells.set_samples(point6, weight, off)
+        for it in range(iters):
+            j0, e0, s0 = o.get()
+            ll = np.concatenate(o.em_step(off, point6, weight, 1, want_loglik=True), axis=1)[0]
+            j1, e1, s1 = o.get()
+            cells.upload(j0, e0, s0)
+            ll_gpu = cells.em_step(1, with_conditioner=False, want_loglik=True).cpu().numpy()[0]
+            jg, eg, sg = cells.download()
+            err, mism = loglik_err(ll_gpu, ll)
+            assert mism == 0.0 and err <= LL_RTOL, "%s it %d: log-likelihood error %.3g" % (name, it, err)
+            assert_joint_close(jg, j1, PARAM_RTOL, "%s it %d" % (name, it))
+            assert (sg[:, 1] == s1[:, 1]).all() and (sg[:, 2] == s1[:, 2]).all(), (name, it)
+            assert (sg[:, 7] == 0).all()
+    _free_running_with_cause(C, K, N, iters, seed=100 + K)
 
 
 def test_em_ragged_cells_and_item_split():

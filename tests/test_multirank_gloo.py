@@ -72,7 +72,8 @@ def test_balance_by_samples():
 
 def test_bench_reference_arm_two_ranks():
     """Under a 2-rank launch rank 0 alone runs the CPU reference arm and prints ONE JSON line."""
-    env = dict(os.environ, OMP_NUM_THREADS="2")
+    # torchrun forces OMP_NUM_THREADS=1 on its workers: the arm must set its thread count itself
+    env = dict(os.environ, OMP_NUM_THREADS="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
            "--master-addr", "127.0.0.1", "--master-port", str(29600 + os.getpid() % 300),
            os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"]
@@ -83,3 +84,7 @@ def test_bench_reference_arm_two_ranks():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["e2e"]["h2d_bytes_per_step"] == 0
+    n_host = len(os.sched_getaffinity(0))
+    assert d["cpu_baseline"]["cores"] == n_host, (d["cpu_baseline"]["cores"], n_host)
+    if n_host > 1:
+        assert d["cpu_baseline"]["cores"] > 1

@@ -3,5 +3,5 @@ import json
 import sys
 sys.path.insert(0, ".")
 import torch
-import bench_render
+from benchlegs import render_leg as bench_render
 print(json.dumps(bench_render.run_render(torch, cpu=False)))

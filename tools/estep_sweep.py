@@ -15,7 +15,7 @@ def one(K, C, N):
     import numpy as np
     import torch
     sys.path.insert(0, ROOT)
-    from bench import make_device_samples
+    from benchlegs.data import make_device_samples
     from sdmm_mitsuba_b200 import synth
     from sdmm_mitsuba_b200.mixture import SDMMCells
     dev = torch.device("cuda", 0)

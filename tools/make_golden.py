@@ -24,6 +24,9 @@ CASES = {
     "em_k16": (2, 16, 300, 4, 2000),
     "em_k64": (1, 64, 640, 4, 2000),
     "em_k128": (1, 128, 512, 2, 1000),
+    # the per-cell shapes bench.py times (cfg2: K=64, N=4096, 4 iterations; cfg5: K=128, N=8192)
+    "em_k64_n4096": (1, 64, 4096, 4, 500),
+    "em_k128_n8192": (1, 128, 8192, 2, 500),
 }
 
 
@@ -156,6 +159,11 @@ if __name__ == "__main__":
         make_checkpoint()
         sys.exit(0)
     assert refbind.available(), "build oracle/_ref first (make -C oracle ref)"
+    _only = [a for a in sys.argv[1:] if a in CASES]
+    if _only:   # regenerate just the named EM fixtures (leaves every other pinned file untouched)
+        for name in _only:
+            make(name, *CASES[name])
+        sys.exit(0)
     for name, cfg in INIT_CASES.items():
         make_init(name, *cfg)
     if "--init-only" in sys.argv:

@@ -10,7 +10,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from bench import make_device_samples  # noqa: E402
+from benchlegs.data import make_device_samples  # noqa: E402
 from sdmm_mitsuba_b200 import synth  # noqa: E402
 from sdmm_mitsuba_b200.mixture import SDMMCells  # noqa: E402
 

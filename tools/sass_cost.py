@@ -68,6 +68,8 @@ def cost(loop):
         ops[base] += 1
         args = ins[len(op):].split(",")
         srcs = [a.strip() for a in args[1:]]
+        if base == "SHFL":   # SHFL.BFLY PT, Rdst, Rsrc, ...: the first register is the destination
+            srcs = [a.strip() for a in args[2:]]
         wide = base in FMA2
         bank = [0, 0]
         seen = set()
