@@ -18,16 +18,19 @@
 // bank, for all pipes together.  A packed FFMA2 with three register sources reads 3 + 3 (three pairs) or
 // 3 + 2 (pair, 32-bit broadcast, pair) and issues every 3 cycles instead of every 2; only an operand
 // served by the reuse cache (same slot as in the previous instruction), a uniform register or a constant
-// is free, and ptxas decides where reuse happens (source order does not survive its scheduler, basic-block
-// boundaries do not either: profiles/r2_k1/).  Per warp pair-step (64 updates) the loop issues 70 packed
-// FP32 instructions and reads ~358 registers = 179 cycles of register-file time against 147 cycles of FMA
-// pipe time; 211 cycles measured.
-// Round 2 tried the un-centred position block (z = W_pos (x - c) + b with the bias folded into the record,
-// statistics accumulated against the sample's own products and re-centred by the M-step): 64 packed
-// instructions, 329 register reads, 2.94 instead of 3.05 ms per cfg2 launch -- and a covariance error of
-// 1.8e-4 after ONE step (sum g x x^T carries (|mu - c| / sigma)^2 times the float32 rounding of the running
-// sum), 1.3e-3 after four free-running iterations where the reference's own two CPU builds differ by 6.5e-5.
-// Parity is the first gate, so the statistics stay centred per component (profiles/r2_k1/).
+// is free.  ptxas decides where reuse happens (source order does not survive its scheduler, block
+// boundaries do not either: profiles/r2_k1/), so the arithmetic is arranged to READ LESS instead:
+//   * positions are NOT centred per component.  With x' = x - c (c = the cell's mixture centre, one
+//     value per cell) and the bias b = -W_pos (mu - c) folded into the record,
+//         z = W (t_pos, t_dir) = W_pos x' + b + W_dir t_dir,
+//     so 12 of the 15 forward-substitution FMAs take x' as a 32-bit broadcast operand (5 register reads
+//     instead of 6) and the three subtractions x - mu disappear;
+//   * the position block of the statistics is accumulated un-centred against the sample's own
+//     products: sum g, sum g x', sum g x'x'^T (products x'x'^T staged once per sample) and
+//     sum (g t_dir) x'; only the three direction-direction entries multiply two per-lane pairs.
+//     The M-step re-centres them about the component mean in double precision
+//     (sum g (x'-m)(x'-m)^T = U2 - m U1^T - U1 m^T + m m^T U0: exact algebra of R: opt/em.h:57-62).
+// Per pair-step: 64 packed instructions (was 70), 329 register reads (was 358).
 #include "kernels.h"
 
 namespace sdmmb {
@@ -117,12 +120,17 @@ __constant__ float2 kC2[11] = {
     {SDMMB_ACOS_C6, SDMMB_ACOS_C6}, {1.f, 1.f}, {-1.f, -1.f}, {-3.14159265358979323846f, -3.14159265358979323846f},
     {-1.5f, -1.5f}};
 
+// One staged sample: four float4 per-warp shared-memory slots, every value a warp- (or group-)
+// uniform scalar that enters the packed arithmetic as a 32-bit broadcast operand.
+//   q0 = (x', y', z', dx)   q1 = (dy, -dz, w * 2^-64, x'x')   q2 = (x'y', x'z', y'y', y'z')   q3 = (z'z', -, -, -)
+constexpr int SLOT_F4 = 4;
+
 struct PairOut {
-    float2 p;     // pi_k p_k(x) for the two components of the pair
-    float2 t[5];  // tangent coordinates
+    float2 p;       // pi_k p_k(x) for the two components of the pair
+    float2 t3, t4;  // directional tangent coordinates (t4 carries the frame's sign, see below)
 };
 
-// prm: 25 packed parameter pairs (kernels.h: EREC_*).  `ndz` is MINUS the sample's direction z.
+// prm: EREC_REG_PLANES packed parameter pairs (kernels.h: EREC_*).  `ndz` is MINUS the sample's direction z.
 //
 // d_loc = R_to d without the 3x3 matrix.  The frame is always the Duff et al. basis of the unit mean
 // direction n (R: linalg/coordinate_system.h:21-38): rows of R_to are
@@ -136,11 +144,26 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
                                               float2 zz, float2 dx, float2 dy, float2 ndz) {
     PairOut o;
     const float2* F = prm + EREC_ROT;  // nx, ny, -nz, a, sign nx, sign ny
+    const float2* W = prm + EREC_W;
+    const float2* Bz = prm + EREC_B;
     float2 q = fma2(F[1], dy, mul2(F[0], dx));
     float2 lz = fma2(F[2], ndz, q);
     float2 h = fma2(F[3], q, ndz);
     float2 lx = fma2(F[4], h, dx);
     float2 ly = fma2(F[5], h, dy);
+    // position part of z = W_pos x' + b: independent of the acos chain below (the scheduler overlaps them)
+    float2 z0 = fma2(W[0], xx, Bz[0]);
+    float2 z1 = fma2(W[1], xx, Bz[1]);
+    float2 z2 = fma2(W[3], xx, Bz[2]);
+    float2 z3 = fma2(W[6], xx, Bz[3]);
+    float2 z4 = fma2(W[10], xx, Bz[4]);
+    z1 = fma2(W[2], yy, z1);
+    z2 = fma2(W[4], yy, z2);
+    z3 = fma2(W[7], yy, z3);
+    z4 = fma2(W[11], yy, z4);
+    z2 = fma2(W[5], zz, z2);
+    z3 = fma2(W[8], zz, z3);
+    z4 = fma2(W[12], zz, z4);
     float2 a = make_float2(fminf(fabsf(lz.x), SDMMB_ONE_MINUS), fminf(fabsf(lz.y), SDMMB_ONE_MINUS));
     float2 P = fma2(a, kC2[6], kC2[5]);
     P = fma2(P, a, kC2[4]);
@@ -155,30 +178,12 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
     float2 alt = fma2(v, kC2[9], P);  // P - pi*rsqrt(1-a) = -(numerator for c < 0)
     float2 sel = make_float2(lz.x >= 0.f ? P.x : -alt.x, lz.y >= 0.f ? P.y : -alt.y);
     float2 r = mul2(sel, u);  // theta / sin(theta) = inv_jacobian    R: spatio_directional.h:105-110
-    o.t[0] = add2(xx, prm[EREC_NMU + 0]);
-    o.t[1] = add2(yy, prm[EREC_NMU + 1]);
-    o.t[2] = add2(zz, prm[EREC_NMU + 2]);
-    o.t[3] = mul2(lx, r);
-    o.t[4] = mul2(ly, r);
-    // z = W t with W = sqrt(log2(e)/2) * L^-1 (replaces linalg::solve, R: linalg/cholesky.h:38-58),
-    // column by column: the five rows are independent chains and consecutive instructions share t_c
-    // (an operand repeated in the same slot comes from the reuse cache instead of the register file)
-    const float2* W = prm + EREC_W;
-    float2 z0 = mul2(W[0], o.t[0]);
-    float2 z1 = mul2(W[1], o.t[0]);
-    float2 z2 = mul2(W[3], o.t[0]);
-    float2 z3 = mul2(W[6], o.t[0]);
-    float2 z4 = mul2(W[10], o.t[0]);
-    z1 = fma2(W[2], o.t[1], z1);
-    z2 = fma2(W[4], o.t[1], z2);
-    z3 = fma2(W[7], o.t[1], z3);
-    z4 = fma2(W[11], o.t[1], z4);
-    z2 = fma2(W[5], o.t[2], z2);
-    z3 = fma2(W[8], o.t[2], z3);
-    z4 = fma2(W[12], o.t[2], z4);
-    z3 = fma2(W[9], o.t[3], z3);
-    z4 = fma2(W[13], o.t[3], z4);
-    z4 = fma2(W[14], o.t[4], z4);
+    o.t3 = mul2(lx, r);
+    o.t4 = mul2(ly, r);
+    // z = W t with W = sqrt(log2(e)/2) * L^-1 (replaces linalg::solve, R: linalg/cholesky.h:38-58)
+    z3 = fma2(W[9], o.t3, z3);
+    z4 = fma2(W[13], o.t3, z4);
+    z4 = fma2(W[14], o.t4, z4);
     // e = |z|^2 (log2 units);  p = (inv_jac * c_k) * 2^-e                   R: distributions/sdmm.h:292-294, 337
     // The reference integrator runs with FTZ/DAZ (flushDenormals = true, volpath_sdmm.cpp:62, 85-87): its exp
     // result is dead below 2^-126 and so is every product below 2^-126.  ex2.ftz gives 0 for e > 126 whatever
@@ -194,30 +199,42 @@ __device__ __forceinline__ PairOut estep_pair(const float2* __restrict__ prm, fl
     return o;
 }
 
+// 21 statistics per component, in the plane order of the partials (kernels.h ESTAT_*):
+//   s0 = sum g | u1[i] = sum g x'_i | sd[d] = sum g t_d | cov (i >= j, row-major lower triangle):
+//   (i, j < 3) sum g x'_i x'_j;  (3 + d, j < 3) sum g t_d x'_j;  (3 + d, 3 + d') sum g t_d t_d'
 struct PairAcc {
     float2 s0;
     float2 s1[5];
     float2 s2[15];
 };
 
-// Stats::plus_eq (R: opt/em.h:57-62) on the 15 unique covariance entries.
-__device__ __forceinline__ void accumulate_pair(PairAcc& acc, const PairOut& o, float2 ss) {
-    float2 g = mul2(o.p, ss);
+// Stats::plus_eq (R: opt/em.h:57-62) on the 15 unique covariance entries, position block un-centred.
+// q0..q3: the sample's staged slot (broadcast scalars); sc = w_n / sum_k pi_k p_k.
+__device__ __forceinline__ void accumulate_pair(PairAcc& acc, const PairOut& o, float sc, const float4& q0,
+                                                float xx, const float4& q2, float zz) {
+    const float2 g = mul2(o.p, splat(sc));
     acc.s0 = add2(acc.s0, g);
-    float2 gt[5];
-#pragma unroll
-    for (int i = 0; i < 5; ++i) {
-        gt[i] = mul2(g, o.t[i]);
-        acc.s1[i] = add2(acc.s1[i], gt[i]);
-    }
-    int e = 0;
-#pragma unroll
-    for (int i = 0; i < 5; ++i)
-#pragma unroll
-        for (int j = 0; j <= i; ++j) {
-            acc.s2[e] = fma2(gt[i], o.t[j], acc.s2[e]);
-            ++e;
-        }
+    acc.s1[0] = fma2(g, splat(q0.x), acc.s1[0]);
+    acc.s1[1] = fma2(g, splat(q0.y), acc.s1[1]);
+    acc.s1[2] = fma2(g, splat(q0.z), acc.s1[2]);
+    acc.s2[0] = fma2(g, splat(xx), acc.s2[0]);     // (0,0)
+    acc.s2[1] = fma2(g, splat(q2.x), acc.s2[1]);   // (1,0) x'y'
+    acc.s2[2] = fma2(g, splat(q2.z), acc.s2[2]);   // (1,1) y'y'
+    acc.s2[3] = fma2(g, splat(q2.y), acc.s2[3]);   // (2,0) x'z'
+    acc.s2[4] = fma2(g, splat(q2.w), acc.s2[4]);   // (2,1) y'z'
+    acc.s2[5] = fma2(g, splat(zz), acc.s2[5]);     // (2,2)
+    const float2 g3 = mul2(g, o.t3), g4 = mul2(g, o.t4);
+    acc.s1[3] = add2(acc.s1[3], g3);
+    acc.s1[4] = add2(acc.s1[4], g4);
+    acc.s2[6] = fma2(g3, splat(q0.x), acc.s2[6]);   // (3,0..2)
+    acc.s2[7] = fma2(g3, splat(q0.y), acc.s2[7]);
+    acc.s2[8] = fma2(g3, splat(q0.z), acc.s2[8]);
+    acc.s2[9] = fma2(g3, o.t3, acc.s2[9]);          // (3,3)
+    acc.s2[10] = fma2(g4, splat(q0.x), acc.s2[10]); // (4,0..2)
+    acc.s2[11] = fma2(g4, splat(q0.y), acc.s2[11]);
+    acc.s2[12] = fma2(g4, splat(q0.z), acc.s2[12]);
+    acc.s2[13] = fma2(g4, o.t3, acc.s2[13]);        // (4,3)
+    acc.s2[14] = fma2(g4, o.t4, acc.s2[14]);        // (4,4)
 }
 
 // One sample-step of a lane: E-step of all its NP component pairs for the sample at smem slot `si`,
@@ -229,12 +246,11 @@ struct StepOut {
 };
 
 template <int NP>
-__device__ __forceinline__ StepOut<NP> estep_sample(const float2 (&prm)[NP][EREC_PLANES],
+__device__ __forceinline__ StepOut<NP> estep_sample(const float2 (&prm)[NP][EREC_REG_PLANES],
                                                     const float4* __restrict__ wbuf, int si) {
     StepOut<NP> r;
-    // (x, y, z, dx) (dy, -dz, w_eff, -): scalars, splat into both halves of the packed operands so
-    // that the compiler can use the 32-bit broadcast operand form (half the register-file traffic)
-    const float4 A = wbuf[si * 2 + 0], B = wbuf[si * 2 + 1];
+    const float4 A = wbuf[si * SLOT_F4 + 0];
+    const float2 B = *reinterpret_cast<const float2*>(wbuf + si * SLOT_F4 + 1);
 #pragma unroll
     for (int q = 0; q < NP; ++q) {
         r.o[q] = estep_pair(prm[q], splat(A.x), splat(A.y), splat(A.z), splat(A.w), splat(B.x), splat(B.y));
@@ -272,8 +288,8 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     constexpr int SPW = 32 / LPS;      // samples a warp processes per step
     constexpr int STEPS = 32 / SPW;    // steps per 32-sample chunk
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* sbuf = reinterpret_cast<float4*>(smem_raw);                     // [WARPS][32][2] float4
-    float* red = reinterpret_cast<float*>(smem_raw + WARPS * 32 * 32);      // [WARPS][21][K]
+    float4* sbuf = reinterpret_cast<float4*>(smem_raw);                                  // [WARPS][32][SLOT_F4] float4
+    float* red = reinterpret_cast<float*>(smem_raw + WARPS * 32 * SLOT_F4 * 16);         // [WARPS][21][K]
     __shared__ float s_wsum[WARPS];
     __shared__ int s_skip[WARPS];
 
@@ -282,17 +298,17 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     const EItem item = items[blockIdx.x];
 
     // this lane's component parameters -> registers (coalesced over lanes within a plane)
-    float2 prm[NP][EREC_PLANES];
-    {
-        const float* base = erec + (size_t)item.cell * EREC_PLANES * K;
+    float2 prm[NP][EREC_REG_PLANES];
+    const float* base = erec + (size_t)item.cell * EREC_PLANES * K;
 #pragma unroll
-        for (int q = 0; q < NP; ++q)
+    for (int q = 0; q < NP; ++q)
 #pragma unroll
-            for (int pl = 0; pl < EREC_PLANES; ++pl) {
-                prm[q][pl].x = base[pl * K + q * 2 * LPS + l];
-                prm[q][pl].y = base[pl * K + q * 2 * LPS + LPS + l];
-            }
-    }
+        for (int pl = 0; pl < EREC_REG_PLANES; ++pl) {
+            prm[q][pl].x = base[pl * K + q * 2 * LPS + l];
+            prm[q][pl].y = base[pl * K + q * 2 * LPS + LPS + l];
+        }
+    // the cell's centre: positions are staged relative to it
+    const float cx = base[(EREC_CEN + 0) * K], cy = base[(EREC_CEN + 1) * K], cz = base[(EREC_CEN + 2) * K];
     PairAcc acc[NP];
 #pragma unroll
     for (int q = 0; q < NP; ++q) {
@@ -307,15 +323,16 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     int n_wvalid = 0;   // samples with a valid weight                    R: opt/data.h:20-23
     int n_ok = 0;       // samples that contributed (valid weight, finite non-zero normaliser)
 
-    float4* wbuf = sbuf + warp * 32 * 2;
+    float4* wbuf = sbuf + warp * 32 * SLOT_F4;
     const uint32_t n_chunks = (item.end - item.begin + 31u) / 32u;
     // CTA-uniform trip count (every warp runs the same number of rounds; a warp whose chunk lies
     // beyond the item processes 32 zero-weight padding samples).  Keeping the loop bound free of
     // the warp index lets the compiler prove the warp converged at the shuffles below, so the
     // whole round stays one basic block that the scheduler can interleave.
     const uint32_t n_rounds = (n_chunks + WARPS - 1) / WARPS;
-    // register prefetch of this lane's sample of the warp's first chunk; rb.w = effective weight
-    float4 ra = make_float4(0.f, 0.f, 0.f, 0.f), rb = make_float4(0.f, 0.f, 1.f, 0.f);
+    // register prefetch of this lane's sample of the warp's first chunk; rb.w = effective weight.
+    // Padding samples sit at the cell centre with direction +z and weight 0.
+    float4 ra = make_float4(cx, cy, cz, 0.f), rb = make_float4(0.f, 0.f, 1.f, 0.f);
     {
         uint32_t idx = item.begin + warp * 32u + lane;
         if (idx < item.end) load_sample<SOA>(samples, soa_p6, soa_stride, soa_w, idx, ra, rb);
@@ -323,15 +340,19 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     for (uint32_t round = 0; round < n_rounds; ++round) {
         const uint32_t cbase = item.begin + (round * WARPS + warp) * 32u;
         __syncwarp();
-        // per-warp staging slot of a sample: (x, y, z, dx) (dy, -dz, w_eff, -)
-        wbuf[lane * 2 + 0] = make_float4(ra.x, ra.y, ra.z, rb.x);
-        wbuf[lane * 2 + 1] = make_float4(rb.y, -rb.z, rb.w * SDMMB_W_SCALE, 0.f);
+        {   // stage this lane's sample: centred position, its six products, direction, scaled weight
+            const float x = ra.x - cx, y = ra.y - cy, z = ra.z - cz;
+            wbuf[lane * SLOT_F4 + 0] = make_float4(x, y, z, rb.x);
+            wbuf[lane * SLOT_F4 + 1] = make_float4(rb.y, -rb.z, rb.w * SDMMB_W_SCALE, x * x);
+            wbuf[lane * SLOT_F4 + 2] = make_float4(x * y, x * z, y * y, y * z);
+            wbuf[lane * SLOT_F4 + 3] = make_float4(z * z, 0.f, 0.f, 0.f);
+        }
         wsum += ra.w;
         n_wvalid += (rb.w > 0.f) ? 1 : 0;
         __syncwarp();
         {   // prefetch the next chunk while this one is processed
             uint32_t nidx = cbase + WARPS * 32u + lane;
-            ra = make_float4(0.f, 0.f, 0.f, 0.f);
+            ra = make_float4(cx, cy, cz, 0.f);
             rb = make_float4(0.f, 0.f, 1.f, 0.f);
             if (nidx < item.end) load_sample<SOA>(samples, soa_p6, soa_stride, soa_w, nidx, ra, rb);
         }
@@ -347,7 +368,11 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             float sum = cur.sum;
 #pragma unroll
             for (int off = LPS / 2; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-            const float w = reinterpret_cast<const float*>(wbuf + si * 2 + 1)[2];
+            const float4 q0 = wbuf[si * SLOT_F4 + 0];
+            const float2 q1 = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(wbuf + si * SLOT_F4 + 1) + 2);
+            const float4 q2 = wbuf[si * SLOT_F4 + 2];
+            const float zz = reinterpret_cast<const float*>(wbuf + si * SLOT_F4 + 3)[0];
+            const float w = q1.x;
             // hsum; skip if 0 / non-finite                           R: opt/em.h:288-293
             const float rs = rcp_approx(sum);
             const bool ok = (rs > 0.f) && (rs <= 3.402823466e+38f);   // sum finite, > 0, 1/sum finite
@@ -356,14 +381,13 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
             if (LL) {
                 if (l == 0 && cbase + si < item.end) out_loglik[cbase + si] = logf(sum);
             }
-            const float2 ss = splat(sc);
 #pragma unroll
             for (int q = 0; q < NP; ++q) {
                 // a NaN/inf normaliser must not leak 0 * inf into the statistics
                 PairOut o = cur.o[q];
                 o.p.x = ok ? o.p.x : 0.f;
                 o.p.y = ok ? o.p.y : 0.f;
-                accumulate_pair(acc[q], o, ss);
+                accumulate_pair(acc[q], o, sc, q0, q1.y, q2, zz);
             }
             cur = nxt;
         }
@@ -434,7 +458,7 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
 template <int NP, int LPS, int WARPS, int MINB, bool LL, bool SOA>
 static cudaError_t launch_estep_inst(const EStepLaunch& L, cudaStream_t st) {
     constexpr int K = 2 * NP * LPS;
-    const size_t smem = (size_t)WARPS * 32 * 32 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
+    const size_t smem = (size_t)WARPS * 32 * SLOT_F4 * 16 + (size_t)WARPS * ESTAT_PLANES * K * sizeof(float);
     auto kern = em_estep_kernel<NP, LPS, WARPS, MINB, LL, SOA>;
     static bool configured = false;
     if (!configured) {

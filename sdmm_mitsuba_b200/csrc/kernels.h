@@ -11,17 +11,22 @@ constexpr int JOINT_PLANES = 32;
 constexpr int EM_PLANES = 81;
 constexpr int SCALAR_WORDS = 8;
 
-// E-step record: 25 planes of K floats per cell ([cell][plane][K], lanes read consecutive k)
-constexpr int EREC_NMU = 0;   // 3: -mean position
-constexpr int EREC_ROT = 3;   // 6: the Duff frame in factored form: n.x, n.y, -n.z, a = -1/(sign + n.z),
+// E-step record: 30 planes of K floats per cell ([cell][plane][K], lanes read consecutive k).  The E-step
+// stages a sample's position relative to the cell's centre `cen` (the mixture's weighted mean position):
+// z = W (x - mu, t_dir) = W_pos (x - cen) + b + W_dir t_dir.
+constexpr int EREC_B = 0;     // 5: bias b_r = -sum_{c<3} W_rc (mu_c - cen_c)
+constexpr int EREC_ROT = 5;   // 6: the Duff frame in factored form: n.x, n.y, -n.z, a = -1/(sign + n.z),
                               //    sign * n.x, sign * n.y  (sign = copysign(1, n.z)); see estep_pair()
-constexpr int EREC_W = 9;     // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major; the (4,4) entry
+constexpr int EREC_W = 11;    // 15: sqrt(log2(e)/2) * L^-1, lower triangle row-major; the (4,4) entry
                               //    carries the factor `sign` because the kernel works with sign * t_4
-constexpr int EREC_NLC = 24;  // 1: pmf * inv_cov_sqrt_det * (2 pi)^-5/2
-constexpr int EREC_PLANES = 25;
+constexpr int EREC_NLC = 26;  // 1: pmf * inv_cov_sqrt_det * (2 pi)^-5/2
+constexpr int EREC_REG_PLANES = 27;  // planes a lane keeps in registers
+constexpr int EREC_CEN = 27;  // 3: the cell's centre (the same value in all K lanes)
+constexpr int EREC_PLANES = 30;
 
-// E-step partial statistics per item: 21 planes of K floats
-//   0 = sum g, 1..5 = sum g t_i, 6 + i(i+1)/2 + j = sum g t_i t_j (i >= j)
+// E-step partial statistics per item: 21 planes of K floats, position entries UN-centred:
+//   with v = (x - cen, t_dir):  0 = sum g, 1..5 = sum g v_i, 6 + i(i+1)/2 + j = sum g v_i v_j (i >= j);
+//   the M-step re-centres them about the component mean (t_pos = x - mu)
 constexpr int ESTAT_PLANES = 21;
 
 // Query record: 32 floats per component, [cell][k][32] (one 128-byte line per component)

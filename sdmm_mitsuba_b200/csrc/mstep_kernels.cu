@@ -1,6 +1,6 @@
 // mstep_kernels.cu -- the per-component half of the SDMM training path on sm_100a:
-//   K2 em_mstep_kernel         reduction of the E-step partials over a cell's items (fixed order, double
-//                              accumulators), stepwise blend, normalise, update_model,
+//   K2 em_mstep_kernel         reduction of the E-step partials over a cell's items (re-centred about the
+//                              component means in double), stepwise blend, normalise, update_model,
 //                              prepare (Cholesky, E-step records, CDF) and -- fused in its tail --
 //   K3                         the conditioner prepare (Schur complement -> query records) and
 //   K5a                        the record exchange over peer memory (NVLink stores from K3's epilogue)
@@ -32,35 +32,43 @@ __device__ inline void prepare_component(const float mean[6], const float cov[25
     cp.inv_det = 1.f / prod;
 }
 
-// pmf must be the NORMALISED weight (after Categorical::prepare).
+// pmf must be the NORMALISED weight (after Categorical::prepare); cen = the cell's centre (the E-step
+// stages positions relative to it and the record carries the matching bias, see estep_kernels.cu).
 __device__ inline void write_erec(float* __restrict__ erec_cell, int K, int k, float pmf,
-                                  const float mean[6], const ComponentPrep& cp) {
+                                  const float mean[6], const ComponentPrep& cp, const float cen[3]) {
     float W[25];
     inverse_lower_tri<5>(cp.L, W);
     const float scale = 0.84932180028801904272f;  // sqrt(log2(e) / 2)
+    // factored Duff frame of the unit mean direction (rows of cp.to are s, t, n)
+    const float nx = cp.to[6], ny = cp.to[7], nz = cp.to[8];
+    const float sign = copysignf(1.f, nz);
+    float* f = erec_cell + (size_t)EREC_ROT * K + k;
+    f[0 * K] = nx;
+    f[1 * K] = ny;
+    f[2 * K] = -nz;
+    f[3 * K] = -1.f / (sign + nz);
+    f[4 * K] = sign * nx;
+    f[5 * K] = sign * ny;
+    // z = W (x - mu, t_dir) = W_pos (x - cen) + b + W_dir t_dir with b = -W_pos (mu - cen): formed in double from
+    // the float32 entries the E-step multiplies with, rounded once
+    const double m[3] = {(double)mean[0] - (double)cen[0], (double)mean[1] - (double)cen[1],
+                         (double)mean[2] - (double)cen[2]};
+    int e = 0;
 #pragma unroll
-    for (int d = 0; d < 3; ++d) erec_cell[(EREC_NMU + d) * K + k] = -mean[d];
-    {   // factored Duff frame of the unit mean direction (rows of cp.to are s, t, n)
-        const float nx = cp.to[6], ny = cp.to[7], nz = cp.to[8];
-        const float sign = copysignf(1.f, nz);
-        float* f = erec_cell + (size_t)EREC_ROT * K + k;
-        f[0 * K] = nx;
-        f[1 * K] = ny;
-        f[2 * K] = -nz;
-        f[3 * K] = -1.f / (sign + nz);
-        f[4 * K] = sign * nx;
-        f[5 * K] = sign * ny;
-        int e = 0;
+    for (int r = 0; r < 5; ++r) {
+        double b = 0.0;
 #pragma unroll
-        for (int r = 0; r < 5; ++r)
-#pragma unroll
-            for (int c = 0; c <= r; ++c) {
-                const float w = W[r * 5 + c] * scale;
-                erec_cell[(EREC_W + e++) * K + k] = (c == 4) ? sign * w : w;
-            }
+        for (int c = 0; c <= r; ++c) {
+            const float w = W[r * 5 + c] * scale;
+            erec_cell[(EREC_W + e++) * K + k] = (c == 4) ? sign * w : w;
+            if (c < 3) b -= (double)w * m[c];
+        }
+        erec_cell[(EREC_B + r) * K + k] = (float)b;
     }
     // pi_k * inv_det * (2 pi)^-5/2; 0 switches a zero-weight component off
     erec_cell[EREC_NLC * K + k] = pmf * cp.inv_det * gaussian_normalization(5);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) erec_cell[(EREC_CEN + d) * K + k] = cen[d];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -279,6 +287,8 @@ em_mstep_kernel(MStepArgs a) {
     __shared__ int s_flag[MSTEP_THREADS / 16 + 1];
     __shared__ int s_psd[MSTEP_THREADS / 16 + 1];
     __shared__ float s_tot[MSTEP_THREADS / 16 + 1];
+    __shared__ float s_mpos[3][MSTEP_THREADS];           // component mean positions (after the update)
+    __shared__ float s_cen[MSTEP_THREADS / 16 + 1][4];   // per cell: centre of the E-step's position frame
     const bool active = ci < a.n_cells;
     const int cell = a.first_cell + (active ? ci : 0);
 
@@ -316,9 +326,45 @@ em_mstep_kernel(MStepArgs a) {
             weight_sum += a.item_scal[2 * (size_t)it];
             nskip += __float_as_int(a.item_scal[2 * (size_t)it + 1]);
         }
+        // The E-step accumulated the position entries about the cell's centre (v = x - cen), not about the
+        // component mean: with m = mu - cen and t_pos = v - m (exact algebra of Stats::plus_eq, R: opt/em.h:57-62)
+        //   sum g t_i       = U1_i - m_i U0
+        //   sum g t_i t_j   = U2_ij - m_i U1_j - m_j U1_i + m_i m_j U0      (i, j < 3)
+        //   sum g t_d t_j   = C_dj - m_j S1_d                               (d directional, j < 3)
+        // The differences cancel to (component extent / distance to the centre)^2 of their terms: double.
         float bt[ESTAT_PLANES];
+        {
+            const float* er = a.erec + (size_t)cell * EREC_PLANES * K;   // the record the E-step read
+            double m[3];
 #pragma unroll
-        for (int i = 0; i < ESTAT_PLANES; ++i) bt[i] = (float)ut[i];
+            for (int d = 0; d < 3; ++d) m[d] = (double)mean[d] - (double)er[(EREC_CEN + d) * K + k];
+            const double u0 = ut[0];
+            bt[0] = (float)u0;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) bt[1 + i] = (float)(ut[1 + i] - m[i] * u0);
+            bt[4] = (float)ut[4];
+            bt[5] = (float)ut[5];
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j <= i; ++j) {
+                    const int e = 6 + i * (i + 1) / 2 + j;
+                    bt[e] = (float)(ut[e] - m[i] * ut[1 + j] - m[j] * ut[1 + i] + m[i] * m[j] * u0);
+                }
+#pragma unroll
+            for (int d = 3; d < 5; ++d) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const int e = 6 + d * (d + 1) / 2 + j;
+                    bt[e] = (float)(ut[e] - m[j] * ut[1 + d]);
+                }
+#pragma unroll
+                for (int j = 3; j <= d; ++j) {
+                    const int e = 6 + d * (d + 1) / 2 + j;
+                    bt[e] = (float)ut[e];
+                }
+            }
+        }
         {   // the E-step accumulated with sign * t_4 (see estep_pair): undo on the t_4-odd statistics
             const float sgn = copysignf(1.f, mean[5]);
             bt[5] *= sgn;
@@ -434,8 +480,25 @@ em_mstep_kernel(MStepArgs a) {
     // (all __syncthreads() below are at the top level: every thread of the CTA reaches them)
     const bool renorm = active && (do_update || (a.mode & 4));
     s_pmf[threadIdx.x] = pmf;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) s_mpos[d][threadIdx.x] = mean[d];
     __syncthreads();
     if (renorm && k == 0) s_tot[local] = categorical_prefix_seq(s_pmf + local * K, s_cdf + local * K, K);
+    if (active && k >= 1 && k <= 3) {
+        // centre of the cell for the next E-step: the mixture's weighted mean position (any point near
+        // the data does; this one minimises sum_k pi_k |mu_k - cen|^2, the cancellation the un-centred
+        // statistics have to survive).  Serial like the prefix sum next to it, one thread per coordinate.
+        const float* w = s_pmf + local * K;
+        const float* mp = s_mpos[k - 1] + local * K;
+        float num = 0.f, den = 0.f;
+        for (int i = 0; i < K; ++i) {
+            const float wi = (w[i] > 0.f && fabsf(mp[i]) <= 3.402823466e+38f) ? w[i] : 0.f;
+            num = fmaf(wi, mp[i], num);
+            den += wi;
+        }
+        const float c = num / den;
+        s_cen[local][k - 1] = (fabsf(c) <= 3.402823466e+38f) ? c : 0.f;
+    }
     __syncthreads();
     if (renorm) {
         const bool ok = categorical_scale_own(&s_pmf[threadIdx.x], &s_cdf[threadIdx.x], s_tot[local]);
@@ -458,7 +521,7 @@ em_mstep_kernel(MStepArgs a) {
 #pragma unroll
             for (int i = 0; i < 25; ++i) joint[(7 + i) * K + k] = cov[i];
         }
-        write_erec(a.erec + (size_t)cell * EREC_PLANES * K, K, k, pmf, mean, cp);
+        write_erec(a.erec + (size_t)cell * EREC_PLANES * K, K, k, pmf, mean, cp, s_cen[local]);
     }
     if (a.mode & 2) {  // uniform over the CTA
         // sdmm::prepare(conditioner, joint): the marginal copies the joint's (already normalised)
