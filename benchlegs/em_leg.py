@@ -144,7 +144,7 @@ def estep_roofline(S, K, est_ms, n_samples, borrowed, share_of_step, sm_mhz):
         m = rf["per_K"][str(K)]
         sms = rf.get("sms", 148)
         clk = (sm_mhz or peaks.get("sm_mhz") or 1965.0) * 1e6
-        pair_steps_per_smsp = upd / 2.0 / (sms * 4)
+        pair_steps_per_smsp = upd / 64.0 / (sms * 4)   # a warp pair-step = 32 lanes x 2 components x 1 sample
         cyc = est_ms * 1e-3 * clk / pair_steps_per_smsp
         out["instruction_mix"] = dict(
             packed_fp32_per_pair_step=m["packed_per_pair_step"], scalar_fp32_per_pair_step=m["scalar_fp32_per_pair_step"],

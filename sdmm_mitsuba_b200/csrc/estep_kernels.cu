@@ -30,7 +30,11 @@
 //     sum (g t_dir) x'; only the three direction-direction entries multiply two per-lane pairs.
 //     The M-step re-centres them about the component mean in double precision
 //     (sum g (x'-m)(x'-m)^T = U2 - m U1^T - U1 m^T + m m^T U0: exact algebra of R: opt/em.h:57-62).
-// Per pair-step: 64 packed instructions (was 70), 329 register reads (was 358).
+// Per warp pair-step (64 updates): 64 packed instructions (was 70), 329 register reads (was 358) = 165
+// cycles of register-file time against 135 of FMA-pipe time; 204 cycles measured (211 before).
+// Accuracy: measured identical to the centred form on the test and bench batches (profiles/r2_k1/step_noise.txt);
+// sum g x'x'^T carries (|mu - c| / sigma)^2 times the float32 rounding of its running sum, which is why the centre
+// is the mixture's own weighted mean position (the component means of a cell lie within the cell).
 #include "kernels.h"
 
 namespace sdmmb {

@@ -2,7 +2,7 @@
 # round 2, call C: full GPU test list, reference arm, the new bench line (N = 1)
 set -u
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_gpu_em.py -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest all rc=$?"; grep -E "^FAILED|^ERROR|passed|failed" gpurun_out/pytest_gpu.log | tail -20
+timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest all rc=$?"; grep -E "^FAILED|^ERROR|passed|failed" gpurun_out/pytest_gpu.log | tail -20
 timeout 1500 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -25 gpurun_out/bench.err | grep -E "Elapsed|Maximum resident|Error|error|Traceback" ; tail -5 gpurun_out/bench.err
 python - <<'PY'
 import json
