@@ -157,6 +157,18 @@ def parity_block(K, N, iters, point6_np, weight_np, joint, em, scal, device, n_c
         for k, v in _param_errs(jg, j1).items():
             step_par[k] = max(step_par.get(k, 0.0), v)
     j_ref, _, s_ref = o.get()
+    # the reference against ITSELF with every cell's samples in a permuted order: the float32 summation-order
+    # noise of sdmm::em_step on this very data, the yardstick for the free-running differences below
+    rng = np.random.default_rng(0)
+    perm = np.concatenate([c * N + rng.permutation(N) for c in range(C)])
+    inv = np.empty_like(perm)
+    inv[perm] = np.arange(perm.size)
+    o2 = cls(C, K)
+    o2.set(joint, em, scal)
+    ll_perm = np.concatenate(o2.em_step(off, np.ascontiguousarray(point6_np[:, perm]), np.ascontiguousarray(weight_np[perm]),
+                                        iters, want_loglik=True), axis=1)[:, inv]
+    rel_n, _ = ll_err(ll_perm, np.stack(ll_ref_all))
+    noise_par = _param_errs(o2.get()[0], j_ref)
     rel, mism = ll_err(ll_free, np.stack(ll_ref_all))
     free_par = _param_errs(j_free, j_ref)
     cells.close()
@@ -166,5 +178,10 @@ def parity_block(K, N, iters, point6_np, weight_np, joint, em, scal, device, n_c
                               ok=bool(step_ll <= 1e-4 and max(step_par.values()) <= 1e-3)),
                 free_running=dict(ll_err_p999=float(np.quantile(rel, 0.999)), ll_err_max=float(rel.max()),
                                   ll_nonfinite_mismatch=mism, param_err=max(free_par.values()), param_errs=free_par,
-                                  skipped_samples_equal=bool((s_free[:, 2] == s_ref[:, 2]).all())),
+                                  skipped_samples_equal=bool((s_free[:, 2] == s_ref[:, 2]).all()),
+                                  reference_order_noise=dict(
+                                      ll_err_p999=float(np.quantile(rel_n, 0.999)), ll_err_max=float(rel_n.max()),
+                                      param_err=max(noise_par.values()),
+                                      what="the reference against itself with each cell's samples fed in a permuted order "
+                                           "(float32 summation-order noise of sdmm::em_step on the same data)")),
                 note="inputs are the timed batch's own first cells (bit-identical planes on both sides)")

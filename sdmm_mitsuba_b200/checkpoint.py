@@ -33,6 +33,7 @@ sdmm.h:157-160); so does `SDMMCells.upload`.  The EM statistics are NOT part of 
 Checked against the reference's own serializers by tests/test_checkpoint.py (oracle/_ref/libsdmm_ref_ckpt.so)
 and, where that checker cannot travel, against a golden file the reference wrote (tests/golden/ref_tree.asdmm)."""
 import json
+import math
 
 import numpy as np
 
@@ -41,8 +42,16 @@ from .tree import HostTree
 REFERENCE_NODE_COUNT = 10000   # spatial_tree.h:89
 
 
+def _num(v):
+    """nlohmann::json writes a non-finite float as null and rejects bare NaN / Infinity tokens when it parses
+    (Python's json would emit those): one non-finite entry -- a cell flagged ST_NON_PSD, an aborted fit -- must
+    not make the whole .asdmm unreadable by the reference.  The loaders map null back to NaN."""
+    v = float(v)
+    return v if math.isfinite(v) else None
+
+
 def _dyn(plane):
-    return {"data": [float(v) for v in plane], "size": int(len(plane))}
+    return {"data": [_num(v) for v in plane], "size": int(len(plane))}
 
 
 def _planes(planes):
@@ -50,7 +59,7 @@ def _planes(planes):
 
 
 def _vec3(v):
-    return {"data": [float(v[0]), float(v[1]), float(v[2])]}
+    return {"data": [_num(v[0]), _num(v[1]), _num(v[2])]}
 
 
 def _box(amin, amax):
@@ -82,6 +91,17 @@ def mixture_to_json(joint, K=None):
     joint = np.asarray(joint, np.float32)
     K = joint.shape[1] if K is None else int(K)
     j = joint[:, :K]
+    # A component with a non-finite entry (a cell flagged ST_NON_PSD, an aborted fit) has no usable parameters,
+    # and ONE non-finite number makes the whole file unreadable by the reference: nlohmann::json writes it as
+    # null and then refuses to read null as a float.  Such components are written switched off -- weight 0,
+    # direction +z, identity covariance: the convention of this package's padding components.
+    bad = ~np.isfinite(j).all(axis=0)
+    if bad.any():
+        j = j.copy()
+        j[:, bad] = 0.0
+        j[6, bad] = 1.0
+        for i in range(5):
+            j[7 + 6 * i, bad] = 1.0
     to, frm = frames_from_mean_dir(j[4:7])
     return {
         "cov": _planes(j[7:32]),
@@ -140,7 +160,7 @@ def save_asdmm(path, tree, joint_by_slot, K=None, em_by_slot=None, scal_by_slot=
                       "is_leaf": True, "value": None})
     doc = {"m_aabb": _box(tree.amin[0], tree.amax[0]), "m_nodes": nodes}
     with open(path, "w") as f:
-        json.dump(doc, f, indent=indent, sort_keys=True)   # nlohmann's std::map orders keys the same way
+        json.dump(doc, f, indent=indent, sort_keys=True, allow_nan=False)   # nlohmann's std::map orders keys the same way
         f.write("\n")
 
 

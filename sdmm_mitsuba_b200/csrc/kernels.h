@@ -74,10 +74,13 @@ struct EStepLaunch {
 //   [0 .. 7]  ready[r]   : rank r has entered training step `epoch` (its queries of the previous
 //                          step are done, so its records may be overwritten)        -- written by r
 //   [8 .. 15] arrived[r] : rank r's records of step `epoch` are complete here       -- written by r
-//   [16] CTA counter of the pushing launch, [17] timeout error count
+//   [16] CTA counter of the pushing launch
+//   [17] error count: bounded waits of THIS rank that timed out, plus one per step in which a PEER gave up
+//        pushing its records here (written by that peer: the records of its cells are stale on this rank)
+//   [18] "some CTA of the pushing launch timed out waiting for a peer's ready flag" (reset by the last CTA)
 constexpr int PEER_MAX = 8;
 constexpr int PEER_FLAG_WORDS = 32;
-constexpr int PEER_READY = 0, PEER_ARRIVED = 8, PEER_COUNTER = 16, PEER_ERROR = 17;
+constexpr int PEER_READY = 0, PEER_ARRIVED = 8, PEER_COUNTER = 16, PEER_ERROR = 17, PEER_FAIL = 18;
 struct PeerPush {
     int world;                       // 0 = disabled
     int rank;

@@ -214,7 +214,8 @@ __device__ __forceinline__ void peer_push_records(const MStepArgs& a) {
     if (threadIdx.x < P.world && (int)threadIdx.x != P.rank) {
         if (!wait_flag(lf + PEER_READY + threadIdx.x, P.epoch, P.timeout_ms)) {
             atomicAdd(lf + PEER_ERROR, 1u);
-            s_go = 0;
+            atomicExch(lf + PEER_FAIL, 1u);
+            s_go = 0;   // several threads may store the same 0: benign
         }
     }
     __syncthreads();
@@ -247,9 +248,14 @@ __device__ __forceinline__ void peer_push_records(const MStepArgs& a) {
         const uint32_t done = atomicAdd(lf + PEER_COUNTER, 1u);
         if (done == gridDim.x - 1) {   // every CTA's stores are fenced: publish this rank's arrival
             lf[PEER_COUNTER] = 0;
+            // some CTA skipped its stores (a peer never raised its ready flag): the peers hold STALE records of
+            // this rank's cells.  They are told so -- one count in THEIR error word, read by sdmmb_peer_status
+            // on the receiving rank -- before the arrival flag lets their waits through (no 10 s stall per step).
+            const bool failed = atomicExch(lf + PEER_FAIL, 0u) != 0u;
             __threadfence_system();
             for (int pp = 1; pp < P.world; ++pp) {
                 const int p = (P.rank + pp) % P.world;
+                if (failed) atomicAdd_system(P.flags[p] + PEER_ERROR, 1u);
                 st_release_sys(P.flags[p] + PEER_ARRIVED + P.rank, P.epoch);
             }
         }

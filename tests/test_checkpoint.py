@@ -127,6 +127,31 @@ def test_reference_reads_our_file(tmp_path):
     assert (found >= 0).all() and all(tree.is_leaf[i] for i in found)
 
 
+def test_non_finite_entries_do_not_break_the_file(tmp_path):
+    """One NaN / inf in one mixture (a cell flagged ST_NON_PSD, an aborted fit) must not make the whole .asdmm
+    unreadable: nlohmann::json would write null and then refuse to read it back as a float, Python's json would
+    write a bare NaN token.  The writer switches the broken component off instead (weight 0, identity covariance);
+    the reference's own from_json parses the file and every other component is untouched."""
+    ck = _ckpt()
+    tree = _host_tree(1)
+    joint = _models(tree.n_leaves, K)
+    good = joint.copy()
+    joint[0, 7, 1] = np.nan
+    joint[1, 2, 0] = np.inf
+    p = str(tmp_path / "nonfinite.asdmm")
+    checkpoint.save_asdmm(p, tree, joint)
+    text = open(p).read()
+    assert "NaN" not in text and "Infinity" not in text
+    rt = ck.RefCheckpointTree(AABB[0], AABB[1], 16)
+    rt.load(p)                                              # the reference's own from_json parses it
+    nodes = rt.stored_nodes(tree.size())
+    assert all(bool(nodes[i, 0]) == tree.is_leaf[i] for i in range(tree.size()))
+    _, j, _ = checkpoint.load_asdmm(p)
+    assert np.isfinite(j).all()
+    assert (j[:, 0, :] == 0).sum() == 2                     # the two broken components are switched off
+    assert (good[:, 0, :] == 0).sum() == 0
+
+
 def test_we_read_the_references_file(tmp_path):
     ck = _ckpt()
     rt = ck.RefCheckpointTree(AABB[0], AABB[1], 16)

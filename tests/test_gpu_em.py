@@ -85,14 +85,36 @@ def test_em_step_parity_per_iteration(K, N):
             assert (sg[:, 7] == 0).all()
 
 
+def _reference_order_noise(cls, C, K, N, iters, point6, weight, off, joint, em, scal):
+    """Free-running differences of the oracle against ITSELF when every cell's samples are fed in a permuted
+    order: the float32 summation-order noise of sdmm::em_step (same arithmetic, same data).  Returns the 99.9th
+    percentile of the relative log-likelihood difference and the largest parameter difference."""
+    rng = np.random.default_rng(0)
+    perm = np.concatenate([int(off[c]) + rng.permutation(int(off[c + 1] - off[c])) for c in range(C)])
+    inv = np.empty_like(perm)
+    inv[perm] = np.arange(perm.size)
+    a, b = cls(C, K), cls(C, K)
+    a.set(joint, em, scal)
+    b.set(joint, em, scal)
+    lla = np.concatenate(a.em_step(off, point6, weight, iters, want_loglik=True), axis=1)
+    llb = np.concatenate(b.em_step(off, np.ascontiguousarray(point6[:, perm]), np.ascontiguousarray(weight[perm]),
+                                   iters, want_loglik=True), axis=1)[:, inv]
+    fin = np.isfinite(lla) & np.isfinite(llb)
+    rel = np.abs(lla[fin] - llb[fin]) / np.maximum(1.0, np.abs(lla[fin]))
+    return float(np.quantile(rel, 0.999)), max(joint_param_errs(b.get()[0], a.get()[0]).values())
+
+
 def _free_running_with_cause(C, K, N, iters, seed):
-    """`iters` iterations without re-synchronising.  Two float32 implementations of EM drift apart (the two
-    CPU builds of the reference differ by ~2e-4 between themselves at a few tail samples), so the free-running
-    log-likelihoods are held to 1e-4 at the 99.9th percentile and to 1e-3 on the final parameters -- and the
-    CAUSE of everything above 1e-4 is proven instead of assumed: at every iteration the oracle is put into the
-    GPU's OWN state entering that iteration and must reproduce the GPU's per-sample log-likelihoods to 1e-4 at
-    EVERY sample, and the state after the step to 1e-3.  What remains between the free-running trajectories is
-    therefore the parameter drift the tolerance of 1e-3 allows, not an E-step error."""
+    """`iters` iterations without re-synchronising.  A free-running float32 EM trajectory is not reproducible to
+    1e-4 even by the reference itself: feeding oracle/_ref the same samples in a permuted order moves its
+    log-likelihoods by ~1e-4 at the 99.9th percentile and its covariances by ~1.4e-4 after four iterations at
+    K=64, N=4096 (profiles/r2_k1/step_noise.txt) -- the first step from a random model cancels large mean shifts.
+    So (1) the CAUSE of every free-running difference is proven instead of assumed: at every iteration the oracle
+    is put into the GPU's OWN state entering that iteration and must reproduce the GPU's per-sample
+    log-likelihoods to 1e-4 at EVERY sample and the state after the step to 1e-3 -- what remains between the
+    trajectories is parameter drift, not an E-step error; (2) the drift itself is bounded against the
+    reference's own order noise measured on the same data: log-likelihoods at the 99.9th percentile within
+    max(1e-4, 3 x noise), final parameters within max(1e-3, 10 x noise)."""
     point6, weight, off, joint, em, scal = _setup(C, K, N, seed=seed)
     cells = _gpu_cells(C, K, joint, em, scal)
     cells.set_samples(point6, weight, off)
@@ -121,7 +143,9 @@ def _free_running_with_cause(C, K, N, iters, seed):
     j_gpu, _, sc_gpu = cells.download()
     out = {}
     for name, (ll, (j, e, s)) in free.items():
-        assert_joint_close(j_gpu, j, PARAM_RTOL, name + " free-running")
+        cls = dict(_oracles())[name]
+        noise_ll, noise_par = _reference_order_noise(cls, C, K, N, iters, point6, weight, off, joint, em, scal)
+        assert_joint_close(j_gpu, j, max(PARAM_RTOL, 10 * noise_par), name + " free-running")
         assert (sc_gpu[:, 1] == s[:, 1]).all() and (sc_gpu[:, 2] == s[:, 2]).all()
         # samples every component underflows at (log 0 = -inf: skipped by the E-step) must be the same ones
         fin = np.isfinite(ll_gpu) & np.isfinite(ll)
@@ -129,7 +153,7 @@ def _free_running_with_cause(C, K, N, iters, seed):
         assert np.mean(np.isfinite(ll_gpu) != np.isfinite(ll)) <= 1e-4, (name, "skip pattern")
         rel = np.where(fin, np.abs(np.where(fin, ll_gpu, 0) - np.where(fin, ll, 0)) / np.maximum(1.0, np.abs(np.where(fin, ll, 0))), 0.0)
         assert rel[0].max() <= LL_RTOL, (name, "iteration 0", rel[0].max())
-        assert np.quantile(rel, 0.999) <= LL_RTOL, (name, np.quantile(rel, 0.999))
+        assert np.quantile(rel, 0.999) <= max(LL_RTOL, 3 * noise_ll), (name, np.quantile(rel, 0.999), noise_ll)
         out[name] = float(rel.max())
     return out
 

@@ -44,7 +44,7 @@ def test_peer_push_matches_single_context(K, world, C_total):
     import torch
     ranks, whole = _ranks(C_total, K, 512, world)
     _attach(ranks)
-    for step in range(3):  # three exchange epochs: the ready/arrived handshake is reused
+    for step in range(3):  # three exchanges (two epochs each): the ready/arrived handshake is reused
         for cells, st in ranks:
             with torch.cuda.stream(st):
                 cells.em_step(2, with_conditioner=True)
@@ -57,7 +57,7 @@ def test_peer_push_matches_single_context(K, world, C_total):
         assert bool((ref != 0).any())
         for r, (cells, _) in enumerate(ranks):
             ep, timeouts = cells.peer_status()
-            assert (ep, timeouts) == (step + 1, 0)
+            assert (ep, timeouts) == (2 * (step + 1), 0)   # every record-writing call consumes two epochs
             assert torch.equal(cells.query_records()[:C_total], ref), "rank %d step %d" % (r, step)
 
 
@@ -79,7 +79,7 @@ def test_peer_push_from_prepare_conditioner():
     whole.prepare(0, 8)
     torch.cuda.synchronize()
     for cells, _ in ranks:
-        assert cells.peer_status() == (1, 0)
+        assert cells.peer_status() == (2, 0)
         assert torch.equal(cells.query_records()[:8], whole.query_records()[:8])
 
 
@@ -104,8 +104,10 @@ def test_peer_wait_is_bounded_when_a_rank_never_arrives():
         a.wait_peers()                        # ... and never pushes
     torch.cuda.synchronize()
     ep, timeouts = a.peer_status()
-    assert ep == 1 and timeouts >= 2
+    assert ep == 2 and timeouts >= 2
     assert torch.equal(b.query_records(), before)
+    # the receiving rank is told that the records it holds for a's cells are stale (one count per failed step)
+    assert b.peer_status()[1] == 1
     a.detach_peers()
     assert a.peer_status() == (0, 0)
 
@@ -119,6 +121,30 @@ def test_peer_push_with_overlapped_schedule():
     for cells, _ in ranks:
         cells.set_em_overlap(True)
     for step in range(2):
+        for cells, st in ranks:
+            with torch.cuda.stream(st):
+                cells.em_step(2, with_conditioner=True)
+        for cells, st in ranks:
+            with torch.cuda.stream(st):
+                cells.wait_peers()
+        whole.em_step(2, with_conditioner=True)
+        torch.cuda.synchronize()
+        for cells, _ in ranks:
+            assert cells.peer_status() == (2 * (step + 1), 0)
+            assert torch.equal(cells.query_records()[:24], whole.query_records()[:24])
+
+
+def test_peer_epochs_stay_in_step_when_ranks_pick_different_schedules():
+    """One rank fits with the overlapped schedule (two pushes per call), the other in order (one push: what the
+    overlapped schedule also falls back to for a shard of one cell or one item).  Both consume two epochs per
+    call, so ready/arrived flags keep matching over several steps and nobody waits for an epoch that never
+    comes (the epoch counters used to drift apart)."""
+    import torch
+    ranks, whole = _ranks(24, 64, 700, 2)
+    _attach(ranks)
+    ranks[0][0].set_em_overlap(True)
+    ranks[1][0].set_em_overlap(False)
+    for step in range(3):
         for cells, st in ranks:
             with torch.cuda.stream(st):
                 cells.em_step(2, with_conditioner=True)
