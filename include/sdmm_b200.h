@@ -44,7 +44,7 @@ extern "C" {
 #define SDMMB_EM_PLANES 81
 #define SDMMB_SCALAR_WORDS 8
 #define SDMMB_QUERY_RECORD_FLOATS 32 /* per component, 30 used */
-#define SDMMB_ESTEP_RECORD_PLANES 25 /* per component planes of the E-step record */
+#define SDMMB_ESTEP_RECORD_PLANES 30 /* per component planes of the E-step record */
 #define SDMMB_MAX_K 128
 
 /* error codes */
@@ -145,7 +145,12 @@ int sdmmb_copy_cells(sdmmb_ctx* ctx, int n, const int32_t* h_src, const int32_t*
  * update_model (:353-488), prepare_vectorized (sdmm.h:163-173).  If with_conditioner != 0 the
  * last iteration also runs sdmm::prepare(conditioner, sdmm) (sdmm_conditioner.h:89-100).
  * d_out_loglik (nullable): [n_iters][n_total] log sum_k pi_k p_k(x_n) under the model ENTERING
- * each iteration, indexed like the bound samples. */
+ * each iteration, indexed like the bound samples.
+ * n_iters = SDMMB_ITERS_INTEGRATOR applies the integrator's own rule PER CELL on the device
+ * (volpath_sdmm.cpp:299-302: `n_iterations = (em.iterations_run < 4) ? 2 : 1`): two passes, the second of
+ * which only touches the cells that entered the call with iterations_run < 4 (d_out_loglik then holds two
+ * rows; the second row's entries of the other cells are not written). */
+#define SDMMB_ITERS_INTEGRATOR (-1)
 int sdmmb_em_step(sdmmb_ctx* ctx, int first_cell, int n_cells, int n_iters, int with_conditioner,
                   float* d_out_loglik, void* stream);
 
@@ -300,6 +305,19 @@ int sdmmb_peer_attach(sdmmb_ctx* ctx, int rank, int world, const unsigned char* 
 int sdmmb_peer_detach(sdmmb_ctx* ctx);
 int sdmmb_peer_wait(sdmmb_ctx* ctx, void* stream);
 int sdmmb_peer_status(sdmmb_ctx* ctx, uint32_t* out_epoch, uint32_t* out_timeouts, void* stream);
+
+/* Pinned (page-locked) host memory for the host-buffer entry points (sdmmb_optimize_host, sdmmb_*_host): their
+ * chunk pipelines only overlap copies with kernels when the buffers are pinned.  The reference keeps its
+ * samples in enoki DynamicArrays (opt/data.h:25-57); the C++ shim gathers them into such a block. */
+int sdmmb_host_alloc(void** out, size_t bytes);
+int sdmmb_host_free(void* p);
+
+/* Threading (the reference queries from concurrent LocalWorker threads with thread_local scratch,
+ * sdmm_proc.cpp:1086-1106, while optimize() fits, volpath_sdmm.cpp:180-242): every entry point locks its
+ * context, so calls from any number of host threads are safe.  Device-pointer queries enqueued by different
+ * threads on different streams run concurrently on the device (binning scratch is per stream); host-buffer
+ * calls hold the context for their duration.  Queries concurrent with a fit need the double-buffered records
+ * (sdmmb_set_async_records), exactly like the reference's optimizeAsync. */
 
 /* Introspection used by bench.py */
 int sdmmb_launch_count(sdmmb_ctx* ctx, uint64_t* out);           /* kernels launched by this ctx */

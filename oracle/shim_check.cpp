@@ -8,6 +8,8 @@
 // and the two sets of reference objects are compared member by member.
 // Built by oracle/Makefile into oracle/_ref/shim_check (it includes the reference headers, so the
 // binary lives with the other reference-derived artefacts); run by tests/test_gpu_shim.py on the GPU box.
+#include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <memory>
@@ -99,6 +101,24 @@ std::unique_ptr<Context> make_cell(int K, int N, int iterations_run, std::mt1993
     return c;
 }
 
+// RNG that replays caller-supplied uniforms in draw order (SDMM::sample only needs next_float32, sdmm.h:220-240)
+struct ReplayRNG {
+    using Float32 = float;
+    using UInt32 = uint32_t;
+    float draws[3];
+    int next = 0;
+    float next_float32() { return draws[next++ % 3]; }
+};
+// box_mueller_transform(rng.next_float32(), rng.next_float32()) has unspecified argument evaluation order:
+// probe which draw becomes the radius with THIS compiler (the shim takes the uniforms by role)
+bool first_draw_is_radius() {
+    ReplayRNG probe;
+    probe.draws[0] = 0.25f; probe.draws[1] = 0.75f; probe.next = 0;
+    auto [a, b] = sdmm::box_mueller_transform(probe.next_float32(), probe.next_float32());
+    (void)b;
+    return std::abs(a + std::sqrt(-2.f * std::log(1.f - 0.25f))) < 1e-4f;
+}
+
 double max_rel(const Value& a, const Value& b, int K, double floor_) {
     double scale = floor_, err = 0;
     for (int k = 0; k < K; ++k) scale = std::max(scale, (double)std::abs(b.coeff(k)));
@@ -130,15 +150,21 @@ int main(int argc, char** argv) {
         context->initialized = true;
     }
     // (b) the drop-in
+    std::unique_ptr<sdmm_b200::Device> dev_holder;
+    std::vector<Context*> ptrs;
+    for (auto& c : gpu) ptrs.push_back(c.get());
     try {
-        sdmm_b200::Device dev(0, C, K);
-        std::vector<Context*> ptrs;
-        for (auto& c : gpu) ptrs.push_back(c.get());
-        sdmm_b200::optimize(dev, 0, ptrs);
+        dev_holder = std::make_unique<sdmm_b200::Device>(0, C, K);
+        sdmm_b200::bind_default_device(dev_holder.get());
+        auto t0 = std::chrono::steady_clock::now();
+        sdmm_b200::optimize(*dev_holder, 0, ptrs);
+        double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        std::printf("sdmm_b200::optimize: %d cells x %d components, first call (uploads every cell) %.2f ms\n", C, K, ms);
     } catch (const std::exception& e) {
         std::printf("FAIL exception: %s\n", e.what());
         return 2;
     }
+    sdmm_b200::Device& dev = *dev_holder;
     double worst = 0;
     bool ok = true;
     for (int c = 0; c < C; ++c) {
@@ -164,6 +190,116 @@ int main(int argc, char** argv) {
                     e_mean, e_cov, e_stat, e_cond);
         ok = ok && same_counts && e <= 1e-3;
     }
-    std::printf("%s worst %.3e (tolerance 1e-3)\n", ok ? "PASS" : "FAIL", worst);
+    // ---- guided queries: the reference's per-vertex calls against the shim's batch and single-vertex wrappers ----
+    // (create_conditional sdmm_conditioner.h:102-107, SDMM::sample sdmm.h:93-97, posterior sdmm.h:112-113; as
+    // sampleSurface uses them, sdmm_proc.cpp:361-372, 419-421, 539-545).  Both sides query the REFERENCE-fitted
+    // mixtures: the shim's prepare() overload (the reference's parameter list) uploads them and builds the records.
+    {
+        const bool radius_first = first_draw_is_radius();
+        const int per_cell = 200;
+        std::mt19937 gq(7);
+        std::uniform_real_distribution<float> U(0.f, 1.f);
+        sdmm_b200::QueryBatch q;
+        q.resize((size_t)C * per_cell);
+        const size_t n = q.size();
+        sdmm_b200::Device qdev(0, C, K);
+        sdmm_b200::bind_default_device(&qdev);
+        for (int c = 0; c < C; ++c) sdmm_b200::prepare(ref[c]->conditioner, ref[c]->sdmm);
+        std::vector<float> r_dir(3 * n), r_pdf(n), r_ij(n);
+        std::vector<uint32_t> r_comp(n);
+        std::vector<uint8_t> r_ok(n);
+        ConditionalSDMM conditional;
+        Value posterior;
+        for (size_t i = 0; i < n; ++i) {
+            const int c = (int)(i / per_cell);
+            q.slot[i] = (uint32_t)qdev.slot_of(&ref[c]->sdmm);
+            float x[3] = {U(gq), U(gq), U(gq)}, u[3] = {U(gq), U(gq), U(gq)};
+            for (int d = 0; d < 3; ++d) { q.pos3[d * n + i] = x[d]; q.u3[d * n + i] = u[d]; }
+            auto& cell = *ref[c];
+            sdmm::embedded_s_t<MarginalSDMM> condition({x[0], x[1], x[2]});
+            if (enoki::slices(conditional) != enoki::slices(cell.conditioner)) enoki::set_slices(conditional, enoki::slices(cell.conditioner));
+            if (enoki::slices(posterior) != enoki::slices(cell.conditioner)) enoki::set_slices(posterior, enoki::slices(cell.conditioner));
+            r_ok[i] = sdmm::create_conditional(cell.conditioner, condition, conditional) ? 1 : 0;
+            if (!r_ok[i]) continue;
+            ReplayRNG rng;
+            rng.draws[0] = u[0];
+            rng.draws[1] = radius_first ? u[1] : u[2];
+            rng.draws[2] = radius_first ? u[2] : u[1];
+            rng.next = 0;
+            sdmm::embedded_s_t<ConditionalSDMM> embedded;
+            sdmm::tangent_s_t<ConditionalSDMM> tangent;
+            float ij = 0.f;
+            conditional.sample(rng, embedded, ij, tangent);
+            uint32_t idx = enoki::binary_search(0, (uint32_t)enoki::slices(conditional.weight.cdf) - 1,
+                                                [&](uint32_t j) { return conditional.weight.cdf[j] < u[0]; });
+            while (idx > 0 && conditional.weight.pmf[idx] == 0) --idx;
+            enoki::vectorize_safe(VECTORIZE_WRAP_MEMBER(posterior), conditional, embedded, posterior);
+            for (int d = 0; d < 3; ++d) r_dir[d * n + i] = embedded.coeff(d);
+            r_pdf[i] = enoki::hsum_nested(posterior);
+            r_ij[i] = ij;
+            r_comp[i] = idx;
+        }
+        sdmm_b200::sample_pdf(qdev, q, /*binned=*/true);
+        size_t same_comp = 0, n_ok = 0, bad_valid = 0;
+        std::vector<double> rel;
+        for (size_t i = 0; i < n; ++i) {
+            if ((q.valid[i] != 0) != (r_ok[i] != 0)) ++bad_valid;
+            if (!r_ok[i]) continue;
+            ++n_ok;
+            if (q.component[i] == r_comp[i]) {
+                ++same_comp;
+                if (r_pdf[i] > 1e-6f) rel.push_back(std::abs(q.pdf[i] - r_pdf[i]) / r_pdf[i]);
+            }
+        }
+        std::sort(rel.begin(), rel.end());
+        const double med = rel.empty() ? 0 : rel[rel.size() / 2], p99 = rel.empty() ? 0 : rel[rel.size() * 99 / 100];
+        // one vertex through the single-vertex wrapper with the reference's own types
+        sdmm::embedded_s_t<ConditionalSDMM> one_dir;
+        float one_ij = 0.f, one_pdf = 0.f;
+        uint32_t one_comp = 0;
+        sdmm::embedded_s_t<MarginalSDMM> p0({q.pos3[0], q.pos3[n], q.pos3[2 * n]});
+        const bool one_ok = sdmm_b200::sample(ref[0]->conditioner, p0, q.u3[0], q.u3[n], q.u3[2 * n], one_dir, one_ij, one_pdf, &one_comp);
+        const bool one_same = one_ok == (q.valid[0] != 0) && one_comp == q.component[0] && one_pdf == q.pdf[0] && one_ij == q.inv_jacobian[0];
+        const bool q_ok = bad_valid == 0 && same_comp >= n_ok - n_ok / 500 && med < 1e-4 && p99 < 5e-3 && one_same;
+        std::printf("queries: %zu vertices, valid flags differ %zu, same component %zu / %zu, pdf rel err median %.2e p99 %.2e, single-vertex wrapper %s\n",
+                    n, bad_valid, same_comp, n_ok, med, p99, one_same ? "identical" : "DIFFERS");
+        ok = ok && q_ok;
+        sdmm_b200::bind_default_device(&dev);
+    }
+    // ---- a second training iteration: nothing changed on the host since the shim wrote the objects, so no model
+    // is uploaded again (Device residency); new samples, then compare with the reference's second pass ----
+    {
+        for (int c = 0; c < C; ++c) {
+            std::mt19937 g1(900 + c), g2(900 + c);
+            auto fresh_a = make_cell(K, N, 0, g1);
+            auto fresh_b = make_cell(K, N, 0, g2);
+            std::swap(ref[c]->training_data, fresh_a->training_data);
+            std::swap(gpu[c]->training_data, fresh_b->training_data);
+        }
+        for (auto& context : ref) {
+            int n_iterations = (context->em.iterations_run < 4) ? 2 : 1;
+            for (int it = 0; it < n_iterations; ++it) sdmm::em_step(context->sdmm, context->em, context->training_data);
+            enoki::set_slices(context->conditioner, enoki::slices(context->sdmm));
+            sdmm::prepare(context->conditioner, context->sdmm);
+            context->training_data.clear();
+        }
+        auto t0 = std::chrono::steady_clock::now();
+        sdmm_b200::optimize(dev, 0, ptrs);
+        double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        double e2 = 0;
+        bool counts = true;
+        for (int c = 0; c < C; ++c) {
+            auto &a = *gpu[c], &b = *ref[c];
+            for (int r = 0; r < 5; ++r)
+                for (int col = 0; col < 5; ++col) e2 = std::max(e2, max_rel(a.sdmm.cov(r, col), b.sdmm.cov(r, col), K, 1e-3));
+            e2 = std::max(e2, max_rel(a.sdmm.weight.pmf, b.sdmm.weight.pmf, K, 1e-12));
+            counts = counts && a.em.iterations_run == b.em.iterations_run && a.em.samples_seen == b.em.samples_seen;
+        }
+        std::printf("sdmm_b200::optimize: second call (models resident, no upload) %.2f ms, worst %.3e, counters %s\n", ms, e2,
+                    counts ? "equal" : "DIFFER");
+        ok = ok && counts && e2 <= 3e-3;   // two free-running calls: float32 drift of two implementations compounds
+        worst = std::max(worst, e2);
+    }
+    std::printf("%s worst %.3e (tolerance 1e-3 per call)\n", ok ? "PASS" : "FAIL", worst);
     return ok ? 0 : 1;
 }

@@ -32,8 +32,10 @@ SYMBOLS = [
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
     "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
+    "sdmmb_host_alloc", "sdmmb_host_free",
 ]
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
+ITERS_INTEGRATOR = -1    # SDMMB_ITERS_INTEGRATOR: the integrator's 2|1 iteration rule per cell
 E_PEER = -9
 
 

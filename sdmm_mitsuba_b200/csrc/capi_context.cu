@@ -1,160 +1,12 @@
-// capi.cu -- the C ABI of include/sdmm_b200.h: context (device memory owner), marshalling between
-// the flat host layouts and the device layouts, work-item construction, kernel launches.
-// No CPU fallback anywhere: every entry point drives the CUDA kernels of this library.
-#include <dlfcn.h>
-#include <unistd.h>
-
-#include <algorithm>
-#include <cstdlib>
-#include <cstring>
-#include <new>
-#include <string>
-#include <vector>
-
-#include "../../include/sdmm_b200.h"
-#include "../../include/sdmm_b200_render.h"
-#include <cmath>
-#include "kernels.h"
-#include "render.h"
+// capi_context.cu -- the context (device memory owner) of the C ABI of include/sdmm_b200.h: create / destroy,
+// marshalling of the model state between the flat host layouts and the device layouts, parity read-outs,
+// introspection.  No CPU fallback anywhere: every entry point drives the CUDA kernels of this library.
+#include "capi_internal.h"
 
 using namespace sdmmb;
-
-struct sdmmb_ctx {
-    int device = 0;
-    int max_cells = 0;
-    int K_user = 0;  // components as the caller sees them
-    int K = 0;       // padded to 16 / 32 / 64 / 128 with zero-weight components
-    // model state
-    float* d_joint = nullptr;    // [max_cells][32][K]
-    float* d_em = nullptr;       // [max_cells][81][K]
-    uint32_t* d_scal = nullptr;  // [max_cells][8]
-    float* d_cdf = nullptr;      // [max_cells][K]
-    float* d_erec = nullptr;     // [max_cells][EREC_PLANES][K]
-    float* d_qrec = nullptr;     // [max_cells][K][32]  records the queries (and the all-gather) read
-    float* d_qrec_back = nullptr;  // async mode: records the fit writes, published by sdmmb_publish_records
-    // bound samples
-    float4* d_samples = nullptr;
-    size_t samples_cap = 0, n_samples = 0;
-    // sdmmb_set_samples_borrowed: the caller's planes, read in place by the E-step (null = packed records)
-    const float* soa_point6 = nullptr;
-    size_t soa_stride = 0;
-    const float* soa_weight = nullptr;
-    int bound_first = 0, bound_cells = 0;
-    std::vector<uint32_t> h_item_begin;  // [bound_cells+1] item index per bound cell
-    EItem* d_items = nullptr;
-    uint32_t* d_cell_item_begin = nullptr;
-    uint32_t* d_cell_sample_count = nullptr;
-    float* d_partials = nullptr;
-    float* d_item_scal = nullptr;
-    size_t items_cap = 0, cells_cap = 0, n_items = 0;
-    // layout of the item table currently on the device (build_items skips an identical rebuild)
-    std::vector<uint32_t> items_off;
-    int items_first = -1;
-    uint32_t items_target = 0;
-    bool items_valid = false;
-    // staging (grow-only)
-    void* d_stage = nullptr;
-    size_t stage_cap = 0;
-    void* d_stage2 = nullptr;
-    size_t stage2_cap = 0;
-    TreeNode* d_tree = nullptr;  // flattened STree
-    int n_tree_nodes = 0;
-    uint32_t min_samples = 0;    // canBeOptimized threshold applied by the M-step
-    void* d_qscratch = nullptr;  // query binning scratch
-    size_t qscratch_cap = 0;
-    // bookkeeping
-    uint64_t launches = 0;
-    std::string last_cuda_error;
-    std::vector<cudaEvent_t> ev;  // pairs around the E-step launches of the last em_step
-    int ev_used = 0;
-    uint32_t item_samples = 1024;
-    int sm_count = 0;
-    // sdmmb_optimize_host pipeline: H2D copy stream, D2H stream, events
-    // [0,1] chunk copied, [2,3] chunk packed (staging buffer reusable), [4] entry fence, [5] chunk fitted
-    cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
-    cudaStream_t pipe_fit_stream[4] = {nullptr, nullptr, nullptr, nullptr};   // optimize_host: alternating chunks
-    int pipe_fit_streams = 2;
-    cudaEvent_t pipe_ev[8] = {};  // [6,7] query_host: chunk's results copied out (staging reusable)
-    size_t pipe_chunk_samples = 2u << 20;
-    size_t query_chunk = 2u << 20;  // vertices per chunk of the host-buffer query pipeline
-    // nccl (resolved lazily)
-    void* nccl_handle = nullptr;
-    int (*nccl_allgather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
-    int (*nccl_user_rank)(void*, int*) = nullptr;
-    // sdmmb_set_em_overlap: two E-step streams + one high-priority M-step stream, fork/E/M events
-    bool em_overlap = false;
-    cudaStream_t ov_stream[2] = {nullptr, nullptr}, ov_mstream = nullptr;
-    cudaEvent_t ov_ev[5] = {};
-    // peer-memory record exchange (capi_part6.inc)
-    uint32_t* d_peer_flags = nullptr;   // PEER_FLAG_WORDS words, exported to the peers
-    PeerPush peer{};                    // world == 0 until sdmmb_peer_attach
-    uint32_t peer_epoch = 0;            // pushing launches issued so far
-    std::vector<void*> peer_ipc_opened; // mappings to close on detach
-};
+using namespace sdmmb_capi;
 
 namespace {
-
-int pad_k(int k) {
-    if (k <= 16) return 16;
-    if (k <= 32) return 32;
-    if (k <= 64) return 64;
-    return 128;
-}
-
-int cuda_fail(sdmmb_ctx* c, cudaError_t e) {
-    if (c) c->last_cuda_error = cudaGetErrorString(e);
-    return (e == cudaErrorMemoryAllocation) ? SDMMB_E_NOMEM : SDMMB_E_CUDA;
-}
-
-#define CK(call)                                          \
-    do {                                                  \
-        cudaError_t _e = (call);                          \
-        if (_e != cudaSuccess) return cuda_fail(ctx, _e); \
-    } while (0)
-
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) {
-        cudaGetDevice(&prev);
-        if (prev != dev) cudaSetDevice(dev);
-        else prev = -1;
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
-
-int ensure(sdmmb_ctx* ctx, void** p, size_t* cap, size_t bytes) {
-    if (bytes <= *cap) return SDMMB_OK;
-    if (*p) cudaFree(*p);
-    *p = nullptr;
-    *cap = 0;
-    size_t want = bytes + bytes / 8;
-    CK(cudaMalloc(p, want));
-    *cap = want;
-    return SDMMB_OK;
-}
-
-bool range_ok(sdmmb_ctx* ctx, int first, int n) {
-    return first >= 0 && n >= 0 && (long long)first + n <= ctx->max_cells;
-}
-
-MStepArgs base_mstep_args(sdmmb_ctx* ctx, int first_cell, int n_cells, int mode) {
-    MStepArgs a{};
-    a.K = ctx->K;
-    a.first_cell = first_cell;
-    a.n_cells = n_cells;
-    a.mode = mode;
-    a.joint = ctx->d_joint;
-    a.em = ctx->d_em;
-    a.scal = ctx->d_scal;
-    a.cdf = ctx->d_cdf;
-    a.erec = ctx->d_erec;
-    a.qrec = ctx->d_qrec_back ? ctx->d_qrec_back : ctx->d_qrec;
-    a.min_samples = ctx->min_samples;
-    a.peer.world = 0;
-    return a;
-}
 
 // host [cell][planes][K_user] -> padded [cell][planes][K]; `fill` per plane for the padding lanes
 void pad_planes(const float* src, float* dst, int n_cells, int planes, int Ku, int K,
@@ -245,11 +97,13 @@ int sdmmb_create(sdmmb_ctx** out, int device, int max_cells, int K) {
 
 int sdmmb_destroy(sdmmb_ctx* ctx) {
     if (!ctx) return SDMMB_OK;
+    // no lock: the caller guarantees that nothing else uses a context it destroys
     DeviceGuard g(ctx->device);
     cudaFree(ctx->d_joint); cudaFree(ctx->d_em); cudaFree(ctx->d_scal); cudaFree(ctx->d_cdf);
     cudaFree(ctx->d_erec); cudaFree(ctx->d_qrec); cudaFree(ctx->d_qrec_back); cudaFree(ctx->d_samples); cudaFree(ctx->d_items);
     cudaFree(ctx->d_cell_item_begin); cudaFree(ctx->d_cell_sample_count); cudaFree(ctx->d_partials);
     cudaFree(ctx->d_item_scal); cudaFree(ctx->d_stage); cudaFree(ctx->d_stage2); cudaFree(ctx->d_qscratch); cudaFree(ctx->d_tree);
+    for (auto& kv : ctx->qscratch_by_stream) cudaFree(kv.second.p);
     for (void* m : ctx->peer_ipc_opened) cudaIpcCloseMemHandle(m);
     cudaFree(ctx->d_peer_flags);
     for (cudaStream_t ps : ctx->pipe_fit_stream) if (ps) cudaStreamDestroy(ps);
@@ -272,6 +126,7 @@ int sdmmb_upload_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, const float*
     if (!ctx || !h_joint) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int K = ctx->K, Ku = ctx->K_user;
@@ -321,6 +176,7 @@ int sdmmb_download_cells(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_j
     if (!ctx) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int K = ctx->K, Ku = ctx->K_user;
@@ -364,6 +220,7 @@ static int readout38(sdmmb_ctx* ctx, int first_cell, int n_cells, float* h_out, 
     if (!ctx || !h_out) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int K = ctx->K, Ku = ctx->K_user;
@@ -387,6 +244,47 @@ int sdmmb_download_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, floa
     return readout38(ctx, first_cell, n_cells, h_out, stream, true);
 }
 
-}  // extern "C"
 
-#include "capi_part2.inc"
+int sdmmb_host_alloc(void** out, size_t bytes) {
+    if (!out) return SDMMB_E_INVALID;
+    *out = nullptr;
+    if (bytes == 0) return SDMMB_OK;
+    cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocPortable);
+    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? SDMMB_E_NOMEM : SDMMB_E_CUDA; }
+    return SDMMB_OK;
+}
+
+int sdmmb_host_free(void* p) {
+    if (p && cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return SDMMB_E_CUDA; }
+    return SDMMB_OK;
+}
+
+int sdmmb_launch_count(sdmmb_ctx* ctx, uint64_t* out) {
+    if (!ctx || !out) return SDMMB_E_INVALID;
+    *out = ctx->launches;
+    return SDMMB_OK;
+}
+int sdmmb_last_estep_ms(sdmmb_ctx* ctx, float* total_ms, int* n_launches) {
+    if (!ctx || !total_ms) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    float tot = 0.f;
+    for (int i = 0; i < ctx->ev_used; ++i) {
+        CK(cudaEventSynchronize(ctx->ev[2 * i + 1]));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, ctx->ev[2 * i], ctx->ev[2 * i + 1]));
+        tot += ms;
+    }
+    *total_ms = tot;
+    if (n_launches) *n_launches = ctx->ev_used;
+    return SDMMB_OK;
+}
+int sdmmb_measure_peaks(int device, float* out4) {
+    if (!out4) return SDMMB_E_INVALID;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return SDMMB_E_CUDA;
+    DeviceGuard g(device);
+    return measure_peaks(out4) == cudaSuccess ? SDMMB_OK : SDMMB_E_CUDA;
+}
+
+}  // extern "C"

@@ -1,7 +1,13 @@
-// capi_part2.inc -- second half of capi.cu (kept in a separate file only for length): sample
-// binding, em_step, conditioner, queries, NCCL all-gather, introspection.
+// capi_fit.cu -- the training half of the C ABI: sample binding and E-step work items, sdmmb_em_step (in order or
+// with the M-steps hidden behind the other half's E-steps), the host-buffer pipeline sdmmb_optimize_host, the
+// conditioner prepare.  Reference: the parallelFor body of SDMMVolumetricPathTracer::optimize
+// (mitsuba/src/integrators/sdmm/volpath_sdmm.cpp:287-311) and sdmm::em_step (sdmm/opt/em.h:218-253).
+#include "capi_internal.h"
 
-namespace {
+using namespace sdmmb;
+using namespace sdmmb_capi;
+
+namespace sdmmb_capi {
 
 // Build the E-step work items for the bound cells: each cell's samples are cut into runs of at
 // most ctx->item_samples (a multiple of 32) so that (a) huge cells (the renderer caps a cell at
@@ -68,8 +74,7 @@ int build_items(sdmmb_ctx* ctx, int first_cell, int n_cells, const uint32_t* h_o
 }
 
 // Reserve the packed-sample array and build the work items for a cell range (no packing yet).
-int bind_layout(sdmmb_ctx* ctx, int first_cell, int n_cells, const uint32_t* h_off, cudaStream_t st,
-                bool reserve = true) {
+int bind_layout(sdmmb_ctx* ctx, int first_cell, int n_cells, const uint32_t* h_off, cudaStream_t st, bool reserve) {
     const size_t n = (size_t)h_off[n_cells] - h_off[0];
     if (n > 0x7fffffffu) return SDMMB_E_DATA_FULL;
     ctx->soa_point6 = nullptr;   // every binding that packs drops a borrowed one
@@ -89,6 +94,7 @@ int bind_layout(sdmmb_ctx* ctx, int first_cell, int n_cells, const uint32_t* h_o
 
 int bind_common(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d_point6, size_t stride,
                 const float* d_weight, const uint32_t* h_off, cudaStream_t st) {
+    SDMMB_NVTX("sdmmb bind samples (K0)");
     int rc = bind_layout(ctx, first_cell, n_cells, h_off, st);
     if (rc) return rc;
     const size_t n = ctx->n_samples;
@@ -126,14 +132,20 @@ int run_em(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int with_condition
     // peers attached: tell them now (stream-ordered after this rank's queries of the previous step)
     // that this rank's records may be overwritten; the last M-step then stores into theirs
     PeerPush push2[2] = {};
-    if (peer_push && with_conditioner && n_iters > 0) {
+    if (peer_push && with_conditioner && n_iters != 0) {
         int rc = arm_peer_push(ctx, push2, st);
         if (rc) return rc;
     }
     const PeerPush& push = push2[1];
+    // n_iters == SDMMB_ITERS_INTEGRATOR: the integrator's rule, two passes of which the second skips (per cell, on
+    // the device) the cells whose em.iterations_run was already >= 4 (volpath_sdmm.cpp:299-302)
+    const bool rule = (n_iters == SDMMB_ITERS_INTEGRATOR);
+    if (rule) n_iters = 2;
     for (int it = 0; it < n_iters; ++it) {
         EStepLaunch L{};
         L.K = ctx->K;
+        L.scal = ctx->d_scal;
+        L.skip_iterations_ge = (rule && it == 1) ? 5u : 0u;
         L.n_items = (int)(it1 - it0);
         L.samples = ctx->d_samples;
         L.soa_point6 = ctx->soa_point6;
@@ -145,7 +157,10 @@ int run_em(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int with_condition
         L.item_scal = ctx->d_item_scal + (size_t)it0 * 2;
         L.out_loglik = d_out_loglik ? d_out_loglik + (size_t)it * ctx->n_samples : nullptr;
         if (timed) CK(cudaEventRecord(ctx->ev[2 * it], st));
-        CK(launch_estep(L, st));
+        {
+            SDMMB_NVTX("sdmmb E-step (K1)");
+            CK(launch_estep(L, st));
+        }
         if (timed) CK(cudaEventRecord(ctx->ev[2 * it + 1], st));
         if (L.n_items) ctx->launches += 1;
         const bool last = (it == n_iters - 1);
@@ -156,8 +171,12 @@ int run_em(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int with_condition
         a.cell_item_begin = ctx->d_cell_item_begin + rel;
         a.cell_sample_count = ctx->d_cell_sample_count + rel;
         a.item_base = it0;
+        a.skip_iterations_ge = L.skip_iterations_ge;
         if (last && with_conditioner) a.peer = push;
-        CK(launch_mstep(a, st));
+        {
+            SDMMB_NVTX((last && with_conditioner) ? (push.world > 1 ? "sdmmb M-step + conditioner + peer push (K2+K3+K5a)" : "sdmmb M-step + conditioner (K2+K3)") : "sdmmb M-step (K2)");
+            CK(launch_mstep(a, st));
+        }
         ctx->launches += 1;
         if (timed) ctx->ev_used = it + 1;
     }
@@ -241,48 +260,6 @@ int run_em_overlapped(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int wit
     return SDMMB_OK;
 }
 
-int load_nccl(sdmmb_ctx* ctx) {
-    if (ctx->nccl_allgather) return SDMMB_OK;
-    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);  // the copy torch already loaded
-    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
-    if (!h) h = dlopen("libnccl.so", RTLD_NOW);
-    if (!h) return SDMMB_E_NCCL;
-    ctx->nccl_handle = h;
-    ctx->nccl_allgather = (decltype(ctx->nccl_allgather))dlsym(h, "ncclAllGather");
-    ctx->nccl_user_rank = (decltype(ctx->nccl_user_rank))dlsym(h, "ncclCommUserRank");
-    return (ctx->nccl_allgather && ctx->nccl_user_rank) ? SDMMB_OK : SDMMB_E_NCCL;
-}
-
-int query_common(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell, const float* d_pos3, const float* d_u3,
-                 const float* d_dir3, float* d_out_dir3, float* d_out_pdf, float* d_out_ij,
-                 uint32_t* d_out_comp, uint8_t* d_out_valid, int binned, cudaStream_t st) {
-    QueryLaunch q{};
-    q.K = ctx->K;
-    q.n = n;
-    q.qrec = ctx->d_qrec;
-    q.cell_idx = d_cell;
-    q.pos3 = d_pos3;
-    q.u3 = d_u3;
-    q.dir3 = d_dir3;
-    q.out_dir3 = d_out_dir3;
-    q.out_pdf = d_out_pdf;
-    q.out_inv_jac = d_out_ij;
-    q.out_comp = d_out_comp;
-    q.out_valid = d_out_valid;
-    q.binned = binned;
-    q.max_cells = ctx->max_cells;
-    q.scratch = nullptr;
-    if (!binned && n) {
-        // device-side binning scratch: count[B] | cursor[B] | invperm[n] | qin[8n] | qout[8n] (words)
-        int rc = ensure(ctx, &ctx->d_qscratch, &ctx->qscratch_cap, (2 * ((size_t)ctx->max_cells + 1) + 17 * n + 4) * 4);
-        if (rc) return rc;
-        q.scratch = (uint32_t*)ctx->d_qscratch;
-    }
-    CK(launch_query(q, st));
-    if (n) ctx->launches += binned ? 1 : 5;
-    return SDMMB_OK;
-}
-
 int ensure_pipe(sdmmb_ctx* ctx) {
     if (ctx->copy_stream) return SDMMB_OK;
     CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -291,62 +268,7 @@ int ensure_pipe(sdmmb_ctx* ctx) {
     return SDMMB_OK;
 }
 
-// Host-buffer queries, pipelined over chunks of vertices: H2D of chunk c+1 (copy stream) and D2H of
-// chunk c-1 (third stream) overlap the kernels of chunk c.  Host planes have stride n; each chunk is
-// staged as its own dense block:  cell[m] pos[3m] in[3m] | dir[3m] pdf[m] ij[m] comp[m] valid[m bytes].
-int query_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell, const float* h_pos3, const float* h_in3,
-               bool sample, float* h_dir3, float* h_pdf, float* h_ij, uint32_t* h_comp, uint8_t* h_valid,
-               int binned, cudaStream_t st) {
-    int rc = ensure_pipe(ctx);
-    if (rc) return rc;
-    const size_t Q = std::min(n, ctx->query_chunk);
-    const size_t block = (Q * (14 * 4) + Q + 255) & ~(size_t)255;
-    rc = ensure(ctx, &ctx->d_stage2, &ctx->stage2_cap, 2 * block);
-    if (rc) return rc;
-    cudaEvent_t* copied = ctx->pipe_ev;        // [0,1]
-    cudaEvent_t* computed = ctx->pipe_ev + 2;  // [2,3]
-    cudaEvent_t* drained = ctx->pipe_ev + 6;   // [6,7]
-    CK(cudaEventRecord(ctx->pipe_ev[4], st));
-    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->pipe_ev[4], 0));
-    size_t c = 0;
-    for (size_t off = 0; off < n; off += Q, ++c) {
-        const size_t m = std::min(Q, n - off);
-        const int buf = (int)(c & 1);
-        float* f = (float*)((unsigned char*)ctx->d_stage2 + (size_t)buf * block);
-        uint32_t* d_cell = (uint32_t*)f;
-        float *d_pos = f + m, *d_in = f + 4 * m, *d_dir = f + 7 * m, *d_pdf = f + 10 * m, *d_ij = f + 11 * m;
-        uint32_t* d_comp = (uint32_t*)(f + 12 * m);
-        uint8_t* d_valid = (uint8_t*)(f + 13 * m);
-        if (c >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, drained[buf], 0));
-        CK(cudaMemcpyAsync(d_cell, h_cell + off, m * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
-        for (int p = 0; p < 3; ++p) {
-            CK(cudaMemcpyAsync(d_pos + p * m, h_pos3 + p * n + off, m * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
-            CK(cudaMemcpyAsync(d_in + p * m, h_in3 + p * n + off, m * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
-        }
-        CK(cudaEventRecord(copied[buf], ctx->copy_stream));
-        CK(cudaStreamWaitEvent(st, copied[buf], 0));
-        if (sample) rc = query_common(ctx, m, d_cell, d_pos, d_in, nullptr, d_dir, d_pdf, d_ij, d_comp, d_valid, binned, st);
-        else rc = query_common(ctx, m, d_cell, d_pos, nullptr, d_in, nullptr, d_pdf, nullptr, nullptr, d_valid, binned, st);
-        if (rc) return rc;
-        CK(cudaEventRecord(computed[buf], st));
-        CK(cudaStreamWaitEvent(ctx->d2h_stream, computed[buf], 0));
-        if (sample) {
-            for (int p = 0; p < 3; ++p)
-                CK(cudaMemcpyAsync(h_dir3 + p * n + off, d_dir + p * m, m * 4, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-            CK(cudaMemcpyAsync(h_ij + off, d_ij, m * 4, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-            CK(cudaMemcpyAsync(h_comp + off, d_comp, m * 4, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-        }
-        CK(cudaMemcpyAsync(h_pdf + off, d_pdf, m * 4, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-        if (h_valid) CK(cudaMemcpyAsync(h_valid + off, d_valid, m, cudaMemcpyDeviceToHost, ctx->d2h_stream));
-        CK(cudaEventRecord(drained[buf], ctx->d2h_stream));
-    }
-    CK(cudaStreamSynchronize(st));
-    CK(cudaStreamSynchronize(ctx->copy_stream));
-    CK(cudaStreamSynchronize(ctx->d2h_stream));
-    return SDMMB_OK;
-}
-
-}  // namespace
+}  // namespace sdmmb_capi
 
 extern "C" {
 
@@ -357,6 +279,7 @@ int sdmmb_set_samples(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* 
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     for (int c = 0; c < n_cells; ++c)
         if (h_cell_offsets[c + 1] < h_cell_offsets[c]) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     return bind_common(ctx, first_cell, n_cells, d_point6, plane_stride, d_weight, h_cell_offsets,
                        (cudaStream_t)stream);
@@ -369,6 +292,7 @@ int sdmmb_set_samples_borrowed(sdmmb_ctx* ctx, int first_cell, int n_cells, cons
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     for (int c = 0; c < n_cells; ++c)
         if (h_cell_offsets[c + 1] < h_cell_offsets[c]) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     int rc = bind_layout(ctx, first_cell, n_cells, h_cell_offsets, (cudaStream_t)stream, false);
     if (rc) return rc;
@@ -385,6 +309,7 @@ int sdmmb_set_samples_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const fl
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     for (int c = 0; c < n_cells; ++c)
         if (h_cell_offsets[c + 1] < h_cell_offsets[c]) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const uint32_t b = h_cell_offsets[0];
@@ -403,15 +328,16 @@ int sdmmb_set_samples_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const fl
 
 int sdmmb_em_step(sdmmb_ctx* ctx, int first_cell, int n_cells, int n_iters, int with_conditioner,
                   float* d_out_loglik, void* stream) {
-    if (!ctx || n_iters < 0) return SDMMB_E_INVALID;
+    if (!ctx || (n_iters < 0 && n_iters != SDMMB_ITERS_INTEGRATOR)) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (first_cell < ctx->bound_first || first_cell + n_cells > ctx->bound_first + ctx->bound_cells)
         return SDMMB_E_STATE;
     if (n_cells == 0 || n_iters == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int rel = first_cell - ctx->bound_first;
-    while ((int)ctx->ev.size() < 2 * n_iters) {
+    while ((int)ctx->ev.size() < 2 * std::max(n_iters, 2)) {
         cudaEvent_t e;
         CK(cudaEventCreate(&e));
         ctx->ev.push_back(e);
@@ -432,13 +358,16 @@ int sdmmb_optimize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const float
                         size_t plane_stride, const float* h_weight, const uint32_t* h_cell_offsets,
                         int n_iters, int with_conditioner, float* h_out_joint, float* h_out_em,
                         uint32_t* h_out_scal, void* stream) {
-    if (!ctx || !h_point6 || !h_weight || !h_cell_offsets || n_iters < 0) return SDMMB_E_INVALID;
+    if (!ctx || !h_point6 || !h_weight || !h_cell_offsets || (n_iters < 0 && n_iters != SDMMB_ITERS_INTEGRATOR))
+        return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     for (int c = 0; c < n_cells; ++c)
         if (h_cell_offsets[c + 1] < h_cell_offsets[c]) return SDMMB_E_INVALID;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
+    SDMMB_NVTX("sdmmb_optimize_host");
     const int K = ctx->K;
     const bool direct_out = (ctx->K_user == K);
     {
@@ -507,7 +436,7 @@ int sdmmb_optimize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const float
         }
         CK(cudaEventRecord(copied, ctx->copy_stream));
         CK(cudaStreamWaitEvent(st, copied, 0));
-        if (n_iters > 0) {
+        if (n_iters != 0) {
             rc = run_em(ctx, c0, c1 - c0, n_iters, with_conditioner, nullptr, false, st);
             if (rc) return rc;
         }
@@ -545,6 +474,7 @@ int sdmmb_prepare_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, void*
     if (!ctx) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     MStepArgs a = base_mstep_args(ctx, first_cell, n_cells, 2);
     PeerPush push2[2] = {};
@@ -556,215 +486,11 @@ int sdmmb_prepare_conditioner(sdmmb_ctx* ctx, int first_cell, int n_cells, void*
     return SDMMB_OK;
 }
 
-int sdmmb_sample_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
-                     const float* d_u3, float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
-                     uint32_t* d_out_comp, uint8_t* d_out_valid, int binned, void* stream) {
-    if (!ctx || (n && (!d_cell_idx || !d_pos3 || !d_u3 || !d_out_dir3 || !d_out_pdf || !d_out_inv_jac || !d_out_comp)))
-        return SDMMB_E_INVALID;
-    DeviceGuard g(ctx->device);
-    return query_common(ctx, n, d_cell_idx, d_pos3, d_u3, nullptr, d_out_dir3, d_out_pdf, d_out_inv_jac,
-                        d_out_comp, d_out_valid, binned, (cudaStream_t)stream);
-}
-
-int sdmmb_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
-              const float* d_dir3, float* d_out_pdf, uint8_t* d_out_valid, int binned, void* stream) {
-    if (!ctx || (n && (!d_cell_idx || !d_pos3 || !d_dir3 || !d_out_pdf))) return SDMMB_E_INVALID;
-    DeviceGuard g(ctx->device);
-    return query_common(ctx, n, d_cell_idx, d_pos3, nullptr, d_dir3, nullptr, d_out_pdf, nullptr, nullptr,
-                        d_out_valid, binned, (cudaStream_t)stream);
-}
-
-int sdmmb_sample_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
-                          const float* h_u3, float* h_out_dir3, float* h_out_pdf, float* h_out_inv_jac,
-                          uint32_t* h_out_comp, uint8_t* h_out_valid, int binned, void* stream) {
-    if (!ctx || (n && (!h_cell_idx || !h_pos3 || !h_u3 || !h_out_dir3 || !h_out_pdf || !h_out_inv_jac || !h_out_comp)))
-        return SDMMB_E_INVALID;
-    if (n == 0) return SDMMB_OK;
-    DeviceGuard g(ctx->device);
-    return query_host(ctx, n, h_cell_idx, h_pos3, h_u3, true, h_out_dir3, h_out_pdf, h_out_inv_jac, h_out_comp,
-                      h_out_valid, binned, (cudaStream_t)stream);
-}
-
-int sdmmb_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
-                   const float* h_dir3, float* h_out_pdf, uint8_t* h_out_valid, int binned, void* stream) {
-    if (!ctx || (n && (!h_cell_idx || !h_pos3 || !h_dir3 || !h_out_pdf))) return SDMMB_E_INVALID;
-    if (n == 0) return SDMMB_OK;
-    DeviceGuard g(ctx->device);
-    return query_host(ctx, n, h_cell_idx, h_pos3, h_dir3, false, nullptr, h_out_pdf, nullptr, nullptr, h_out_valid,
-                      binned, (cudaStream_t)stream);
-}
-
-int sdmmb_set_tree(sdmmb_ctx* ctx, int n_nodes, const sdmmb_tree_node* h_nodes) {
-    if (!ctx || n_nodes <= 0 || !h_nodes) return SDMMB_E_INVALID;
-    static_assert(sizeof(sdmmb_tree_node) == sizeof(TreeNode), "tree node layout");
-    for (int i = 0; i < n_nodes; ++i) {
-        const sdmmb_tree_node& nd = h_nodes[i];
-        if (nd.axis > 2) return SDMMB_E_INVALID;
-        if (nd.axis >= 0 && (nd.child0 >= (uint32_t)n_nodes || nd.child1 >= (uint32_t)n_nodes)) return SDMMB_E_INVALID;
-        if (nd.axis < 0 && nd.child0 >= (uint32_t)ctx->max_cells) return SDMMB_E_RANGE;
-    }
-    DeviceGuard g(ctx->device);
-    CK(cudaDeviceSynchronize());
-    cudaFree(ctx->d_tree);
-    ctx->d_tree = nullptr;
-    ctx->n_tree_nodes = 0;
-    CK(cudaMalloc(&ctx->d_tree, (size_t)n_nodes * sizeof(TreeNode)));
-    CK(cudaMemcpy(ctx->d_tree, h_nodes, (size_t)n_nodes * sizeof(TreeNode), cudaMemcpyHostToDevice));
-    ctx->n_tree_nodes = n_nodes;
-    return SDMMB_OK;
-}
-
-int sdmmb_find_cells(sdmmb_ctx* ctx, size_t n, const float* d_pos3, uint32_t* d_out_cell, void* stream) {
-    if (!ctx || (n && (!d_pos3 || !d_out_cell))) return SDMMB_E_INVALID;
-    if (!ctx->d_tree) return SDMMB_E_STATE;
-    DeviceGuard g(ctx->device);
-    CK(launch_find_cells(ctx->d_tree, ctx->n_tree_nodes, d_pos3, n, n, d_out_cell, 0xffffffffu, (cudaStream_t)stream));
-    if (n) ctx->launches += 1;
-    return SDMMB_OK;
-}
-
-int sdmmb_find_cells_host(sdmmb_ctx* ctx, size_t n, const float* h_pos3, uint32_t* h_out_cell, void* stream) {
-    if (!ctx || (n && (!h_pos3 || !h_out_cell))) return SDMMB_E_INVALID;
-    if (!ctx->d_tree) return SDMMB_E_STATE;
-    if (n == 0) return SDMMB_OK;
-    DeviceGuard g(ctx->device);
-    cudaStream_t st = (cudaStream_t)stream;
-    int rc = ensure(ctx, &ctx->d_stage2, &ctx->stage2_cap, n * 16);
-    if (rc) return rc;
-    float* d_pos = (float*)ctx->d_stage2;
-    uint32_t* d_out = (uint32_t*)(d_pos + 3 * n);
-    CK(cudaMemcpyAsync(d_pos, h_pos3, n * 12, cudaMemcpyHostToDevice, st));
-    CK(launch_find_cells(ctx->d_tree, ctx->n_tree_nodes, d_pos, n, n, d_out, 0xffffffffu, st));
-    ctx->launches += 1;
-    CK(cudaMemcpyAsync(h_out_cell, d_out, n * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    return SDMMB_OK;
-}
-
 int sdmmb_set_min_samples(sdmmb_ctx* ctx, uint32_t min_samples) {
     if (!ctx) return SDMMB_E_INVALID;
     ctx->min_samples = min_samples;
     return SDMMB_OK;
 }
 
-int sdmmb_collect_samples(sdmmb_ctx* ctx, size_t n, const float* d_point6, size_t plane_stride,
-                          const float* d_weight, const float* d_key3, size_t key_stride,
-                          uint32_t* h_out_counts, uint64_t* h_out_dropped, void* stream) {
-    if (!ctx || (n && (!d_point6 || !d_weight))) return SDMMB_E_INVALID;
-    if (!ctx->d_tree) return SDMMB_E_STATE;
-    if (n > 0x7fffffffu) return SDMMB_E_DATA_FULL;
-    DeviceGuard g(ctx->device);
-    cudaStream_t st = (cudaStream_t)stream;
-    const uint32_t B = (uint32_t)ctx->max_cells + 1;   // trailing bucket = dropped samples
-    // scratch (words): count[B] | cursor[B] | cell[n]
-    int rc = ensure(ctx, &ctx->d_qscratch, &ctx->qscratch_cap, (2 * (size_t)B + n + 4) * 4);
-    if (rc) return rc;
-    uint32_t* count = (uint32_t*)ctx->d_qscratch;
-    uint32_t* cursor = count + B;
-    uint32_t* cell = cursor + B;
-    const float* key = d_key3 ? d_key3 : d_point6;
-    const size_t kstride = d_key3 ? key_stride : plane_stride;
-    CK(launch_collect_count(ctx->d_tree, ctx->n_tree_nodes, key, kstride, d_weight, n, B, cell, count, cursor, st));
-    ctx->launches += 2;
-    std::vector<uint32_t> h_count(B);
-    CK(cudaMemcpyAsync(h_count.data(), count, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    std::vector<uint32_t> off((size_t)ctx->max_cells + 1, 0u);
-    for (int c = 0; c < ctx->max_cells; ++c) off[c + 1] = off[c] + h_count[c];
-    rc = bind_layout(ctx, 0, ctx->max_cells, off.data(), st);
-    if (rc) return rc;
-    CK(launch_collect_scatter(cell, d_point6, plane_stride, d_weight, n, B - 1, cursor, ctx->d_samples, st));
-    if (n) ctx->launches += 1;
-    if (h_out_counts) std::memcpy(h_out_counts, h_count.data(), (size_t)ctx->max_cells * 4);
-    if (h_out_dropped) *h_out_dropped = h_count[B - 1];
-    return SDMMB_OK;
-}
-
-int sdmmb_set_async_records(sdmmb_ctx* ctx, int enabled) {
-    if (!ctx) return SDMMB_E_INVALID;
-    DeviceGuard g(ctx->device);
-    const size_t bytes = (size_t)ctx->max_cells * ctx->K * QREC_FLOATS * 4;
-    if (enabled && !ctx->d_qrec_back) {
-        CK(cudaDeviceSynchronize());
-        CK(cudaMalloc(&ctx->d_qrec_back, bytes));
-        CK(cudaMemcpy(ctx->d_qrec_back, ctx->d_qrec, bytes, cudaMemcpyDeviceToDevice));
-    } else if (!enabled && ctx->d_qrec_back) {
-        // leaving async mode publishes whatever is pending
-        CK(cudaDeviceSynchronize());
-        CK(cudaMemcpy(ctx->d_qrec, ctx->d_qrec_back, bytes, cudaMemcpyDeviceToDevice));
-        cudaFree(ctx->d_qrec_back);
-        ctx->d_qrec_back = nullptr;
-    }
-    return SDMMB_OK;
-}
-
-int sdmmb_publish_records(sdmmb_ctx* ctx, int first_cell, int n_cells, void* stream) {
-    if (!ctx) return SDMMB_E_INVALID;
-    if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
-    if (!ctx->d_qrec_back || n_cells == 0) return SDMMB_OK;   // synchronous mode: already visible
-    DeviceGuard g(ctx->device);
-    const size_t per = (size_t)ctx->K * QREC_FLOATS;
-    CK(cudaMemcpyAsync(ctx->d_qrec + (size_t)first_cell * per, ctx->d_qrec_back + (size_t)first_cell * per,
-                       (size_t)n_cells * per * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-    return SDMMB_OK;
-}
-
-int sdmmb_query_records(sdmmb_ctx* ctx, float** d_records, size_t* floats_per_cell) {
-    if (!ctx || !d_records || !floats_per_cell) return SDMMB_E_INVALID;
-    *d_records = ctx->d_qrec;
-    *floats_per_cell = (size_t)ctx->K * QREC_FLOATS;
-    return SDMMB_OK;
-}
-
-int sdmmb_allgather_records(sdmmb_ctx* ctx, void* nccl_comm, int cells_per_rank, void* stream) {
-    if (!ctx || !nccl_comm || cells_per_rank <= 0) return SDMMB_E_INVALID;
-    int rc = load_nccl(ctx);
-    if (rc) return rc;
-    DeviceGuard g(ctx->device);
-    int rank = -1;
-    if (ctx->nccl_user_rank(nccl_comm, &rank) != 0 || rank < 0) return SDMMB_E_NCCL;
-    const size_t per_rank = (size_t)cells_per_rank * ctx->K * QREC_FLOATS;
-    if (((size_t)rank + 1) * cells_per_rank > (size_t)ctx->max_cells) return SDMMB_E_RANGE;
-    // in-place all-gather: this rank's slice already sits at its final offset
-    const int nccl_float = 7;
-    if (ctx->nccl_allgather(ctx->d_qrec + (size_t)rank * per_rank, ctx->d_qrec, per_rank, nccl_float,
-                            nccl_comm, (cudaStream_t)stream) != 0)
-        return SDMMB_E_NCCL;
-    return SDMMB_OK;
-}
-
-int sdmmb_launch_count(sdmmb_ctx* ctx, uint64_t* out) {
-    if (!ctx || !out) return SDMMB_E_INVALID;
-    *out = ctx->launches;
-    return SDMMB_OK;
-}
-
-int sdmmb_last_estep_ms(sdmmb_ctx* ctx, float* total_ms, int* n_launches) {
-    if (!ctx || !total_ms) return SDMMB_E_INVALID;
-    DeviceGuard g(ctx->device);
-    float tot = 0.f;
-    for (int i = 0; i < ctx->ev_used; ++i) {
-        CK(cudaEventSynchronize(ctx->ev[2 * i + 1]));
-        float ms = 0.f;
-        CK(cudaEventElapsedTime(&ms, ctx->ev[2 * i], ctx->ev[2 * i + 1]));
-        tot += ms;
-    }
-    *total_ms = tot;
-    if (n_launches) *n_launches = ctx->ev_used;
-    return SDMMB_OK;
-}
-
-int sdmmb_measure_peaks(int device, float* out4) {
-    if (!out4) return SDMMB_E_INVALID;
-    int n_dev = 0;
-    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return SDMMB_E_CUDA;
-    DeviceGuard g(device);
-    return measure_peaks(out4) == cudaSuccess ? SDMMB_OK : SDMMB_E_CUDA;
-}
-
-#include "capi_part3.inc"
-#include "capi_part4.inc"
-#include "capi_part5.inc"
-#include "capi_part6.inc"
 
 }  // extern "C"

@@ -1,5 +1,11 @@
-// capi_part3.inc -- included inside the extern "C" block of capi.cu (via capi_part2.inc):
-// sdmm::initialize on the device (row F3 of SURVEY.md section 8f).
+// capi_init.cu -- sdmm::initialize on the device (row F3 of SURVEY.md section 8f; sdmm/include/sdmm/opt/init.h:17-193)
+// and cell copies (a split's children inherit the parent's mixture and EM state, spatial_tree.h:187-196).
+#include "capi_internal.h"
+
+using namespace sdmmb;
+using namespace sdmmb_capi;
+
+extern "C" {
 
 int sdmmb_initialize(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d_point6,
                      const float* d_normal3, size_t plane_stride, const float* d_weight,
@@ -12,6 +18,7 @@ int sdmmb_initialize(sdmmb_ctx* ctx, int first_cell, int n_cells, const float* d
     if (n_cells == 0) return SDMMB_OK;
     for (int c = 0; c < n_cells; ++c)
         if (h_cell_offsets[c + 1] < h_cell_offsets[c]) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n_total = h_cell_offsets[n_cells];
@@ -66,6 +73,7 @@ int sdmmb_initialize_host(sdmmb_ctx* ctx, int first_cell, int n_cells, const flo
     if (!ctx || !h_point6 || !h_normal3 || !h_weight || !h_cell_offsets) return SDMMB_E_INVALID;
     if (!range_ok(ctx, first_cell, n_cells)) return SDMMB_E_RANGE;
     if (n_cells == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n = h_cell_offsets[n_cells];
@@ -86,6 +94,7 @@ int sdmmb_copy_cells(sdmmb_ctx* ctx, int n, const int32_t* h_src, const int32_t*
     if (!ctx || n < 0 || (n && (!h_src || !h_dst))) return SDMMB_E_INVALID;
     for (int i = 0; i < n; ++i)
         if (!range_ok(ctx, h_src[i], 1) || !range_ok(ctx, h_dst[i], 1)) return SDMMB_E_RANGE;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t K = (size_t)ctx->K;
@@ -110,3 +119,5 @@ int sdmmb_copy_cells(sdmmb_ctx* ctx, int n, const int32_t* h_src, const int32_t*
     CK(cudaStreamSynchronize(st));
     return SDMMB_OK;
 }
+
+}  // extern "C"

@@ -1,5 +1,9 @@
-// capi_part4.inc -- included inside the extern "C" block of capi.cu: the device path tracer
-// (include/sdmm_b200_render.h; kernels in render_kernels.cu).
+// capi_render.cu -- host side of the device path tracer (include/sdmm_b200_render.h; kernels in render_kernels.cu):
+// the progressive training loop's render pass with device-resident mixtures (rows F1 of SURVEY.md section 8f).
+#include "capi_internal.h"
+
+using namespace sdmmb;
+using namespace sdmmb_capi;
 
 struct sdmmb_pt {
     sdmmb_ctx* ctx = nullptr;
@@ -11,8 +15,6 @@ struct sdmmb_pt {
     size_t lists_cap = 0;      // in paths
     uint32_t* d_counters = nullptr;
 };
-
-}  // extern "C"  (helpers with C++ linkage)
 
 namespace {
 
@@ -62,6 +64,7 @@ int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, i
     if (n_quads <= 0 || n_quads > PT_MAX_QUADS) return SDMMB_E_RANGE;
     if (cfg->max_depth < 1 || cfg->max_depth > PT_MAX_VERTS + 1 || cfg->saved_per_path < 0) return SDMMB_E_RANGE;
     if (cam->width <= 0 || cam->height <= 0 || !(cfg->spatial_norm > 0.f)) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     sdmmb_pt* pt = new (std::nothrow) sdmmb_pt();
     if (!pt) return SDMMB_E_NOMEM;
@@ -119,6 +122,7 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     sdmmb_ctx* ctx = pt->ctx;
     if ((guided || collect) && !ctx->d_tree) return SDMMB_E_STATE;
     if (guided && !d_cell_initialized) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n = (size_t)pt->h_scene.width * pt->h_scene.height * (size_t)spp;
@@ -197,3 +201,5 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     }
     return SDMMB_OK;
 }
+
+}  // extern "C"

@@ -287,7 +287,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
 em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ items,
                 const float* __restrict__ erec, float* __restrict__ partials,
                 float* __restrict__ item_scal, float* __restrict__ out_loglik,
-                const float* __restrict__ soa_p6, size_t soa_stride, const float* __restrict__ soa_w) {
+                const float* __restrict__ soa_p6, size_t soa_stride, const float* __restrict__ soa_w,
+                const uint32_t* __restrict__ scal, uint32_t skip_iterations_ge) {
     constexpr int K = 2 * NP * LPS;
     constexpr int SPW = 32 / LPS;      // samples a warp processes per step
     constexpr int STEPS = 32 / SPW;    // steps per 32-sample chunk
@@ -300,6 +301,8 @@ em_estep_kernel(const float4* __restrict__ samples, const EItem* __restrict__ it
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int grp = lane / LPS, l = lane % LPS;
     const EItem item = items[blockIdx.x];
+    // second pass of the integrator's 2|1 iteration rule: cells that are done sit this launch out (CTA-uniform)
+    if (skip_iterations_ge != 0u && scal[(size_t)item.cell * SCALAR_WORDS + 1] >= skip_iterations_ge) return;
 
     // this lane's component parameters -> registers (coalesced over lanes within a plane)
     float2 prm[NP][EREC_REG_PLANES];
@@ -471,7 +474,7 @@ static cudaError_t launch_estep_inst(const EStepLaunch& L, cudaStream_t st) {
         configured = true;
     }
     kern<<<L.n_items, WARPS * 32, smem, st>>>(L.samples, L.items, L.erec, L.partials, L.item_scal, L.out_loglik,
-                                             L.soa_point6, L.soa_stride, L.soa_weight);
+                                             L.soa_point6, L.soa_stride, L.soa_weight, L.scal, L.skip_iterations_ge);
     return cudaGetLastError();
 }
 

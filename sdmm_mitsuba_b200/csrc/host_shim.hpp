@@ -10,9 +10,14 @@
 // compiles against the unmodified headers under /root/reference/sdmm/include.
 //
 //   reference call                                              replacement
-//   sdmm::em_step(sdmm, em, data)        opt/em.h:218-253       sdmm_b200::em_step(dev, slot, sdmm, em, data)
-//   sdmm::prepare(conditioner, sdmm)     sdmm_conditioner.h:89  sdmm_b200::prepare(dev, slot, conditioner, sdmm)
-//   the parallelFor body                 volpath_sdmm.cpp:287   sdmm_b200::optimize(dev, contexts, n_iterations)
+//   sdmm::em_step(sdmm, em, data)        opt/em.h:218-253       sdmm_b200::em_step(sdmm, em, data)        [bound device]
+//   sdmm::prepare(conditioner, sdmm)     sdmm_conditioner.h:89  sdmm_b200::prepare(conditioner, sdmm)     [bound device]
+//   the parallelFor body                 volpath_sdmm.cpp:287   sdmm_b200::optimize(dev, first_slot, contexts)
+//   create_conditional + sample + posterior per vertex          sdmm_b200::sample_pdf(dev, QueryBatch&) (batched),
+//     sdmm_conditioner.h:102-107, sdmm.h:93-97, 112-113         sdmm_b200::sample(conditioner, x, u) (one vertex)
+// The overloads without a Device argument have the reference's exact parameter lists: they use the Device
+// bound with sdmm_b200::bind_default_device() and the slot the Device assigned to the object (its address) the
+// first time it saw it, so call sites change only their namespace.
 //
 // There is no CPU fallback: every function needs the CUDA library and a device; errors surface as
 // std::runtime_error carrying the C ABI's error string (the reference throws std::runtime_error for
@@ -20,8 +25,10 @@
 #pragma once
 #include <cstdint>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "sdmm_b200.h"
@@ -39,7 +46,7 @@ inline void check(int rc, const char* what, sdmmb_ctx* ctx = nullptr) {
 // counterpart of the STree's SDMMContext bundles (distributions/sdmm_context.h:11-45).
 class Device {
 public:
-    Device(int device, int max_cells, int K) : K_(K), max_cells_(max_cells) {
+    Device(int device, int max_cells, int K) : K_(K), max_cells_(max_cells), resident_((size_t)max_cells) {
         check(sdmmb_create(&ctx_, device, max_cells, K), "sdmmb_create");
     }
     ~Device() { sdmmb_destroy(ctx_); }
@@ -49,9 +56,79 @@ public:
     int K() const { return K_; }
     int max_cells() const { return max_cells_; }
 
+    // Device slot of a reference object (keyed by its address): assigned in order of first use.  What lets
+    // em_step(sdmm, em, data) / prepare(conditioner, sdmm) keep the reference's parameter lists.
+    int slot_of(const void* key) {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto it = slots_.find(key);
+        if (it != slots_.end()) return it->second;
+        if (next_slot_ >= max_cells_) throw std::runtime_error("sdmm_b200::Device: more cells than slots");
+        const int s = next_slot_++;
+        slots_.emplace(key, s);
+        return s;
+    }
+    void alias(const void* key, const void* existing) {   // a second object of the same cell (its conditioner)
+        const int s = slot_of(existing);
+        std::lock_guard<std::mutex> lk(mu_);
+        slots_[key] = s;
+    }
+
+    // Which host object the device copy of a slot mirrors, and the EM counters it had when the shim last wrote
+    // it back: optimize() uploads only the cells whose host state changed since (a freshly initialised cell, a
+    // child a split created from its parent, a model somebody edited and invalidate()d).
+    struct Resident { const void* owner = nullptr; int iterations_run = -1; int samples_seen = -1; uint32_t total_weight = 0; };
+    bool is_resident(int slot, const void* owner, int iterations_run, int samples_seen, float total_weight) const {
+        const Resident& r = resident_[(size_t)slot];
+        uint32_t tw;
+        std::memcpy(&tw, &total_weight, 4);
+        return r.owner == owner && r.iterations_run == iterations_run && r.samples_seen == samples_seen && r.total_weight == tw;
+    }
+    void set_resident(int slot, const void* owner, int iterations_run, int samples_seen, float total_weight) {
+        Resident& r = resident_[(size_t)slot];
+        r.owner = owner; r.iterations_run = iterations_run; r.samples_seen = samples_seen;
+        std::memcpy(&r.total_weight, &total_weight, 4);
+    }
+    void invalidate(int slot) { resident_[(size_t)slot] = Resident{}; }
+
 private:
     sdmmb_ctx* ctx_ = nullptr;
     int K_, max_cells_;
+    std::mutex mu_;
+    int next_slot_ = 0;
+    std::unordered_map<const void*, int> slots_;
+    std::vector<Resident> resident_;
+};
+
+// The Device the reference-signature overloads below use (one per process is the integrator's case).
+inline Device*& default_device_ref() { static Device* d = nullptr; return d; }
+inline void bind_default_device(Device* d) { default_device_ref() = d; }
+inline Device& default_device() {
+    if (!default_device_ref()) throw std::runtime_error("sdmm_b200: no default device bound (bind_default_device)");
+    return *default_device_ref();
+}
+
+// page-locked host block (sdmmb_host_alloc): the host-buffer pipelines only overlap copies and kernels from it
+template <typename T>
+class PinnedBuffer {
+public:
+    PinnedBuffer() = default;
+    ~PinnedBuffer() { sdmmb_host_free(p_); }
+    PinnedBuffer(const PinnedBuffer&) = delete;
+    PinnedBuffer& operator=(const PinnedBuffer&) = delete;
+    void resize(size_t n) {
+        if (n <= cap_) { n_ = n; return; }
+        sdmmb_host_free(p_);
+        p_ = nullptr; cap_ = n_ = 0;
+        void* q = nullptr;
+        check(sdmmb_host_alloc(&q, (n + n / 4) * sizeof(T)), "sdmmb_host_alloc");
+        p_ = (T*)q; cap_ = n + n / 4; n_ = n;
+    }
+    T* data() { return p_; }
+    const T* data() const { return p_; }
+    size_t size() const { return n_; }
+private:
+    T* p_ = nullptr;
+    size_t n_ = 0, cap_ = 0;
 };
 
 inline uint32_t f2w(float f) { uint32_t w; std::memcpy(&w, &f, 4); return w; }
@@ -122,8 +199,8 @@ void unpack_em(EM& em, int K, const float* e, const uint32_t* scal) {
 // ---- sample staging: the reference keeps one Data<> object per cell (opt/data.h:25-57); the device
 // wants one SoA block per call.  Planes of all cells are gathered into one host block. --------------
 struct SampleBlock {
-    std::vector<float> point6;       // [6][n_total]
-    std::vector<float> weight;       // [n_total]
+    PinnedBuffer<float> point6;      // [6][n_total]
+    PinnedBuffer<float> weight;      // [n_total]
     std::vector<uint32_t> offsets;   // [n_cells + 1]
     size_t n_total = 0;
 
@@ -184,47 +261,136 @@ void prepare(Device& dev, int slot, Conditioner& conditioner, SDMM_& distributio
 }
 
 // ---- the body of SDMMVolumetricPathTracer::optimize's parallelFor (volpath_sdmm.cpp:287-311) for ALL
-// trainable cells in one go.  `contexts[i]` is the SDMMContext* of device slot first_slot + i; its
-// `training_data` must already hold the samples (the swap at :290 stays at the call site).  Cells whose
-// em.iterations_run < 4 get 2 iterations, the others 1 (:299-302); then the conditioner (:306-307).
+// trainable cells in one go.  `contexts[i]` is the SDMMContext* of device slot first_slot + i (slots are stable:
+// flatten_tree's leaf order); its `training_data` must already hold the samples (the swap at :290 stays at the
+// call site).  One sdmmb_optimize_host call: the samples cross PCIe chunk by chunk while earlier chunks are being
+// fitted and fitted mixtures travel back; cells whose em.iterations_run < 4 get 2 iterations, the others 1
+// (:299-302, applied per cell on the device: SDMMB_ITERS_INTEGRATOR); then the conditioner (:306-307).  Only the
+// cells whose host objects changed since the shim last wrote them are uploaded first.
+struct OptimizeScratch {               // reused across calls (pinned)
+    SampleBlock samples;
+    PinnedBuffer<float> joint, em;
+    PinnedBuffer<uint32_t> scal;
+};
+
 template <typename ContextPtr>
-void optimize(Device& dev, int first_slot, const std::vector<ContextPtr>& contexts) {
+void optimize(Device& dev, int first_slot, const std::vector<ContextPtr>& contexts, OptimizeScratch* scratch = nullptr) {
     const int K = dev.K();
     const int n = (int)contexts.size();
     if (n == 0) return;
-    // device slots are ordered: cells that need two iterations first
-    std::vector<int> order;
-    int n_two = 0;
-    for (int i = 0; i < n; ++i) if (contexts[i]->em.iterations_run < 4) { order.push_back(i); ++n_two; }
-    for (int i = 0; i < n; ++i) if (!(contexts[i]->em.iterations_run < 4)) order.push_back(i);
-    std::vector<float> joint((size_t)n * 32 * K), e((size_t)n * 81 * K);
-    std::vector<uint32_t> scal((size_t)n * 8);
+    OptimizeScratch local;
+    OptimizeScratch& S = scratch ? *scratch : local;
+    S.joint.resize((size_t)n * 32 * K);
+    S.em.resize((size_t)n * 81 * K);
+    S.scal.resize((size_t)n * 8);
+    sdmmb_ctx* ctx = dev.ctx();
+    // upload runs of cells the device does not mirror yet
+    int run_begin = -1;
+    auto flush = [&](int end) {
+        if (run_begin < 0) return;
+        check(sdmmb_upload_cells(ctx, first_slot + run_begin, end - run_begin, S.joint.data() + (size_t)run_begin * 32 * K,
+                                 S.em.data() + (size_t)run_begin * 81 * K, S.scal.data() + (size_t)run_begin * 8, nullptr),
+              "sdmmb_upload_cells", ctx);
+        run_begin = -1;
+    };
     std::vector<const decltype(contexts[0]->training_data)*> datas(n);
     for (int s = 0; s < n; ++s) {
-        auto& c = *contexts[order[s]];
-        pack_joint(c.sdmm, K, joint.data() + (size_t)s * 32 * K);
-        pack_em(c.em, K, e.data() + (size_t)s * 81 * K, scal.data() + (size_t)s * 8);
+        auto& c = *contexts[s];
         datas[s] = &c.training_data;
+        if (dev.is_resident(first_slot + s, &c, c.em.iterations_run, c.em.samples_seen, c.em.total_weight)) {
+            flush(s);
+            continue;
+        }
+        pack_joint(c.sdmm, K, S.joint.data() + (size_t)s * 32 * K);
+        pack_em(c.em, K, S.em.data() + (size_t)s * 81 * K, S.scal.data() + (size_t)s * 8);
+        if (run_begin < 0) run_begin = s;
     }
-    SampleBlock blk;
-    blk.gather(datas.begin(), datas.end());
-    sdmmb_ctx* ctx = dev.ctx();
-    check(sdmmb_upload_cells(ctx, first_slot, n, joint.data(), e.data(), scal.data(), nullptr), "sdmmb_upload_cells", ctx);
-    check(sdmmb_set_samples_host(ctx, first_slot, n, blk.point6.data(), blk.n_total, blk.weight.data(),
-                                 blk.offsets.data(), nullptr), "sdmmb_set_samples_host", ctx);
-    if (n_two > 0) check(sdmmb_em_step(ctx, first_slot, n_two, 1, 0, nullptr, nullptr), "sdmmb_em_step", ctx);
-    check(sdmmb_em_step(ctx, first_slot, n, 1, 1, nullptr, nullptr), "sdmmb_em_step", ctx);
-    check(sdmmb_download_cells(ctx, first_slot, n, joint.data(), e.data(), scal.data(), nullptr), "sdmmb_download_cells", ctx);
+    flush(n);
+    S.samples.gather(datas.begin(), datas.end());
+    check(sdmmb_optimize_host(ctx, first_slot, n, S.samples.point6.data(), S.samples.n_total, S.samples.weight.data(),
+                              S.samples.offsets.data(), SDMMB_ITERS_INTEGRATOR, 1, S.joint.data(), S.em.data(),
+                              S.scal.data(), nullptr), "sdmmb_optimize_host", ctx);
     for (int s = 0; s < n; ++s) {
-        auto& c = *contexts[order[s]];
-        unpack_joint(c.sdmm, K, joint.data() + (size_t)s * 32 * K);
-        unpack_em(c.em, K, e.data() + (size_t)s * 81 * K, scal.data() + (size_t)s * 8);
+        auto& c = *contexts[s];
+        unpack_joint(c.sdmm, K, S.joint.data() + (size_t)s * 32 * K);
+        unpack_em(c.em, K, S.em.data() + (size_t)s * 81 * K, S.scal.data() + (size_t)s * 8);
         enoki::set_slices(c.conditioner, enoki::slices(c.sdmm));
         sdmm::prepare(c.conditioner, c.sdmm);
         c.training_data.clear();
         c.data.clear();
         c.initialized = true;
+        dev.set_resident(first_slot + s, &c, c.em.iterations_run, c.em.samples_seen, c.em.total_weight);
     }
+}
+
+// ---- the reference's exact parameter lists over the bound default device ---------------------------------
+// void sdmm::em_step(SDMM&, EM<SDMM>&, Data<SDMM>&)            opt/em.h:218-219
+template <typename SDMM_, typename EM_, typename Data_>
+void em_step(SDMM_& distribution, EM_& em, Data_& data) {
+    Device& dev = default_device();
+    em_step(dev, dev.slot_of(&distribution), distribution, em, data, 1);
+}
+// void sdmm::prepare(Conditioner&, JointSDMM&)                 distributions/sdmm_conditioner.h:89-93
+template <typename Conditioner, typename SDMM_>
+void prepare(Conditioner& conditioner, SDMM_& distribution) {
+    Device& dev = default_device();
+    const int slot = dev.slot_of(&distribution);
+    dev.alias(&conditioner, &distribution);
+    prepare(dev, slot, conditioner, distribution);
+}
+
+// ---- guided queries ----------------------------------------------------------------------------------------
+// The reference answers a path vertex with three calls on thread_local scratch objects (sdmm_proc.cpp:361-372,
+// 419-421, 539-545): create_conditional(conditioner, x, conditional) (sdmm_conditioner.h:102-107),
+// conditional.sample(rng, dir, inv_jacobian, tangent) (sdmm.h:93-97), conditional.posterior(dir, posterior) + hsum
+// (sdmm.h:112-113).  The device answers a whole batch of vertices in one fused kernel; the conditional mixture
+// never leaves the GPU.  `slot[i]` = device slot of the vertex's cell (Device::slot_of(&context->sdmm), or
+// sdmmb_find_cells on the uploaded tree); u = the three uniforms the reference's RNG would have drawn.
+struct QueryBatch {
+    std::vector<uint32_t> slot;                    // [n]
+    std::vector<float> pos3, u3, dir_in3;          // [3][n] planes (u3 for sample_pdf, dir_in3 for pdf)
+    std::vector<float> dir3, pdf, inv_jacobian;    // results
+    std::vector<uint32_t> component;
+    std::vector<uint8_t> valid;                    // 0 = create_conditional returned false
+    size_t size() const { return slot.size(); }
+    void resize(size_t n) {
+        slot.resize(n); pos3.resize(3 * n); u3.resize(3 * n); dir_in3.resize(3 * n);
+        dir3.resize(3 * n); pdf.resize(n); inv_jacobian.resize(n); component.resize(n); valid.resize(n);
+    }
+};
+
+// create_conditional + SDMM::sample + posterior/hsum for every vertex of the batch
+inline void sample_pdf(Device& dev, QueryBatch& q, bool binned = false) {
+    check(sdmmb_sample_pdf_host(dev.ctx(), q.size(), q.slot.data(), q.pos3.data(), q.u3.data(), q.dir3.data(), q.pdf.data(),
+                                q.inv_jacobian.data(), q.component.data(), q.valid.data(), binned ? 1 : 0, nullptr),
+          "sdmmb_sample_pdf_host", dev.ctx());
+}
+// create_conditional + posterior/hsum at given directions (pdfSurface, sdmm_proc.cpp:510-590)
+inline void pdf(Device& dev, QueryBatch& q, bool binned = false) {
+    check(sdmmb_pdf_host(dev.ctx(), q.size(), q.slot.data(), q.pos3.data(), q.dir_in3.data(), q.pdf.data(), q.valid.data(),
+                         binned ? 1 : 0, nullptr), "sdmmb_pdf_host", dev.ctx());
+}
+
+// One vertex with the reference's own types: fills the caller's scratch exactly where sampleSurface reads it.
+// `conditioner` identifies the cell (prepare() registered it); point = the normalised position; u0,u1,u2 = the
+// uniforms.  Returns create_conditional's bool; sample / inv_jacobian / pdf as SDMM::sample and hsum(posterior).
+template <typename Conditioner, typename MarginalEmbedded, typename EmbeddedOut, typename Scalar>
+bool sample(Conditioner& conditioner, const MarginalEmbedded& point, float u0, float u1, float u2, EmbeddedOut& sample_out,
+            Scalar& inv_jacobian, Scalar& pdf_out, uint32_t* component = nullptr) {
+    Device& dev = default_device();
+    const uint32_t slot = (uint32_t)dev.slot_of(&conditioner);
+    const float pos[3] = {(float)point.coeff(0), (float)point.coeff(1), (float)point.coeff(2)};
+    const float u[3] = {u0, u1, u2};
+    float dir[3], p = 0.f, ij = 0.f;
+    uint32_t comp = 0;
+    uint8_t ok = 0;
+    check(sdmmb_sample_pdf_host(dev.ctx(), 1, &slot, pos, u, dir, &p, &ij, &comp, &ok, 1, nullptr), "sdmmb_sample_pdf_host",
+          dev.ctx());
+    for (int i = 0; i < 3; ++i) sample_out.coeff(i) = dir[i];
+    inv_jacobian = ij;
+    pdf_out = p;
+    if (component) *component = comp;
+    return ok != 0;
 }
 
 }  // namespace sdmm_b200

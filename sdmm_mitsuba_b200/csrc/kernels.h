@@ -66,6 +66,11 @@ struct EStepLaunch {
     float* partials;   // [n_items][21][K]
     float* item_scal;  // [n_items][2]: sum of weights, skipped-sample count (int bits)
     float* out_loglik; // nullable, indexed by absolute sample index
+    // the integrator's iteration rule (volpath_sdmm.cpp:299-302: two em_steps while em.iterations_run < 4, else
+    // one) evaluated per cell on the device: in the rule's second pass the items of cells whose iterations_run
+    // has reached `skip_iterations_ge` do nothing.  0 = every item runs.
+    const uint32_t* scal;
+    uint32_t skip_iterations_ge;
 };
 
 // Multi-GPU record exchange fused into K3 (sdmmb_peer_attach): the CTA that wrote the query records
@@ -106,6 +111,7 @@ struct MStepArgs {
     uint32_t item_base;                 // item index that `partials` / `item_scal` start at
     const uint32_t* cell_sample_count;  // [n_cells]
     uint32_t min_samples;               // cells with fewer bound samples are left untouched by the EM update
+    uint32_t skip_iterations_ge;        // != 0: cells whose iterations_run >= this skip the EM update (see EStepLaunch)
     PeerPush peer;                      // world == 0: no peer stores
 };
 

@@ -316,7 +316,8 @@ em_mstep_kernel(MStepArgs a) {
     }
 
     // canBeOptimized (volpath_sdmm.cpp:140-149): cells that hold too few samples are not trained
-    const bool trainable = active && (a.mode & 1) && a.cell_sample_count[ci] >= a.min_samples;
+    const bool trainable = active && (a.mode & 1) && a.cell_sample_count[ci] >= a.min_samples &&
+                           !(a.skip_iterations_ge != 0u && scal[1] >= a.skip_iterations_ge);
     if (trainable) {
         // ---- reduce the E-step partials of this cell's items (fixed order, double accumulators) --
         const uint32_t ib = a.cell_item_begin[ci] - a.item_base, ie = a.cell_item_begin[ci + 1] - a.item_base;

@@ -166,7 +166,9 @@ class SDMMCells:
 
     def em_step(self, n_iters=1, first_cell=None, n_cells=None, with_conditioner=True, want_loglik=False):
         """n_iters x sdmm::em_step on every bound cell (+ sdmm::prepare of the conditioner after the
-        last one).  want_loglik -> torch tensor [n_iters, N] of per-sample log-likelihoods."""
+        last one).  want_loglik -> torch tensor [n_iters, N] of per-sample log-likelihoods.
+        n_iters = capi.ITERS_INTEGRATOR (-1): the integrator's rule per cell on the device -- two iterations for
+        cells whose em.iterations_run < 4, one for the others (volpath_sdmm.cpp:299-302)."""
         if first_cell is None:
             first_cell, n_cells = self._bound
         ll = None
@@ -174,7 +176,8 @@ class SDMMCells:
         st = None
         if want_loglik:
             import torch
-            ll = torch.empty((n_iters, self.n_samples), dtype=torch.float32, device="cuda:%d" % self.device)
+            ll = torch.full((2 if n_iters < 0 else n_iters, self.n_samples), float("nan"), dtype=torch.float32,
+                            device="cuda:%d" % self.device)
             ptr = C.c_void_p(ll.data_ptr())
             st = _stream(self.device)
         else:

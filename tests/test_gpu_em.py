@@ -189,6 +189,34 @@ def test_em_parity_at_bench_shapes(K, N, C, iters):
     _free_running_with_cause(C, K, N, iters, seed=100 + K)
 
 
+def test_integrator_iteration_rule_on_the_device():
+    """n_iters = SDMMB_ITERS_INTEGRATOR: `n_iterations = (em.iterations_run < 4) ? 2 : 1` per cell
+    (volpath_sdmm.cpp:299-302) evaluated on the device in one call -- bit-identical to fitting the young cells
+    twice and the old cells once by hand, whatever their order in the slot range."""
+    from sdmm_mitsuba_b200 import capi
+    C, K, N = 12, 32, 900
+    point6, weight, off, joint, em, scal = _setup(C, K, N, seed=41)
+    runs = np.array([0, 5, 3, 4, 1, 9, 2, 6, 3, 0, 7, 4], np.uint32)   # iterations_run entering the call
+    scal[:, 1] = runs
+    a = _gpu_cells(C, K, joint, em, scal)
+    a.set_samples(point6, weight, off)
+    a.em_step(capi.ITERS_INTEGRATOR, with_conditioner=True)
+    ja, ea, sa = a.download()
+    qa = a.query_records().clone()
+    b = _gpu_cells(C, K, joint, em, scal)
+    for c in range(C):                                   # by hand, cell by cell
+        lo, hi = int(off[c]), int(off[c + 1])
+        b.set_samples(point6[:, lo:hi].copy(), weight[lo:hi].copy(), np.array([0, hi - lo], np.uint32), first_cell=c)
+        b.em_step(2 if runs[c] < 4 else 1, first_cell=c, n_cells=1, with_conditioner=True)
+    jb, eb, sb = b.download()
+    np.testing.assert_array_equal(sa[:, 1], runs + np.where(runs < 4, 2, 1))
+    np.testing.assert_array_equal(sa, sb)
+    np.testing.assert_array_equal(ja, jb)
+    np.testing.assert_array_equal(ea, eb)
+    import torch
+    assert torch.equal(qa, b.query_records())
+
+
 def test_em_ragged_cells_and_item_split():
     """Cells of very different sizes (8 ... 5000 samples, one empty) so that work items split and
     partial chunks are exercised; invalid weights (0, 1e-9, NaN, inf) are skipped like
