@@ -187,6 +187,17 @@ int sdmmb_sample_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const
 int sdmmb_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
               const float* d_dir3, float* d_out_pdf, uint8_t* d_out_valid, int binned, void* stream);
 /* Host-buffer variants (H2D of inputs, kernel, D2H of outputs inside the call). */
+/* The same query on a PRUNED conditional: sdmm::create_conditional_pruned
+ * (sdmm/include/sdmm/distributions/sdmm_conditioner.h:128-168) keeps the max_components strongest conditional
+ * weights of the vertex (the weakest K - max_components are zeroed; preserve_idx >= 0 is never zeroed and takes
+ * one place of the budget; -1 = none), re-normalises, then sample + pdf as above.  d_u3 != NULL: sample mode;
+ * d_u3 == NULL: pdf of d_dir3 (then d_out_dir3 / d_out_inv_jac / d_out_comp may be NULL).  The reference defines
+ * the function for product guiding with many components; no call site of its integrator uses it. */
+int sdmmb_sample_pdf_pruned(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+                            const float* d_u3, const float* d_dir3, int max_components, int preserve_idx,
+                            float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac, uint32_t* d_out_comp,
+                            uint8_t* d_out_valid, void* stream);
+
 int sdmmb_sample_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
                           const float* h_u3, float* h_out_dir3, float* h_out_pdf,
                           float* h_out_inv_jac, uint32_t* h_out_comp, uint8_t* h_out_valid,

@@ -97,6 +97,9 @@ def product_lib():
         L.sdmm_ref_product_sample_pdf.argtypes = [C.POINTER(C.c_void_p), C.c_long, up, fp, fp, fp, fp, fp, fp, C.c_int, fp,
                                                   fp, fp, fp, up, bp, C.c_int]
         L.sdmm_ref_product_components.argtypes = [C.c_void_p, fp, fp, C.c_int, fp, fp, C.c_int]
+        L.sdmm_ref_pruned_sample_pdf.restype = C.c_double
+        L.sdmm_ref_pruned_sample_pdf.argtypes = [C.POINTER(C.c_void_p), C.c_long, up, fp, fp, C.c_int, C.c_int, fp, fp, fp,
+                                                 up, bp, fp]
         _plib = L
     return _plib
 
@@ -254,6 +257,17 @@ class RefCells:
                                              _f(bsdf), _f(out_dir),
                                              _f(out_pdf), _f(out_ij), _u(out_comp), _b(out_valid), n_threads)
         return dict(dir=out_dir, pdf=out_pdf, inv_jac=out_ij, comp=out_comp, valid=out_valid), secs
+
+    def pruned_sample_pdf(self, cell_idx, pos3, u3, max_components, preserve_idx=-1):
+        """create_conditional_pruned (sdmm_conditioner.h:128-168) -> sample -> posterior, per vertex."""
+        L = product_lib()
+        n = pos3.shape[1]
+        out = dict(dir=np.zeros((3, n), np.float32), pdf=np.zeros(n, np.float32), inv_jac=np.zeros(n, np.float32),
+                   comp=np.zeros(n, np.uint32), valid=np.zeros(n, np.uint8), pmf=np.zeros((n, self.K), np.float32))
+        L.sdmm_ref_pruned_sample_pdf(C.cast(self.handles, C.POINTER(C.c_void_p)), n, _u(cell_idx), _f(pos3), _f(u3),
+                                     int(max_components), int(preserve_idx), _f(out["dir"]), _f(out["pdf"]),
+                                     _f(out["inv_jac"]), _u(out["comp"]), _b(out["valid"]), _f(out["pmf"]))
+        return out
 
     def product_components(self, cell, x, bsdf, normal=None):
         """The product mixture at one vertex: [P,7] rows (pmf, tangent_mean2, cov00, cov10, cov11, cdf)."""

@@ -32,7 +32,7 @@ SYMBOLS = [
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
     "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
-    "sdmmb_host_alloc", "sdmmb_host_free",
+    "sdmmb_host_alloc", "sdmmb_host_free", "sdmmb_sample_pdf_pruned",
 ]
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
 ITERS_INTEGRATOR = -1    # SDMMB_ITERS_INTEGRATOR: the integrator's 2|1 iteration rule per cell
@@ -133,6 +133,9 @@ def lib():
     L.sdmmb_pt_create.argtypes = [vp, C.POINTER(vp), C.POINTER(Quad), i, C.POINTER(Camera), C.POINTER(PtConfig)]
     L.sdmmb_pt_destroy.argtypes = [vp]
     L.sdmmb_copy_cells.argtypes = [vp, i, vp, vp, vp]
+    L.sdmmb_sample_pdf_pruned.argtypes = [vp, sz, vp, vp, vp, vp, i, i, vp, vp, vp, vp, vp, vp]
+    L.sdmmb_host_alloc.argtypes = [C.POINTER(vp), sz]
+    L.sdmmb_host_free.argtypes = [vp]
     L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
     L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp]
     L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]

@@ -184,6 +184,35 @@ int sdmmb_query_records(sdmmb_ctx* ctx, float** d_records, size_t* floats_per_ce
     return SDMMB_OK;
 }
 
+int sdmmb_sample_pdf_pruned(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+                            const float* d_u3, const float* d_dir3, int max_components, int preserve_idx,
+                            float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac, uint32_t* d_out_comp,
+                            uint8_t* d_out_valid, void* stream) {
+    if (!ctx || max_components < 1 || (n && (!d_cell_idx || !d_pos3 || !d_out_pdf || (!d_u3 && !d_dir3)))) return SDMMB_E_INVALID;
+    if (n && d_u3 && (!d_out_dir3 || !d_out_inv_jac || !d_out_comp)) return SDMMB_E_INVALID;
+    if (preserve_idx >= ctx->K_user) return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    SDMMB_NVTX("sdmmb pruned query");
+    QueryLaunch q{};
+    q.K = ctx->K;
+    q.n = n;
+    q.qrec = ctx->d_qrec;
+    q.cell_idx = d_cell_idx;
+    q.pos3 = d_pos3;
+    q.u3 = d_u3;
+    q.dir3 = d_dir3;
+    q.out_dir3 = d_out_dir3;
+    q.out_pdf = d_out_pdf;
+    q.out_inv_jac = d_out_inv_jac;
+    q.out_comp = d_out_comp;
+    q.out_valid = d_out_valid;
+    q.max_cells = ctx->max_cells;
+    CK(launch_query_pruned(q, ctx->K_user, max_components, preserve_idx, (cudaStream_t)stream));
+    if (n) ctx->launches += 1;
+    return SDMMB_OK;
+}
+
 // ---- product guiding (row F4 of SURVEY.md section 8f) ----
 static int product_common(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
                           const float* d_u3, const float* d_dir3, const float* d_normal3, const float* d_frame9,

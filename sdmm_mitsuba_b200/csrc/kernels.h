@@ -182,6 +182,8 @@ cudaError_t launch_derived_readout(const float* joint, const float* cdf, int fir
 cudaError_t launch_conditioner_readout(const float* joint, const float* qrec, int first_cell, int n_cells,
                                        int K, float* out, cudaStream_t st);
 cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st);
+// create_conditional_pruned + sample + pdf, one thread per vertex (u3 != null: sample mode, else dir3)
+cudaError_t launch_query_pruned(const QueryLaunch& q, int K_user, int max_components, int preserve_idx, cudaStream_t st);
 // counting sort of vertices by cell (query_kernels.cu); scratch: 2 * (max_cells + 1) + 9 * n + 4 words
 cudaError_t launch_bin_vertices(const uint32_t* cell_idx, size_t n, int max_cells, const float* pos3,
                                 const float* in3, uint32_t* scratch, float4** out_qin, uint32_t** out_invperm,

@@ -24,6 +24,7 @@ namespace sdmmb {
 namespace {
 
 constexpr int QTHREADS = 128;
+constexpr int SDMMB_QUERY_MAX_K = 128;
 
 __device__ __forceinline__ float q_rsqrt(float x) {
     float y;
@@ -152,6 +153,55 @@ __device__ __forceinline__ int select_component(const float4* __restrict__ rec, 
     return sel;
 }
 
+// Box-Muller + `L_c z` + offset exp map of component `sel` for one vertex        R: sdmm.h:238-265,
+// spaces/offset_directional.h:62-82
+__device__ __forceinline__ void sample_direction(const float4* __restrict__ rec, int sel, float x, float y, float z,
+                                                 float u1, float u2, float& wx, float& wy, float& wz, float& ij) {
+    float radius = sqrtf(-2.f * logf(1.f - u1));
+    float theta = 2.f * kPi * u2;
+    float sn, cs;
+    sincosf(theta, &sn, &cs);
+    float g0 = sn * radius, g1 = cs * radius;
+    const QRec r = load_rec<true>(rec, sel);
+    float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
+    float tm0 = r.f(QREC_M + 0) * dx0 + r.f(QREC_M + 1) * dx1 + r.f(QREC_M + 2) * dx2;
+    float tm1 = r.f(QREC_M + 3) * dx0 + r.f(QREC_M + 4) * dx1 + r.f(QREC_M + 5) * dx2;
+    float t0 = r.f(QREC_LC + 0) * g0;
+    float t1 = r.f(QREC_LC + 1) * g0 + r.f(QREC_LC + 2) * g1;
+    const float max_length = kPi - 1e-1f;
+    float ox = t0 + tm0, oy = t1 + tm1;
+    float length = sqrtf(ox * ox + oy * oy);
+    float sl, cl;
+    sincosf(length, &sl, &cl);
+    float sinc = ((sl < 1e-2f) || length > max_length) ? 1.f : sl / length;
+    ij = (length > max_length) ? 0.f : sinc;
+    float l0 = ox * sinc, l1 = oy * sinc, l2 = cl;
+    wx = r.f(QREC_R + 0) * l0 + r.f(QREC_R + 3) * l1 + r.f(QREC_R + 6) * l2;
+    wy = r.f(QREC_R + 1) * l0 + r.f(QREC_R + 4) * l1 + r.f(QREC_R + 7) * l2;
+    wz = r.f(QREC_R + 2) * l0 + r.f(QREC_R + 5) * l1 + r.f(QREC_R + 8) * l2;
+}
+
+// conditional pdf of component k at direction w for ONE vertex: the scalar twin of pass 3 of query_pair (each half
+// of a packed FFMA2 is an IEEE fma, so this reproduces that half bit for bit)          R: sdmm.h:284-313, 331-339
+__device__ __forceinline__ float cond_pdf_single(const float4* __restrict__ rec, int k, float x, float y, float z,
+                                                 float wx, float wy, float wz) {
+    const QRec r = load_rec<true>(rec, k);
+    const float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
+    const float tm0 = fmaf(r.f(QREC_M + 2), dx2, fmaf(r.f(QREC_M + 1), dx1, r.f(QREC_M + 0) * dx0));
+    const float tm1 = fmaf(r.f(QREC_M + 5), dx2, fmaf(r.f(QREC_M + 4), dx1, r.f(QREC_M + 3) * dx0));
+    const float lx = fmaf(r.f(QREC_R + 2), wz, fmaf(r.f(QREC_R + 1), wy, r.f(QREC_R + 0) * wx));
+    const float ly = fmaf(r.f(QREC_R + 5), wz, fmaf(r.f(QREC_R + 4), wy, r.f(QREC_R + 3) * wx));
+    const float lz = fmaf(r.f(QREC_R + 8), wz, fmaf(r.f(QREC_R + 7), wy, r.f(QREC_R + 6) * wx));
+    const float rs = rcp_sinc_from_cos(lz);
+    const float ij = (lz < -0.98f) ? 0.f : rs;
+    const float t0 = fmaf(lx, rs, -tm0), t1 = fmaf(ly, rs, -tm1);
+    const float z0 = r.f(QREC_WC + 0) * t0;
+    const float z1 = fmaf(r.f(QREC_WC + 2), t1, r.f(QREC_WC + 1) * t0);
+    float e = fmaf(z0, z0, r.f(QREC_NLCC));
+    e = fmaf(z1, z1, e);
+    return ij * q_ex2(-e);
+}
+
 template <bool SAMPLE, int K>
 __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float2* __restrict__ pref, int ps,
                                            PairIn& in, PairRes& out) {
@@ -184,28 +234,8 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float
             const float x = h ? in.x.y : in.x.x, y = h ? in.y.y : in.y.x, z = h ? in.z.y : in.z.x;
             const float u1 = h ? in.u1.y : in.u1.x, u2 = h ? in.u2.y : in.u2.x;
             const int sel = h ? sel1 : sel0;
-            float radius = sqrtf(-2.f * logf(1.f - u1));
-            float theta = 2.f * kPi * u2;
-            float sn, cs;
-            sincosf(theta, &sn, &cs);
-            float g0 = sn * radius, g1 = cs * radius;
-            const QRec r = load_rec<true>(rec, sel);
-            float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
-            float tm0 = r.f(QREC_M + 0) * dx0 + r.f(QREC_M + 1) * dx1 + r.f(QREC_M + 2) * dx2;
-            float tm1 = r.f(QREC_M + 3) * dx0 + r.f(QREC_M + 4) * dx1 + r.f(QREC_M + 5) * dx2;
-            float t0 = r.f(QREC_LC + 0) * g0;
-            float t1 = r.f(QREC_LC + 1) * g0 + r.f(QREC_LC + 2) * g1;
-            const float max_length = kPi - 1e-1f;
-            float ox = t0 + tm0, oy = t1 + tm1;
-            float length = sqrtf(ox * ox + oy * oy);
-            float sl, cl;
-            sincosf(length, &sl, &cl);
-            float sinc = ((sl < 1e-2f) || length > max_length) ? 1.f : sl / length;
-            float ij = (length > max_length) ? 0.f : sinc;
-            float l0 = ox * sinc, l1 = oy * sinc, l2 = cl;
-            float wx = r.f(QREC_R + 0) * l0 + r.f(QREC_R + 3) * l1 + r.f(QREC_R + 6) * l2;
-            float wy = r.f(QREC_R + 1) * l0 + r.f(QREC_R + 4) * l1 + r.f(QREC_R + 7) * l2;
-            float wz = r.f(QREC_R + 2) * l0 + r.f(QREC_R + 5) * l1 + r.f(QREC_R + 8) * l2;
+            float wx, wy, wz, ij;
+            sample_direction(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
             if (h) { in.wx.y = wx; in.wy.y = wy; in.wz.y = wz; out.ij.y = ij; }
             else { in.wx.x = wx; in.wy.x = wy; in.wz.x = wz; out.ij.x = ij; }
         }
@@ -497,6 +527,88 @@ __global__ void query_unpermute_kernel(QueryLaunch q, const uint32_t* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// create_conditional_pruned (R: distributions/sdmm_conditioner.h:128-168) + SDMM::sample + posterior: only the
+// `max_components` strongest conditional weights of a vertex survive (the reference walks the components in
+// ascending order of weight and zeroes the first K_user - max_components, skipping `preserve_idx`, which shrinks
+// the survivor budget by one), then Categorical::prepare, select, sample, pdf as in the full query.  The reference
+// defines the function but no call site of its integrator uses it, so this is a plain one-thread-per-vertex kernel
+// (the K weights of a vertex live in local memory), not a tuned one; with max_components >= K_user it returns
+// the bits of query_pair_kernel.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+query_pruned_kernel(QueryLaunch q, int K_user, int max_components, int preserve_idx) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q.n) return;
+    const int K = q.K;
+    const uint32_t cell = q.cell_idx[i];
+    float wx = 0.f, wy = 0.f, wz = 0.f, pdf = 0.f, ij = 0.f;
+    uint32_t comp = 0u;
+    uint8_t valid = 0;
+    if (cell < (uint32_t)q.max_cells) {
+        const float4* rec = reinterpret_cast<const float4*>(q.qrec + (size_t)cell * K * QREC_FLOATS);
+        const float x = q.pos3[i], y = q.pos3[q.n + i], z = q.pos3[2 * q.n + i];
+        float w[SDMMB_QUERY_MAX_K];
+        for (int k = 0; k < K; ++k) w[k] = single_weight(rec, k, x, y, z);
+        // kill the weakest components: ascending order of (weight, index), visited once each
+        uint32_t seen[SDMMB_QUERY_MAX_K / 32] = {0u, 0u, 0u, 0u};
+        int budget = max_components;
+        for (int slice = 0; slice < K_user - budget; ++slice) {
+            int best = -1;
+            float bw = 0.f;
+            for (int k = 0; k < K_user; ++k) {
+                if (seen[k >> 5] >> (k & 31) & 1u) continue;
+                const float wk = w[k];
+                if (best < 0 || wk < bw) { best = k; bw = wk; }
+            }
+            if (best < 0) break;
+            seen[best >> 5] |= 1u << (best & 31);
+            if (best == preserve_idx) { --budget; continue; }
+            w[best] = 0.f;
+        }
+        // a killed weight entered `seen` with its ORIGINAL value, so zeroing never changes the visiting order
+        float total = 0.f;
+        for (int k = 0; k < K; ++k) total = (k == 0) ? w[0] : total + w[k];
+        valid = total > 1e-20f ? 1 : 0;                                // R: categorical.h:97-101
+        if (valid) {
+            const float inv = 1.f / total;
+            if (q.u3) {
+                const float u0 = q.u3[i], u1 = q.u3[q.n + i], u2 = q.u3[2 * q.n + i];
+                int sel = K - 1;
+                float run = 0.f;
+                bool found = false;
+                for (int k = 0; k < K; ++k) {
+                    run = (k == 0) ? w[0] : run + w[k];
+                    if (!found && !(run * inv < u0)) { sel = k; found = true; }
+                }
+                while (sel > 0 && w[sel] * inv == 0.f) --sel;
+                comp = (uint32_t)sel;
+                sample_direction(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
+            } else {
+                wx = q.dir3[i]; wy = q.dir3[q.n + i]; wz = q.dir3[2 * q.n + i];
+            }
+            for (int k = 0; k < K; ++k) pdf = fmaf(cond_pdf_single(rec, k, x, y, z, wx, wy, wz), w[k] * inv, pdf);
+        }
+    }
+    if (q.u3) {
+        q.out_dir3[i] = wx; q.out_dir3[q.n + i] = wy; q.out_dir3[2 * q.n + i] = wz;
+        q.out_inv_jac[i] = ij;
+        q.out_comp[i] = comp;
+    }
+    q.out_pdf[i] = valid ? pdf : 0.f;
+    if (q.out_valid) q.out_valid[i] = valid;
+}
+
+}  // namespace
+
+cudaError_t launch_query_pruned(const QueryLaunch& q, int K_user, int max_components, int preserve_idx, cudaStream_t st) {
+    if (q.n == 0) return cudaSuccess;
+    if (q.K > SDMMB_QUERY_MAX_K) return cudaErrorInvalidValue;
+    query_pruned_kernel<<<(unsigned)((q.n + 127) / 128), 128, 0, st>>>(q, K_user, max_components, preserve_idx);
+    return cudaGetLastError();
+}
+
+namespace {
 }  // namespace
 
 // Counting sort of n vertices by cell into the caller-provided scratch (words):

@@ -327,6 +327,30 @@ class SDMMCells:
                                      1 if binned else 0, None), "sdmmb_pdf_host", self._h)
         return out_pdf, out_valid
 
+    def sample_pdf_pruned(self, cell_idx, pos3, u3, max_components, preserve_idx=-1, dir3=None):
+        """create_conditional_pruned (sdmm_conditioner.h:128-168) -> sample -> posterior per vertex: only the
+        max_components strongest conditional weights survive.  u3=None + dir3: pdf only.  Host arrays or device tensors."""
+        import torch
+        dev = torch.device("cuda", self.device)
+
+        def dv(a, dt):
+            if a is None:
+                return None
+            return a.contiguous() if _is_torch(a) else torch.from_numpy(np.ascontiguousarray(a, dt)).to(dev)
+
+        cell_d, pos_d = dv(cell_idx if _is_torch(cell_idx) else np.asarray(cell_idx).view(np.int32), np.int32), dv(pos3, np.float32)
+        u_d, d_d = dv(u3, np.float32), dv(dir3, np.float32)
+        n = pos_d.shape[1]
+        out = dict(dir=torch.zeros((3, n), dtype=torch.float32, device=dev), pdf=torch.zeros(n, dtype=torch.float32, device=dev),
+                   inv_jac=torch.zeros(n, dtype=torch.float32, device=dev), comp=torch.zeros(n, dtype=torch.int32, device=dev),
+                   valid=torch.zeros(n, dtype=torch.uint8, device=dev))
+        p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+        check(self._L.sdmmb_sample_pdf_pruned(self._h, n, p(cell_d), p(pos_d), p(u_d), p(d_d), int(max_components),
+                                              int(preserve_idx), p(out["dir"]), p(out["pdf"]), p(out["inv_jac"]),
+                                              p(out["comp"]), p(out["valid"]), _stream(self.device)),
+              "sdmmb_sample_pdf_pruned", self._h)
+        return out
+
     def sample_pdf_product(self, cell_idx, pos3, u3, bsdf, normal3=None, dir3=None, frame9=None, wi3=None):
         """Product guiding per vertex (sdmm_proc.cpp:327-339, 375-381; sdmm_product.h:62-203): conditional x
         learned-BSDF mixture.  `bsdf`: [M][7] rows (pmf, mean3, cov00, cov10, cov11) in world space; `normal3`

@@ -265,3 +265,45 @@ def test_async_records_visible_only_after_publish():
         np.testing.assert_array_equal(full[key], after[key])
     a.set_async_records(False)
     np.testing.assert_array_equal(a.sample_pdf(cell, pos3, u3, binned=True)["pdf"], after["pdf"])
+
+
+@pytest.mark.parametrize("K", [16, 64])
+def test_pruned_conditional_matches_reference(K):
+    """sdmm::create_conditional_pruned (sdmm_conditioner.h:128-168) + sample + posterior against the reference's own
+    function (oracle/_ref/libsdmm_ref_product.so): validity identical, component selection identical away from CDF
+    ties, pdf within the query tolerance; keeping every component reproduces the full query bit for bit."""
+    from oracle import refbind
+    if not refbind.product_available():
+        pytest.skip("oracle/_ref/libsdmm_ref_product.so not built")
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, N, nq = 6, 600, 3000
+    point6, weight, off = synth.make_samples(C, N, seed=60 + K)
+    joint, em, scal = synth.make_initial_model(C, K, seed=61 + K)
+    o = refbind.RefCells(C, K)
+    o.set(joint, em, scal)
+    o.em_step(off, point6, weight, 3)
+    o.prepare_conditioner()
+    j, e, s = o.get()
+    cells = SDMMCells(C, K)
+    cells.upload(j, e, s)
+    cells.prepare()
+    cell, pos3, u3 = synth.make_queries(nq, C, seed=62 + K, binned=True)
+    full = cells.sample_pdf(cell, pos3, u3, binned=True)
+    same = cells.sample_pdf_pruned(cell, pos3, u3, max_components=K)
+    for k in ("dir", "pdf", "inv_jac", "comp", "valid"):
+        np.testing.assert_array_equal(same[k].cpu().numpy().astype(full[k].dtype), full[k], err_msg=k)
+    for max_c, keep in ((4, -1), (K // 2, -1), (3, 1)):
+        r = o.pruned_sample_pdf(cell, pos3, u3, max_c, keep)
+        g = {k: v.cpu().numpy() for k, v in cells.sample_pdf_pruned(cell, pos3, u3, max_c, keep).items()}
+        np.testing.assert_array_equal(g["valid"], r["valid"])
+        v = r["valid"].astype(bool)
+        assert ((r["pmf"] > 0).sum(axis=1)[v] <= max_c).all()          # the oracle really pruned
+        agree = g["comp"].astype(np.uint32)[v] == r["comp"][v]
+        assert agree.mean() >= 0.995, (max_c, keep, agree.mean())
+        ok = v.copy()
+        ok[v] = agree
+        ok &= r["pdf"] > 1e-6
+        rel = np.abs(g["pdf"][ok] - r["pdf"][ok]) / r["pdf"][ok]
+        assert np.median(rel) < 1e-4 and np.quantile(rel, 0.999) < 5e-3, (max_c, keep, np.median(rel), rel.max())
+        np.testing.assert_allclose(g["dir"][:, ok], r["dir"][:, ok], atol=2e-4)
