@@ -195,11 +195,26 @@ int run_em_overlapped(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int wit
     *done = false;
     const uint32_t it0 = ctx->h_item_begin[rel], it1 = ctx->h_item_begin[rel + n_cells];
     if (n_cells < 2 || it1 - it0 < 2 || n_iters <= 0) return SDMMB_OK;
-    // first cell whose items start at or after the midpoint
-    const uint32_t target = it0 + (it1 - it0) / 2;
-    int mid = rel + 1;
-    while (mid < rel + n_cells - 1 && ctx->h_item_begin[mid] < target) ++mid;
-    if (ctx->h_item_begin[mid] == it0 || ctx->h_item_begin[mid] == it1) return SDMMB_OK;
+    // Parts of (nearly) equal item counts, cut at cell boundaries: 2 without peers (enough to hide the M-steps),
+    // 4 with peers attached -- the record push of a part rides in its last M-step, so only the LAST part's push
+    // (a quarter of the records) is exposed after the last E-step has drained.  SDMMB_OVERLAP_PARTS overrides.
+    constexpr int MAXP = 8;
+    static const int env_parts = [] { const char* v = getenv("SDMMB_OVERLAP_PARTS"); return v ? atoi(v) : 0; }();
+    int want = env_parts > 0 ? env_parts : ((ctx->peer.world > 1 && !ctx->d_qrec_back) ? 4 : 2);
+    want = std::max(2, std::min(MAXP, want));
+    int cut[MAXP + 1];
+    int P = 0;
+    cut[0] = rel;
+    for (int p = 1; p < want; ++p) {
+        const uint32_t target = it0 + (uint32_t)(((uint64_t)(it1 - it0) * p) / want);
+        int c = cut[P] + 1;
+        while (c < rel + n_cells - 1 && ctx->h_item_begin[c] < target) ++c;
+        if (c >= rel + n_cells) break;
+        if (ctx->h_item_begin[c] == ctx->h_item_begin[cut[P]] || ctx->h_item_begin[c] == it1) continue;   // empty part
+        cut[++P] = c;
+    }
+    cut[++P] = rel + n_cells;
+    if (P < 2) return SDMMB_OK;
     if (!ctx->ov_mstream) {
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));   // hi = numerically lowest = greatest priority
@@ -207,11 +222,12 @@ int run_em_overlapped(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int wit
         CK(cudaStreamCreateWithPriority(&ctx->ov_mstream, cudaStreamNonBlocking, hi));
         for (cudaEvent_t& e : ctx->ov_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
-    cudaEvent_t fork = ctx->ov_ev[0], ev_e[2] = {ctx->ov_ev[1], ctx->ov_ev[2]}, ev_m[2] = {ctx->ov_ev[3], ctx->ov_ev[4]};
+    cudaEvent_t fork = ctx->ov_ev[0];
+    cudaEvent_t* ev_e = ctx->ov_ev + 1;          // [MAXP] E-step of part p done
+    cudaEvent_t* ev_m = ctx->ov_ev + 1 + MAXP;   // [MAXP] M-step of part p done
     CK(cudaEventRecord(fork, st));
     for (int h = 0; h < 2; ++h) CK(cudaStreamWaitEvent(ctx->ov_stream[h], fork, 0));
     CK(cudaStreamWaitEvent(ctx->ov_mstream, fork, 0));
-    const int h_rel[2] = {rel, mid}, h_n[2] = {mid - rel, rel + n_cells - mid};
     PeerPush push[2] = {};
     if (with_conditioner) {
         int rc = arm_peer_push(ctx, push, ctx->ov_mstream);
@@ -219,8 +235,10 @@ int run_em_overlapped(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int wit
     }
     for (int it = 0; it < n_iters; ++it) {
         const bool last = (it == n_iters - 1);
-        for (int h = 0; h < 2; ++h) {
-            const uint32_t b = ctx->h_item_begin[h_rel[h]], e = ctx->h_item_begin[h_rel[h] + h_n[h]];
+        for (int p = 0; p < P; ++p) {
+            cudaStream_t es = ctx->ov_stream[p & 1];
+            const int p_rel = cut[p], p_n = cut[p + 1] - cut[p];
+            const uint32_t b = ctx->h_item_begin[p_rel], e = ctx->h_item_begin[p_rel + p_n];
             EStepLaunch L{};
             L.K = ctx->K;
             L.n_items = (int)(e - b);
@@ -233,26 +251,26 @@ int run_em_overlapped(sdmmb_ctx* ctx, int rel, int n_cells, int n_iters, int wit
             L.partials = ctx->d_partials + (size_t)b * ESTAT_PLANES * ctx->K;
             L.item_scal = ctx->d_item_scal + (size_t)b * 2;
             L.out_loglik = d_out_loglik ? d_out_loglik + (size_t)it * ctx->n_samples : nullptr;
-            CK(launch_estep(L, ctx->ov_stream[h]));
+            if (it > 0) CK(cudaStreamWaitEvent(es, ev_m[p], 0));   // E(p, it) needs M(p, it - 1)
+            CK(launch_estep(L, es));
             if (L.n_items) ctx->launches += 1;
-            CK(cudaEventRecord(ev_e[h], ctx->ov_stream[h]));
-            CK(cudaStreamWaitEvent(ctx->ov_mstream, ev_e[h], 0));
-            MStepArgs a = base_mstep_args(ctx, ctx->bound_first + h_rel[h], h_n[h], 1 | ((last && with_conditioner) ? 2 : 0));
+            CK(cudaEventRecord(ev_e[p], es));
+            CK(cudaStreamWaitEvent(ctx->ov_mstream, ev_e[p], 0));
+            MStepArgs a = base_mstep_args(ctx, ctx->bound_first + p_rel, p_n, 1 | ((last && with_conditioner) ? 2 : 0));
             a.partials = L.partials;
             a.item_scal = L.item_scal;
-            a.cell_item_begin = ctx->d_cell_item_begin + h_rel[h];
-            a.cell_sample_count = ctx->d_cell_sample_count + h_rel[h];
+            a.cell_item_begin = ctx->d_cell_item_begin + p_rel;
+            a.cell_sample_count = ctx->d_cell_sample_count + p_rel;
             a.item_base = b;
-            if (last && with_conditioner) a.peer = push[h];
+            // every part but the last pushes with the call's first epoch, the last one with its second: the
+            // peers' waits are satisfied by the second only (arm_peer_push)
+            if (last && with_conditioner) a.peer = push[p == P - 1 ? 1 : 0];
             CK(launch_mstep(a, ctx->ov_mstream));
             ctx->launches += 1;
-            if (!last) {
-                CK(cudaEventRecord(ev_m[h], ctx->ov_mstream));
-                CK(cudaStreamWaitEvent(ctx->ov_stream[h], ev_m[h], 0));
-            }
+            if (!last) CK(cudaEventRecord(ev_m[p], ctx->ov_mstream));
         }
     }
-    // join: the M stream has waited for both halves' last E-steps
+    // join: the M stream has waited for every part's last E-step
     CK(cudaEventRecord(ev_m[0], ctx->ov_mstream));
     CK(cudaStreamWaitEvent(st, ev_m[0], 0));
     ctx->ev_used = 0;   // per-launch E-step timing is meaningless while launches queue behind each other

@@ -102,7 +102,7 @@ struct sdmmb_ctx {
     // sdmmb_set_em_overlap: two E-step streams + one high-priority M-step stream, fork/E/M events
     bool em_overlap = false;
     cudaStream_t ov_stream[2] = {nullptr, nullptr}, ov_mstream = nullptr;
-    cudaEvent_t ov_ev[5] = {};
+    cudaEvent_t ov_ev[17] = {};   // fork, E-step done [8], M-step done [8]
     // peer-memory record exchange (capi_part6.inc)
     uint32_t* d_peer_flags = nullptr;   // PEER_FLAG_WORDS words, exported to the peers
     sdmmb::PeerPush peer{};                    // world == 0 until sdmmb_peer_attach
