@@ -56,6 +56,16 @@ int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, i
                     const sdmmb_camera* h_camera, const sdmmb_pt_config* h_config);
 int sdmmb_pt_destroy(sdmmb_pt* pt);
 
+/* sampleProduct (mitsuba/src/integrators/sdmm/sdmm_proc.cpp:326-392, 409-417, 476-487): guided vertices sample the
+ * PRODUCT of the cell's conditional mixture and a learned-BSDF directional mixture (the BSDF::DMM of
+ * mitsuba/include/mitsuba/render/bsdf.h:301-304) instead of the conditional alone, and the BSDF sampling fraction
+ * of the one-sample MIS drops from 0.5 to 0.3 (heuristicConditionalWeight, :383-390).  h_bsdf: n_bsdf rows of
+ * (pmf, mean3, c00, c10, c11), one mixture for the whole scene; all surfaces of this tracer are diffuse, so
+ * component 0 is re-centred on the shading normal at every vertex (:335-339).  n_bsdf = 0 switches back to the
+ * plain conditional.  A vertex whose product has no valid component is treated like one without a valid
+ * conditional (BSDF sampling, weight 1); the reference falls back to the plain conditional there (:375-381). */
+int sdmmb_pt_set_product(sdmmb_pt* pt, int n_bsdf, const float* h_bsdf);
+
 /* One render pass = `spp` paths per pixel (one iteration's samplesPerIteration).  Uses the tree bound with
  * sdmmb_set_tree and the query records of ctx.  guided = 0 reproduces iteration 0 (BSDF sampling only,
  * sdmm_proc.cpp:316-323); d_cell_initialized [max_cells] marks cells whose conditioner may be used

@@ -853,4 +853,9 @@ void sdmm_ref_tree_find_stored(void* h, long n, const float* pos3, int32_t* out_
 #endif  // SDMM_REF_WITH_JSON
 
 }  // extern "C"
+// libsdmm_ref_product.so (ref_product.cpp) compiles this file with the product-guiding entry points in front of the
+// render loop, so that the loop can take sampleSurface's product branch; libsdmm_ref.so itself stays as pinned.
+#ifdef SDMM_REF_WITH_PRODUCT
+#include "ref_product.inc"
+#endif
 #include "ref_render.inc"

@@ -4,5 +4,5 @@
 // reference's EM (-funsafe-math-optimizations -ffp-contract=fast), which moves samples sitting on the FTZ
 // underflow edge and with them the EM fixtures pinned to that build.  RefCell handles created by libsdmm_ref.so
 // are passed in as plain pointers (same headers, same flags, same layout).
+#define SDMM_REF_WITH_PRODUCT 1
 #include "ref_driver.cpp"
-#include "ref_product.inc"

@@ -393,8 +393,9 @@ class RefRenderer:
     scene; mixture, tree and EM work is the reference's own code."""
 
     def __init__(self, quads, camera, lo, norm, root_min, root_max, K=16, max_depth=5, saved_per_path=8,
-                 capacity=200000, split_threshold=4000):
-        L = lib()
+                 capacity=200000, split_threshold=4000, product_bsdf=None):
+        # the render loop with sampleSurface's product branch only exists in libsdmm_ref_product.so
+        L = self._L = product_lib() if product_bsdf is not None else lib()
         fp = C.POINTER(C.c_float)
         L.sdmm_ref_renderer_create.restype = C.c_void_p
         L.sdmm_ref_renderer_create.argtypes = [fp, C.c_int, fp, C.c_int, C.c_int, fp, C.c_float, fp, fp, C.c_int, C.c_int,
@@ -417,20 +418,24 @@ class RefRenderer:
             _f(np.asarray(root_min, np.float32)), _f(np.asarray(root_max, np.float32)), max_depth, saved_per_path, K,
             capacity, 0, split_threshold))
         self.total_spp = 0
+        if product_bsdf is not None:
+            b = np.ascontiguousarray(product_bsdf, np.float32).reshape(-1, 7)
+            L.sdmm_ref_renderer_set_product.argtypes = [C.c_void_p, C.c_int, fp]
+            assert L.sdmm_ref_renderer_set_product(self._h, b.shape[0], _f(b)) == 1
 
     def __del__(self):
         try:
-            lib().sdmm_ref_renderer_destroy(self._h)
+            self._L.sdmm_ref_renderer_destroy(self._h)
         except Exception:
             pass
 
     def set_async(self, enabled=True):
         """optimizeAsync schedule (volpath_sdmm.cpp:180-242): fits become visible one pass later."""
-        lib().sdmm_ref_renderer_set_async(self._h, 1 if enabled else 0)
+        self._L.sdmm_ref_renderer_set_async(self._h, 1 if enabled else 0)
 
     def iteration(self, spp, pass_seed, still_training, force_unguided=False):
         st = (C.c_double * 7)()
-        lib().sdmm_ref_renderer_iteration(self._h, spp, pass_seed, 1 if still_training else 0,
+        self._L.sdmm_ref_renderer_iteration(self._h, spp, pass_seed, 1 if still_training else 0,
                                           1 if force_unguided else 0, st)
         self.total_spp += spp
         keys = ["trained", "leaves", "fresh", "train_samples", "data_samples", "guided_queries", "mis_queries"]
@@ -438,17 +443,17 @@ class RefRenderer:
 
     def image(self):
         out = np.zeros((3, self.H, self.W), np.float32)
-        lib().sdmm_ref_renderer_image(self._h, _f(out))
+        self._L.sdmm_ref_renderer_image(self._h, _f(out))
         return out / max(1, self.total_spp)
 
     def nodes(self):
-        n = lib().sdmm_ref_renderer_tree_size(self._h)
+        n = self._L.sdmm_ref_renderer_tree_size(self._h)
         out = np.zeros((n, 13), np.float32)
-        lib().sdmm_ref_renderer_tree_export(self._h, _f(out))
+        self._L.sdmm_ref_renderer_tree_export(self._h, _f(out))
         return out
 
     def leaf_joint(self, node):
         joint = np.zeros((JOINT_PLANES, self.K), np.float32)
         scal = np.zeros(SCALAR_WORDS, np.uint32)
-        k = lib().sdmm_ref_renderer_leaf_joint(self._h, node, _f(joint), _u(scal))
+        k = self._L.sdmm_ref_renderer_leaf_joint(self._h, node, _f(joint), _u(scal))
         return (joint, scal) if k else (None, None)

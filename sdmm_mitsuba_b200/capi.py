@@ -32,7 +32,7 @@ SYMBOLS = [
     "sdmmb_launch_count", "sdmmb_last_estep_ms", "sdmmb_measure_peaks", "sdmmb_initialize", "sdmmb_initialize_host",
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
     "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
-    "sdmmb_host_alloc", "sdmmb_host_free", "sdmmb_sample_pdf_pruned",
+    "sdmmb_host_alloc", "sdmmb_host_free", "sdmmb_sample_pdf_pruned", "sdmmb_pt_set_product",
 ]
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
 ITERS_INTEGRATOR = -1    # SDMMB_ITERS_INTEGRATOR: the integrator's 2|1 iteration rule per cell
@@ -138,6 +138,7 @@ def lib():
     L.sdmmb_host_free.argtypes = [vp]
     L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
     L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp]
+    L.sdmmb_pt_set_product.argtypes = [vp, i, fp]
     L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):

@@ -14,6 +14,9 @@ struct sdmmb_pt {
     void* d_lists = nullptr;
     size_t lists_cap = 0;      // in paths
     uint32_t* d_counters = nullptr;
+    // sampleProduct: scene-wide learned-BSDF mixture [n_bsdf][7] on the device (0 = plain conditional guiding)
+    float* d_bsdf = nullptr;
+    int n_bsdf = 0;
 };
 
 namespace {
@@ -51,12 +54,62 @@ void pt_carve_lists(sdmmb_pt* pt, size_t n, PtLists& L) {
     L.compA = (uint32_t*)take(n * 4); L.validA = (uint8_t*)take(n);
     L.cellB = (uint32_t*)take(n * 4); L.posB = (float*)take(3 * n * 4); L.dirB = (float*)take(3 * n * 4);
     L.pdfB = (float*)take(n * 4); L.validB = (uint8_t*)take(n);
+    L.nrmA = (float*)take(3 * n * 4); L.nrmB = (float*)take(3 * n * 4);
     L.counters = pt->d_counters;
+}
+
+// one product-guiding query launch over a list of the tracer (the BSDF table already lives on the device)
+int product_query(sdmmb_ctx* ctx, sdmmb_pt* pt, size_t n, const uint32_t* cell, const float* pos3, const float* u3,
+                  const float* dir3, const float* normal3, float* out_dir3, float* out_pdf, float* out_ij,
+                  uint32_t* out_comp, uint8_t* out_valid, cudaStream_t st) {
+    void* scratch = nullptr;
+    int rc = stream_scratch(ctx, st, (2 * ((size_t)ctx->max_cells + 1) + 9 * n + 4) * 4, &scratch);
+    if (rc) return rc;
+    ProductLaunch q{};
+    q.scratch = (uint32_t*)scratch;
+    q.K = ctx->K;
+    q.K_user = ctx->K_user;
+    q.max_cells = ctx->max_cells;
+    q.n = n;
+    q.qrec = ctx->d_qrec;
+    q.cell_idx = cell;
+    q.pos3 = pos3;
+    q.u3 = u3;
+    q.dir3 = dir3;
+    q.normal3 = normal3;
+    q.M = pt->n_bsdf;
+    q.bsdf = pt->d_bsdf;
+    q.out_dir3 = out_dir3;
+    q.out_pdf = out_pdf;
+    q.out_inv_jac = out_ij;
+    q.out_comp = out_comp;
+    q.out_valid = out_valid;
+    CK(launch_product_query(q, st));
+    ctx->launches += 4;
+    return SDMMB_OK;
 }
 
 }  // namespace
 
 extern "C" {
+
+int sdmmb_pt_set_product(sdmmb_pt* pt, int n_bsdf, const float* h_bsdf) {
+    if (!pt || n_bsdf < 0 || n_bsdf > SDMMB_PRODUCT_MAX_BSDF || (n_bsdf > 0 && !h_bsdf)) return SDMMB_E_INVALID;
+    sdmmb_ctx* ctx = pt->ctx;
+    for (int m = 0; m < n_bsdf; ++m) {
+        const float* b = h_bsdf + 7 * m;
+        if (!(b[0] >= 0.f) || !(b[1] * b[1] + b[2] * b[2] + b[3] * b[3] > 0.f)) return SDMMB_E_INVALID;
+    }
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    CK(cudaDeviceSynchronize());
+    if (n_bsdf > 0) {
+        if (!pt->d_bsdf) CK(cudaMalloc(&pt->d_bsdf, (size_t)SDMMB_PRODUCT_MAX_BSDF * 7 * 4));
+        CK(cudaMemcpy(pt->d_bsdf, h_bsdf, (size_t)n_bsdf * 7 * 4, cudaMemcpyHostToDevice));
+    }
+    pt->n_bsdf = n_bsdf;
+    return SDMMB_OK;
+}
 
 int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, int n_quads,
                     const sdmmb_camera* cam, const sdmmb_pt_config* cfg) {
@@ -109,7 +162,7 @@ int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, i
 int sdmmb_pt_destroy(sdmmb_pt* pt) {
     if (!pt) return SDMMB_OK;
     DeviceGuard g(pt->ctx->device);
-    cudaFree(pt->d_scene); cudaFree(pt->d_paths); cudaFree(pt->d_lists); cudaFree(pt->d_counters);
+    cudaFree(pt->d_scene); cudaFree(pt->d_paths); cudaFree(pt->d_lists); cudaFree(pt->d_counters); cudaFree(pt->d_bsdf);
     delete pt;
     return SDMMB_OK;
 }
@@ -134,7 +187,7 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     }
     if (guided && n > pt->lists_cap) {
         cudaFree(pt->d_lists); pt->d_lists = nullptr; pt->lists_cap = 0;
-        CK(cudaMalloc(&pt->d_lists, n * 160 + 64 * 256));  // 150 B of records + query planes per path
+        CK(cudaMalloc(&pt->d_lists, n * 184 + 64 * 256));  // 174 B of records + query planes per path
         pt->lists_cap = n;
     }
     PtPaths P{};
@@ -148,6 +201,7 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     F.cell_initialized = d_cell_initialized;
     F.max_cells = (uint32_t)ctx->max_cells;
     F.guided = guided ? 1 : 0;
+    F.w_bsdf = pt->n_bsdf > 0 ? 0.3f : 0.5f;   // heuristicConditionalWeight with / without the product  R: 383-390
     F.collect = collect ? 1 : 0;
     F.seed = seed;
     F.spp = spp;
@@ -173,15 +227,28 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
         nA = c2[0];
         nB = c2[1];
         if (nA + nB == 0) continue;
-        CK(pt_launch_pack_lists(L, nA, nB, st));
+        CK(pt_launch_pack_lists(pt->d_scene, L, nA, nB, st));
         ++launches;
-        if (nA) {
-            int rc = query_common(ctx, nA, L.cellA, L.posA, L.uA, nullptr, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, 0, st);
-            if (rc) return rc;
-        }
-        if (nB) {
-            int rc = query_common(ctx, nB, L.cellB, L.posB, nullptr, L.dirB, nullptr, L.pdfB, nullptr, nullptr, L.validB, 0, st);
-            if (rc) return rc;
+        if (pt->n_bsdf > 0) {
+            // sampleProduct: conditional x learned-BSDF mixture, component 0 re-centred on the shading normal
+            // (every surface here is diffuse: sdmm_proc.cpp:335-339), sampled / evaluated per vertex (:375-381, 409-417)
+            if (nA) {
+                int rc = product_query(ctx, pt, nA, L.cellA, L.posA, L.uA, nullptr, L.nrmA, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, st);
+                if (rc) return rc;
+            }
+            if (nB) {
+                int rc = product_query(ctx, pt, nB, L.cellB, L.posB, nullptr, L.dirB, L.nrmB, nullptr, L.pdfB, nullptr, nullptr, L.validB, st);
+                if (rc) return rc;
+            }
+        } else {
+            if (nA) {
+                int rc = query_common(ctx, nA, L.cellA, L.posA, L.uA, nullptr, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, 0, st);
+                if (rc) return rc;
+            }
+            if (nB) {
+                int rc = query_common(ctx, nB, L.cellB, L.posB, nullptr, L.dirB, nullptr, L.pdfB, nullptr, nullptr, L.validB, 0, st);
+                if (rc) return rc;
+            }
         }
         qa += nA;
         qb += nB;

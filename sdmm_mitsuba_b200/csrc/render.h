@@ -53,12 +53,13 @@ struct PtPaths {
 
 struct PtLists {
     // AoS staging records written by the bounce kernel (slot allocated with atomicAdd)
-    float* recA;        // [n][8]: cell(bits), npos3, g0, g1, g2, -
-    float* recB;        // [n][8]: cell(bits), npos3, dir3, -
+    float* recA;        // [n][8]: cell(bits), npos3, g0, g1, g2, quad(bits)
+    float* recB;        // [n][8]: cell(bits), npos3, dir3, quad(bits)
     uint32_t* counters; // [0] nA, [1] nB, [2] pool count, [3] pool overflow
     // dense SoA query inputs/outputs (stride = list length)
     uint32_t* cellA; float* posA; float* uA; float* dirA; float* pdfA; float* ijA; uint32_t* compA; uint8_t* validA;
     uint32_t* cellB; float* posB; float* dirB; float* pdfB; uint8_t* validB;
+    float* nrmA; float* nrmB;   // [3][n] shading normals of the vertices (product guiding re-centres the BSDF lobe on them)
 };
 
 struct PtFrame {
@@ -67,6 +68,7 @@ struct PtFrame {
     const uint8_t* cell_initialized;  // [max_cells]
     uint32_t max_cells;
     int guided;
+    float w_bsdf;     // heuristicConditionalWeight: 0.5, or 0.3 with product guiding (sdmm_proc.cpp:383-390)
     int collect;
     uint64_t seed;
     int spp;
@@ -78,7 +80,7 @@ struct PtFrame {
 cudaError_t pt_launch_generate(const PtScene* d_scene, const PtPaths& P, const PtFrame& F, cudaStream_t st);
 cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, int first,
                              size_t nA, size_t nB, cudaStream_t st);
-cudaError_t pt_launch_pack_lists(const PtLists& L, size_t nA, size_t nB, cudaStream_t st);
+cudaError_t pt_launch_pack_lists(const PtScene* d_scene, const PtLists& L, size_t nA, size_t nB, cudaStream_t st);
 cudaError_t pt_launch_finish(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, cudaStream_t st);
 
 }  // namespace sdmmb

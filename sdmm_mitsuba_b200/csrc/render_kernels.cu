@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
                 const float cos_o = dot(nrm, wo);
                 const float bsdfPdf = cos_o * PT_INV_PI;
                 if (!(bsdfPdf > 0.f)) alive = false;     // pdfSurface: bsdfPdf <= 0 -> 0       R: 527-530
-                misPdf = 0.5f * bsdfPdf + 0.5f * L.pdfA[slot];
+                misPdf = F.w_bsdf * bsdfPdf + (1.f - F.w_bsdf) * L.pdfA[slot];      // R: 587-589
                 const float f = PT_INV_PI * cos_o / misPdf;   // bsdf->eval / pdf               R: 464, 507
                 weight = rho * f;
             } else {
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
             const float bsdfPdf = loc.z * PT_INV_PI;
             if (!(bsdfPdf > 0.f)) alive = false;
             if (mode == 1 && L.validB[slot]) {
-                misPdf = 0.5f * bsdfPdf + 0.5f * L.pdfB[slot];   // bsdfWeight *= pdf; / pdfSurface  R: 404, 507
+                misPdf = F.w_bsdf * bsdfPdf + (1.f - F.w_bsdf) * L.pdfB[slot];   // bsdfWeight *= pdf; / pdfSurface  R: 404, 507
                 weight = rho * (bsdfPdf / misPdf);
             } else {
                 misPdf = bsdfPdf;                        // pdf *= 1; bsdfWeight / 1            R: 398-402
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
             const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, npos, sc.root_min, sc.root_max, amin, amax,
                                                  0xffffffffu);
             if (cell < F.max_cells && F.cell_initialized[cell]) {
-                if (u_mis <= 0.5f) {                     // heuristicConditionalWeight       R: 383-392
+                if (u_mis <= F.w_bsdf) {                 // heuristicConditionalWeight       R: 383-392
                     mode = 1;
                     const PtQuad& H = sc.quads[hq];
                     const V3 hn = ld3(H.n);
@@ -294,13 +294,13 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
                     slot = atomicAdd(&L.counters[1], 1u);
                     float4* r = reinterpret_cast<float4*>(L.recB + (size_t)slot * 8);
                     r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
-                    r[1] = make_float4(wo.x, wo.y, wo.z, 0.f);
+                    r[1] = make_float4(wo.x, wo.y, wo.z, __int_as_float(hq));
                 } else {
                     mode = 2;
                     slot = atomicAdd(&L.counters[0], 1u);
                     float4* r = reinterpret_cast<float4*>(L.recA + (size_t)slot * 8);
                     r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
-                    r[1] = make_float4(g0, g1, g2, 0.f);
+                    r[1] = make_float4(g0, g1, g2, __int_as_float(hq));
                 }
             }
         }
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
 }
 
 // AoS staging records -> the dense SoA planes (stride = list length) the query kernels take
-__global__ void pt_pack_lists_kernel(PtLists L, size_t nA, size_t nB) {
+__global__ void pt_pack_lists_kernel(const PtScene* __restrict__ scp, PtLists L, size_t nA, size_t nB) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nA) {
         const float4* r = reinterpret_cast<const float4*>(L.recA + i * 8);
@@ -327,6 +327,8 @@ __global__ void pt_pack_lists_kernel(PtLists L, size_t nA, size_t nB) {
         L.cellA[i] = __float_as_uint(a.x);
         L.posA[i] = a.y; L.posA[nA + i] = a.z; L.posA[2 * nA + i] = a.w;
         L.uA[i] = b.x; L.uA[nA + i] = b.y; L.uA[2 * nA + i] = b.z;
+        const float* nq = scp->quads[__float_as_int(b.w)].n;      // shading normal (product guiding)
+        L.nrmA[i] = nq[0]; L.nrmA[nA + i] = nq[1]; L.nrmA[2 * nA + i] = nq[2];
     }
     if (i < nB) {
         const float4* r = reinterpret_cast<const float4*>(L.recB + i * 8);
@@ -334,6 +336,8 @@ __global__ void pt_pack_lists_kernel(PtLists L, size_t nA, size_t nB) {
         L.cellB[i] = __float_as_uint(a.x);
         L.posB[i] = a.y; L.posB[nB + i] = a.z; L.posB[2 * nB + i] = a.w;
         L.dirB[i] = b.x; L.dirB[nB + i] = b.y; L.dirB[2 * nB + i] = b.z;
+        const float* nq = scp->quads[__float_as_int(b.w)].n;
+        L.nrmB[i] = nq[0]; L.nrmB[nB + i] = nq[1]; L.nrmB[2 * nB + i] = nq[2];
     }
 }
 
@@ -412,10 +416,10 @@ cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtL
     return cudaGetLastError();
 }
 
-cudaError_t pt_launch_pack_lists(const PtLists& L, size_t nA, size_t nB, cudaStream_t st) {
+cudaError_t pt_launch_pack_lists(const PtScene* d_scene, const PtLists& L, size_t nA, size_t nB, cudaStream_t st) {
     const size_t m = nA > nB ? nA : nB;
     if (m == 0) return cudaSuccess;
-    pt_pack_lists_kernel<<<blocks_for(m, 256), 256, 0, st>>>(L, nA, nB);
+    pt_pack_lists_kernel<<<blocks_for(m, 256), 256, 0, st>>>(d_scene, L, nA, nB);
     return cudaGetLastError();
 }
 

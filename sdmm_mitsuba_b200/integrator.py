@@ -78,6 +78,14 @@ class SDMMIntegrator:
         self.total_spp = 0
         self.stats = []
 
+    def set_product(self, bsdf):
+        """sampleProduct (sdmm_proc.cpp:326-392): guided vertices sample conditional x learned-BSDF mixture; `bsdf` =
+        [M, 7] rows (pmf, mean3, c00, c10, c11), one mixture for the whole (diffuse) scene, component 0 re-centred on
+        the shading normal per vertex; the BSDF fraction of the MIS drops to 0.3.  None / empty switches it off."""
+        b = np.zeros((0, 7), np.float32) if bsdf is None else np.ascontiguousarray(bsdf, np.float32).reshape(-1, 7)
+        check(self.cells._L.sdmmb_pt_set_product(self._pt, int(b.shape[0]), b.ctypes.data_as(C.POINTER(C.c_float))),
+              "sdmmb_pt_set_product", self.cells._h)
+
     def close(self):
         if getattr(self, "_pt", None) is not None and self._pt:
             self.cells._L.sdmmb_pt_destroy(self._pt)

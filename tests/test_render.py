@@ -129,6 +129,57 @@ def test_progressive_loop_matches_cpu_restatement(oracle_ref):
 
 
 @pytest.mark.gpu
+def test_product_guiding_in_the_tracer_matches_cpu_restatement(oracle_ref):
+    """sampleProduct inside the device path tracer (sdmm_proc.cpp:326-392, 409-417, 476-487): guided vertices sample
+    conditional x learned-BSDF mixture (component 0 re-centred on the shading normal: all surfaces are diffuse), the
+    BSDF fraction of the MIS is 0.3.  Oracle: the same loop on the CPU calling the reference's own sdmm::product
+    (oracle/ref_render.inc compiled into libsdmm_ref_product.so); learned-BSDF files are LFS-only, so the mixture is
+    synthetic (a cosine-like lobe about the normal + two broad side lobes)."""
+    if not oracle_ref.product_available():
+        pytest.skip("oracle/_ref/libsdmm_ref_product.so not built")
+    from sdmm_mitsuba_b200 import scenes
+    from sdmm_mitsuba_b200.integrator import SDMMIntegrator
+    W, H, K, MD, SPI = 320, 180, 16, 5, 64
+    bsdf = np.array([[0.6, 0, 0, 1, 0.45, 0.0, 0.45],
+                     [0.2, 0.6, 0.0, 0.8, 0.30, 0.05, 0.25],
+                     [0.2, -0.6, 0.0, 0.8, 0.30, -0.05, 0.25]], np.float32)
+    quads, cam = scenes.cornell_box(W, H)
+    lo, hi, norm = scenes.scene_bounds(quads)
+    rmin, rmax = scenes.root_aabb(lo, hi, norm)
+    g = SDMMIntegrator(quads, cam, K=K, max_depth=MD, samples_per_iteration=SPI, seed=7, pool_capacity=4_000_000)
+    g.set_product(bsdf)
+    r = oracle_ref.RefRenderer(quads, cam, lo, norm, rmin, rmax, K=K, max_depth=MD, capacity=150000, product_bsdf=bsdf)
+    plain = SDMMIntegrator(quads, cam, K=K, max_depth=MD, samples_per_iteration=SPI, seed=7, pool_capacity=4_000_000)
+    stats = []
+    for it in range(3):
+        seed = (g.seed * 0x9E3779B97F4A7C15 + g.iteration) & 0xFFFFFFFFFFFFFFFF
+        st, new = g.render_pass(SPI, collect=True)
+        g.optimize(new)
+        g.iteration += 1
+        g.total_spp += SPI
+        rs = r.iteration(SPI, seed, True)
+        stp, newp = plain.render_pass(SPI, collect=True)
+        plain.optimize(newp)
+        plain.iteration += 1
+        plain.total_spp += SPI
+        stats.append((int(st.guided_queries), int(st.mis_queries), rs, int(stp.guided_queries), int(stp.mis_queries)))
+        ig, ir = g.image(), r.image()
+        assert abs(ig.mean() - ir.mean()) <= 2e-3 * ir.mean(), (it, ig.mean(), ir.mean())
+        if it < 2:
+            assert np.abs(ig - ir).mean() <= 1e-5 * ir.mean(), (it, np.abs(ig - ir).mean())
+    ga, gb, rs, pa, pb = stats[2]
+    assert ga > 100000 and gb > 50000
+    # the same vertices were guided as in the oracle, and with the 0.3 / 0.7 split instead of 0.5 / 0.5
+    assert abs(ga - rs["guided_queries"]) <= 2e-3 * ga and abs(gb - rs["mis_queries"]) <= 2e-3 * gb
+    frac = gb / float(ga + gb)
+    assert 0.28 < frac < 0.32, frac
+    assert 0.48 < pb / float(pa + pb) < 0.52
+    # guided iteration: images agree with the CPU restatement far below the noise of the estimate
+    ig, ir = g.image(), r.image()
+    assert np.abs(ig - ir).mean() <= 2e-2 * ir.mean(), np.abs(ig - ir).mean() / ir.mean()
+
+
+@pytest.mark.gpu
 def test_async_schedule_matches_cpu_restatement(oracle_ref):
     """optimizeAsync, the reference's default schedule (volpath_sdmm.cpp:65, 180-242): fits become visible one pass
     later (double-buffered records + deferred `initialized` flags), one em_step per fit, seeds spaced from 0.1 x the
