@@ -53,6 +53,26 @@ __device__ __forceinline__ float rcp_sinc_from_cos(float c) {
     return num * u;
 }
 
+// the same for the two vertices of a pair: the polynomial and the final product ride in packed instructions
+// (each half is the IEEE fma sequence of the scalar form above: bit-identical results)
+__device__ __forceinline__ float2 rcp_sinc_from_cos2(float2 c) {
+    const float2 a = make_float2(fminf(fabsf(c.x), 0.99999994f), fminf(fabsf(c.y), 0.99999994f));
+    float2 P = make_float2(2.295893482e-03f, 2.295893482e-03f);
+    P = __ffma2_rn(P, a, make_float2(-1.114577623e-02f, -1.114577623e-02f));
+    P = __ffma2_rn(P, a, make_float2(2.689914581e-02f, 2.689914581e-02f));
+    P = __ffma2_rn(P, a, make_float2(-4.880191494e-02f, -4.880191494e-02f));
+    P = __ffma2_rn(P, a, make_float2(8.875543537e-02f, 8.875543537e-02f));
+    P = __ffma2_rn(P, a, make_float2(-2.145852374e-01f, -2.145852374e-01f));
+    P = __ffma2_rn(P, a, make_float2(1.570796172e+00f, 1.570796172e+00f));
+    const float2 opa = __fadd2_rn(a, make_float2(1.f, 1.f));
+    const float2 oma = __fadd2_rn(make_float2(1.f, 1.f), make_float2(-a.x, -a.y));
+    const float2 u = make_float2(q_rsqrt(opa.x), q_rsqrt(opa.y));
+    const float2 v = make_float2(q_rsqrt(oma.x), q_rsqrt(oma.y));
+    const float2 alt = __ffma2_rn(make_float2(kPi, kPi), v, make_float2(-P.x, -P.y));
+    const float2 num = make_float2(c.x >= 0.f ? P.x : alt.x, c.y >= 0.f ? P.y : alt.y);
+    return __fmul2_rn(num, u);
+}
+
 struct QRec {
     float4 v[8];
     __device__ __forceinline__ float f(int i) const { return reinterpret_cast<const float*>(v)[i]; }
@@ -253,7 +273,7 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float
         const float2 lx = q_fma2(q_splat(r.f(QREC_R + 2)), in.wz, q_fma2(q_splat(r.f(QREC_R + 1)), in.wy, q_mul2(q_splat(r.f(QREC_R + 0)), in.wx)));
         const float2 ly = q_fma2(q_splat(r.f(QREC_R + 5)), in.wz, q_fma2(q_splat(r.f(QREC_R + 4)), in.wy, q_mul2(q_splat(r.f(QREC_R + 3)), in.wx)));
         const float2 lz = q_fma2(q_splat(r.f(QREC_R + 8)), in.wz, q_fma2(q_splat(r.f(QREC_R + 7)), in.wy, q_mul2(q_splat(r.f(QREC_R + 6)), in.wx)));
-        const float2 rs = make_float2(rcp_sinc_from_cos(lz.x), rcp_sinc_from_cos(lz.y));
+        const float2 rs = rcp_sinc_from_cos2(lz);
         const float2 ij = make_float2((lz.x < -0.98f) ? 0.f : rs.x, (lz.y < -0.98f) ? 0.f : rs.y);
         const float2 t0 = q_fma2(lx, rs, make_float2(-tm0.x, -tm0.y)), t1 = q_fma2(ly, rs, make_float2(-tm1.x, -tm1.y));
         const float2 z0 = q_mul2(q_splat(r.f(QREC_WC + 0)), t0);

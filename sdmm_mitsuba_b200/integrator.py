@@ -264,22 +264,11 @@ class SDMMIntegrator:
                                           normal3[:, base:base + int(sub_off[-1])].contiguous(),
                                           weight[base:base + int(sub_off[-1])].contiguous(), sub_off, sd, first_cell=a)
                 self.has_mixture[fresh] = True
-            # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305); optimize_async_run: always 1 (:217)
-            if self.optimize_async:
-                iters_run = np.full(self.cells.max_cells, 4, np.int64)       # one em_step per fit, no read-back
-            else:
-                _, _, scal = self.cells.download(want_em=False)
-                iters_run = scal[:, 1].astype(np.int64)
+            # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305): the rule is applied per cell ON
+            # the device (SDMMB_ITERS_INTEGRATOR), no read-back of the iteration counters and no second gather of the
+            # young cells' samples; optimize_async_run: always 1 (:217)
             self.cells.set_samples(point6, weight, off)
-            self.cells.em_step(1, with_conditioner=True)
-            twice = can & (iters_run < 4)
-            if twice.any():
-                sel2 = torch.as_tensor(twice, device=self.dev)[cells_all[idx]]
-                p2 = train[:, sel2].contiguous()
-                counts2 = np.where(twice, data_size, 0)
-                off2 = np.concatenate([[0], np.cumsum(counts2)]).astype(np.uint32)
-                self.cells.set_samples(p2[0:6].contiguous(), p2[9].contiguous(), off2)
-                self.cells.em_step(1, with_conditioner=True)
+            self.cells.em_step(1 if self.optimize_async else capi.ITERS_INTEGRATOR, with_conditioner=True)
         if self.optimize_async:
             self._pending = can_t          # published by publish_pending() after the next pass
         else:

@@ -49,5 +49,6 @@ def test_gpu_queries_match_golden(name, binned):
     cells.prepare()
     q = cells.sample_pdf(g["q_cell"], g["q_pos3"], g["q_u3"], binned=binned)
     G.check_queries(g, q, "gpu " + name)
+    G.check_query_pdf_cause(g, q, "gpu " + name)
     p, v = cells.pdf(g["q_cell"], g["q_pos3"], g["p_dir"], binned=binned)
     G.check_pdf(g, p, v, "gpu " + name)
