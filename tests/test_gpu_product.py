@@ -115,6 +115,53 @@ def _shading_frames(n, seed):
     return frame9, np.ascontiguousarray(wi.T.astype(np.float32))
 
 
+def test_product_pdf_outliers_are_float32_conditioning():
+    """Why the product pdf is held to 2e-3 at the 99th percentile and 5e-2 at the maximum instead of 1e-4: at the
+    vertices where GPU and reference differ most the product pdf amplifies float32 rounding several-hundred-fold.
+    Three differences are measured against the FLOAT64 evaluation of the reference's formulas (product_f64.py):
+    the two sides' conditioner planes agree to float32 rounding, yet that alone moves the float64 pdf by ~6e-3
+    there; the REFERENCE's own float32 result is as far from float64 as the GPU's; and the GPU is never further
+    from float64 than 3 x the reference's worst.  At typical vertices all three are below 1e-4."""
+    from product_f64 import product_pdf64
+    K, C, n = 128, 4, 6000
+    cells, ref, cell, pos3, u3, nrm = _setup(C, K, n, seed=50 + K)
+    bsdf = _bsdf()
+    rng = np.random.default_rng(3)
+    d = rng.normal(size=(3, n)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=0, keepdims=True)
+    d = np.ascontiguousarray(d)                       # pdf at GIVEN directions: no sampled-direction difference
+    gp = cells.sample_pdf_product(cell, pos3, None, bsdf, normal3=nrm, dir3=d)
+    rp, _ = ref.product_sample_pdf(cell, pos3, bsdf, dir3=d, normal3=nrm)
+    gpdf = gp["pdf"].cpu().numpy() if hasattr(gp["pdf"], "cpu") else np.asarray(gp["pdf"])
+    Pg, Pr = cells.conditioner(), ref.conditioner()
+    big = rp["valid"].astype(bool) & (rp["pdf"] > 1e-6)
+    rel = np.where(big, np.abs(gpdf - rp["pdf"]) / np.maximum(rp["pdf"], 1e-30), 0)
+    worst = list(np.argsort(-rel)[:16])
+    typical = list(np.nonzero(big)[0][:16])
+    e_gpu, e_ref, e_in = [], [], []
+    for i in worst + typical:
+        c = int(cell[i])
+        fg = product_pdf64(Pg[c], pos3[:, i], bsdf, nrm[:, i], d[:, i])
+        fr = product_pdf64(Pr[c], pos3[:, i], bsdf, nrm[:, i], d[:, i])
+        e_in.append(abs(fg - fr) / fr)
+        e_gpu.append(abs(gpdf[i] - fg) / fg)
+        e_ref.append(abs(rp["pdf"][i] - fr) / fr)
+    e_gpu, e_ref, e_in = np.array(e_gpu), np.array(e_ref), np.array(e_in)
+    print("product pdf vs float64: inputs %.2e | worst 16: gpu %.2e ref %.2e | typical: gpu %.2e ref %.2e | gpu-ref worst %.2e"
+          % (e_in.max(), e_gpu[:16].max(), e_ref[:16].max(), np.median(e_gpu[16:]), np.median(e_ref[16:]), rel[worst[0]]))
+    # the two sides' conditioner planes (float32 prepare(): Cholesky of Sigma_aa, Schur complement) agree to float32
+    # rounding; at the worst vertices that alone moves the FLOAT64 pdf by up to ~6e-3 -- the amplification that also
+    # separates each side's float32 evaluation from float64
+    cs = sorted(set(int(cell[i]) for i in worst))
+    plane = max(float((np.abs(Pg[c] - Pr[c]).max(axis=1) / np.maximum(np.abs(Pr[c]).max(axis=1), 1e-30)).max())
+                for c in cs)
+    print("conditioner planes: worst relative difference %.2e -> float64 pdf moves %.2e (x%.0f)" % (plane, e_in.max(), e_in.max() / max(plane, 1e-30)))
+    assert plane < 5e-6, plane                        # measured 4.4e-7 (a few float32 ulp) -> pdf moves 6e-3: x14000
+    assert np.median(e_in[16:]) < 1e-4 and np.median(e_gpu[16:]) < 1e-4 and np.median(e_ref[16:]) < 1e-4   # typical vertices: exact
+    assert e_ref[:16].max() > 0.3 * rel[worst[0]], (e_ref[:16].max(), rel[worst[0]])   # the reference's own float32 is off as far
+    assert e_gpu.max() <= 3 * e_ref.max() + 1e-4, (e_gpu.max(), e_ref.max())
+
+
 @pytest.mark.parametrize("K", [16, 64])
 def test_product_glossy_branch_parity(K):
     """sdmm_proc.cpp:340-355: the BSDF mixture is given in the local shading frame; per vertex it is rotated to the
