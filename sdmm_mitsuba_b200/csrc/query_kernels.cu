@@ -78,11 +78,22 @@ struct QRec {
     __device__ __forceinline__ float f(int i) const { return reinterpret_cast<const float*>(v)[i]; }
 };
 
-template <bool SMEM>
+// Where record k starts (in float4) in a record array.  SW = false: the conditioner's own layout in global memory,
+// 8 float4 per record.  SW = true: the shared-memory copy, skewed by one float4 per record and one more per block
+// of QBLOCK records (k * 9 + k / 8): in the uniform loops every lane reads the same address (broadcast), but in the
+// per-vertex parts (block re-scan of pass 2: lanes at the same j of DIFFERENT blocks; Box-Muller of the selected
+// component: arbitrary k) lanes read different records, and with a 128-byte stride those all sit in the same
+// 16-byte bank group -- a 32-way conflict per LDS.128 that made shared-memory wavefronts the busiest unit of the
+// kernel (l1tex 67 %).  With the skew, bank group = (block + j + i) mod 8.
+template <bool SW>
+__device__ __forceinline__ int qoff(int k) { return SW ? k * 9 + (k >> 3) : k * 8; }
+
+template <bool SW>
 __device__ __forceinline__ QRec load_rec(const float4* __restrict__ base, int k) {
     QRec r;
+    const float4* p = base + qoff<SW>(k);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r.v[i] = SMEM ? base[k * 8 + i] : __ldg(base + k * 8 + i);
+    for (int i = 0; i < 8; ++i) r.v[i] = p[i];
     return r;
 }
 
@@ -115,7 +126,8 @@ struct PairRes {
 // registers, not by a K x threads shared-memory column.  Same instruction sequence each time ->
 // bit-identical weights in every pass.
 __device__ __forceinline__ float2 pair_weight(const float4* __restrict__ rec, int k, const PairIn& in) {
-    const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
+    const float4* rk = rec + qoff<true>(k);
+    const float4 r0 = rk[0], r1 = rk[1], r2 = rk[2];
     // r0 = (mu0, mu1, mu2, wa00), r1 = (wa10, wa11, wa20, wa21), r2 = (wa22, nlca, m00, m01)
     const float2 d0 = q_sub2(in.x, q_splat(r0.x)), d1 = q_sub2(in.y, q_splat(r0.y)), d2 = q_sub2(in.z, q_splat(r0.z));
     const float2 z0 = q_mul2(q_splat(r0.w), d0);
@@ -129,8 +141,10 @@ __device__ __forceinline__ float2 pair_weight(const float4* __restrict__ rec, in
 
 // The same weight for ONE vertex with scalar instructions (each half of a packed FFMA2 is an IEEE fma,
 // so this is bit-identical to the corresponding half of pair_weight).
+template <bool SW>
 __device__ __forceinline__ float single_weight(const float4* __restrict__ rec, int k, float x, float y, float z) {
-    const float4 r0 = rec[k * 8 + 0], r1 = rec[k * 8 + 1], r2 = rec[k * 8 + 2];
+    const float4* rk = rec + qoff<SW>(k);
+    const float4 r0 = rk[0], r1 = rk[1], r2 = rk[2];
     const float d0 = x - r0.x, d1 = y - r0.y, d2 = z - r0.z;
     const float z0 = r0.w * d0;
     const float z1 = fmaf(r1.y, d1, r1.x * d0);
@@ -163,18 +177,19 @@ __device__ __forceinline__ int select_component(const float4* __restrict__ rec, 
 #pragma unroll
         for (int j = 0; j < QBLOCK; ++j) {
             const int k = b * QBLOCK + j;
-            const float w = single_weight(rec, k, x, y, z);
+            const float w = single_weight<true>(rec, k, x, y, z);
             run = (k == 0) ? w : run + w;
             if (!found && !(run * inv < u0)) { sel = k; found = true; }
         }
     }
     // back off over zero-pmf components
-    while (sel > 0 && single_weight(rec, sel, x, y, z) * inv == 0.f) --sel;
+    while (sel > 0 && single_weight<true>(rec, sel, x, y, z) * inv == 0.f) --sel;
     return sel;
 }
 
 // Box-Muller + `L_c z` + offset exp map of component `sel` for one vertex        R: sdmm.h:238-265,
 // spaces/offset_directional.h:62-82
+template <bool SW>
 __device__ __forceinline__ void sample_direction(const float4* __restrict__ rec, int sel, float x, float y, float z,
                                                  float u1, float u2, float& wx, float& wy, float& wz, float& ij) {
     float radius = sqrtf(-2.f * logf(1.f - u1));
@@ -182,7 +197,7 @@ __device__ __forceinline__ void sample_direction(const float4* __restrict__ rec,
     float sn, cs;
     sincosf(theta, &sn, &cs);
     float g0 = sn * radius, g1 = cs * radius;
-    const QRec r = load_rec<true>(rec, sel);
+    const QRec r = load_rec<SW>(rec, sel);
     float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
     float tm0 = r.f(QREC_M + 0) * dx0 + r.f(QREC_M + 1) * dx1 + r.f(QREC_M + 2) * dx2;
     float tm1 = r.f(QREC_M + 3) * dx0 + r.f(QREC_M + 4) * dx1 + r.f(QREC_M + 5) * dx2;
@@ -203,9 +218,10 @@ __device__ __forceinline__ void sample_direction(const float4* __restrict__ rec,
 
 // conditional pdf of component k at direction w for ONE vertex: the scalar twin of pass 3 of query_pair (each half
 // of a packed FFMA2 is an IEEE fma, so this reproduces that half bit for bit)          R: sdmm.h:284-313, 331-339
+template <bool SW>
 __device__ __forceinline__ float cond_pdf_single(const float4* __restrict__ rec, int k, float x, float y, float z,
                                                  float wx, float wy, float wz) {
-    const QRec r = load_rec<true>(rec, k);
+    const QRec r = load_rec<SW>(rec, k);
     const float dx0 = x - r.f(QREC_MU + 0), dx1 = y - r.f(QREC_MU + 1), dx2 = z - r.f(QREC_MU + 2);
     const float tm0 = fmaf(r.f(QREC_M + 2), dx2, fmaf(r.f(QREC_M + 1), dx1, r.f(QREC_M + 0) * dx0));
     const float tm1 = fmaf(r.f(QREC_M + 5), dx2, fmaf(r.f(QREC_M + 4), dx1, r.f(QREC_M + 3) * dx0));
@@ -255,7 +271,7 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float
             const float u1 = h ? in.u1.y : in.u1.x, u2 = h ? in.u2.y : in.u2.x;
             const int sel = h ? sel1 : sel0;
             float wx, wy, wz, ij;
-            sample_direction(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
+            sample_direction<true>(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
             if (h) { in.wx.y = wx; in.wy.y = wy; in.wz.y = wz; out.ij.y = ij; }
             else { in.wx.x = wx; in.wy.x = wy; in.wz.x = wz; out.ij.x = ij; }
         }
@@ -431,9 +447,10 @@ __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* _
 template <bool SAMPLE, int K, bool REC>
 __global__ void __launch_bounds__(QTHREADS)
 query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restrict__ qout, int tile) {
-    __shared__ __align__(16) float4 srec[K * 8];                                        // [K][8]
+    __shared__ __align__(16) float4 srec[K * 9 + K / 8];                            // skewed [K][8], see qoff
     __shared__ float2 spref[SAMPLE ? (K / QBLOCK) * QTHREADS : 1];                      // [K/8][QTHREADS]
     __shared__ uint32_t s_cell;
+    __shared__ uint32_t s_part[QTHREADS / 32];
     const size_t tbegin = (size_t)blockIdx.x * tile;
     const size_t tend = (tbegin + tile < q.n) ? tbegin + tile : q.n;
     size_t pos = tbegin;
@@ -445,22 +462,33 @@ query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restr
         const bool cell_ok = cell < (uint32_t)q.max_cells;
         if (cell_ok) {
             const float4* g = reinterpret_cast<const float4*>(q.qrec + (size_t)cell * K * QREC_FLOATS);
-            for (int i = threadIdx.x; i < K * 8; i += QTHREADS) srec[i] = __ldg(g + i);
+            for (int i = threadIdx.x; i < K * 8; i += QTHREADS) srec[qoff<true>(i >> 3) + (i & 7)] = __ldg(g + i);
         }
         __syncthreads();
-        bool run_over = false;
-        while (!run_over && pos < tend) {
-            const size_t p0 = pos + threadIdx.x, p1 = p0 + QTHREADS;
+        // length of this cell's run inside the tile, found once (first position whose cell differs); the rounds
+        // below then need no barrier between them.  Any order of vertices gives correct results -- unsorted input
+        // just degenerates into short runs.
+        {
+            uint32_t first = (uint32_t)(tend - pos);
+            for (size_t p = pos + threadIdx.x; p < tend; p += QTHREADS) {
+                const uint32_t c = REC ? __float_as_uint(__ldg(&qin[2 * p + 1].w)) : q.cell_idx[p];
+                if (c != cell) { first = (uint32_t)(p - pos); break; }
+            }
+            first = __reduce_min_sync(0xffffffffu, first);
+            if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = first;
+        }
+        __syncthreads();
+        uint32_t run = s_part[0];
+#pragma unroll
+        for (int w = 1; w < QTHREADS / 32; ++w) run = min(run, s_part[w]);
+        const size_t rend = pos + run;
+        for (size_t base = pos; base < rend; base += 2 * QTHREADS) {
+            const size_t p0 = base + threadIdx.x, p1 = p0 + QTHREADS;
             float4 a0, b0, a1, b1;   // REC: the two vertices' input records
-            bool m0, m1;
+            const bool m0 = p0 < rend, m1 = p1 < rend;
             if (REC) {
-                m0 = p0 < tend;
-                m1 = p1 < tend;
-                if (m0) { a0 = qin[2 * p0]; b0 = qin[2 * p0 + 1]; m0 = __float_as_uint(b0.w) == cell; }
-                if (m1) { a1 = qin[2 * p1]; b1 = qin[2 * p1 + 1]; m1 = __float_as_uint(b1.w) == cell; }
-            } else {
-                m0 = (p0 < tend) && (q.cell_idx[p0] == cell);
-                m1 = (p1 < tend) && (q.cell_idx[p1] == cell);
+                if (m0) { a0 = qin[2 * p0]; b0 = qin[2 * p0 + 1]; }
+                if (m1) { a1 = qin[2 * p1]; b1 = qin[2 * p1 + 1]; }
             }
             if (m0) {   // a sorted run is contiguous: m1 implies m0
                 if (!m1) { a1 = a0; b1 = b0; }
@@ -519,10 +547,8 @@ query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restr
                     }
                 }
             }
-            const int n_mine = __syncthreads_count(m0 ? 1 : 0) + __syncthreads_count(m1 ? 1 : 0);
-            pos += n_mine;
-            run_over = (n_mine < 2 * QTHREADS);
         }
+        pos = rend;
     }
 }
 
@@ -569,7 +595,7 @@ query_pruned_kernel(QueryLaunch q, int K_user, int max_components, int preserve_
         const float4* rec = reinterpret_cast<const float4*>(q.qrec + (size_t)cell * K * QREC_FLOATS);
         const float x = q.pos3[i], y = q.pos3[q.n + i], z = q.pos3[2 * q.n + i];
         float w[SDMMB_QUERY_MAX_K];
-        for (int k = 0; k < K; ++k) w[k] = single_weight(rec, k, x, y, z);
+        for (int k = 0; k < K; ++k) w[k] = single_weight<false>(rec, k, x, y, z);
         // kill the weakest components: ascending order of (weight, index), visited once each
         uint32_t seen[SDMMB_QUERY_MAX_K / 32] = {0u, 0u, 0u, 0u};
         int budget = max_components;
@@ -603,11 +629,11 @@ query_pruned_kernel(QueryLaunch q, int K_user, int max_components, int preserve_
                 }
                 while (sel > 0 && w[sel] * inv == 0.f) --sel;
                 comp = (uint32_t)sel;
-                sample_direction(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
+                sample_direction<false>(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
             } else {
                 wx = q.dir3[i]; wy = q.dir3[q.n + i]; wz = q.dir3[2 * q.n + i];
             }
-            for (int k = 0; k < K; ++k) pdf = fmaf(cond_pdf_single(rec, k, x, y, z, wx, wy, wz), w[k] * inv, pdf);
+            for (int k = 0; k < K; ++k) pdf = fmaf(cond_pdf_single<false>(rec, k, x, y, z, wx, wy, wz), w[k] * inv, pdf);
         }
     }
     if (q.u3) {
