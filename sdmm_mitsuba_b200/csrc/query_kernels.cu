@@ -187,6 +187,35 @@ __device__ __forceinline__ int select_component(const float4* __restrict__ rec, 
     return sel;
 }
 
+// The same selection when pass 1 parked the K weights of the pair in shared memory (`wst`, stride `ps`) and kept the
+// block-end running sums in registers: the block re-scan reads the stored bits instead of recomputing them.
+template <int K, int H>
+__device__ __forceinline__ int select_stored(const float2* __restrict__ wst, int ps,
+                                             const float2 (&bsum)[K / QBLOCK], float u0, float inv) {
+    const float* w1 = reinterpret_cast<const float*>(wst) + H;
+    int b = K / QBLOCK;
+#pragma unroll
+    for (int j = K / QBLOCK - 1; j >= 0; --j)
+        if (!((H ? bsum[j].y : bsum[j].x) * inv < u0)) b = j;
+    int sel = K - 1;
+    if (b < K / QBLOCK) {
+        float run = 0.f;
+#pragma unroll
+        for (int j = 0; j < K / QBLOCK - 1; ++j)
+            if (j == b - 1) run = H ? bsum[j].y : bsum[j].x;
+        bool found = false;
+#pragma unroll
+        for (int j = 0; j < QBLOCK; ++j) {
+            const int k = b * QBLOCK + j;
+            const float w = w1[(size_t)k * ps * 2];
+            run = (k == 0) ? w : run + w;
+            if (!found && !(run * inv < u0)) { sel = k; found = true; }
+        }
+    }
+    while (sel > 0 && w1[(size_t)sel * ps * 2] * inv == 0.f) --sel;
+    return sel;
+}
+
 // Box-Muller + `L_c z` + offset exp map of component `sel` for one vertex        R: sdmm.h:238-265,
 // spaces/offset_directional.h:62-82
 template <bool SW>
@@ -238,66 +267,102 @@ __device__ __forceinline__ float cond_pdf_single(const float4* __restrict__ rec,
     return ij * q_ex2(-e);
 }
 
-template <bool SAMPLE, int K>
-__device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float2* __restrict__ pref, int ps,
+// conditional density of component k at the pair's directions, times the log-map Jacobian (R: sdmm.h:284-313,
+// offset_directional.h:39-60)
+__device__ __forceinline__ float2 pair_cond_pdf(const float4* __restrict__ rec, int k, const PairIn& in) {
+    const QRec r = load_rec<true>(rec, k);
+    const float2 dx0 = q_sub2(in.x, q_splat(r.f(QREC_MU + 0))), dx1 = q_sub2(in.y, q_splat(r.f(QREC_MU + 1))),
+                 dx2 = q_sub2(in.z, q_splat(r.f(QREC_MU + 2)));
+    const float2 tm0 = q_fma2(q_splat(r.f(QREC_M + 2)), dx2, q_fma2(q_splat(r.f(QREC_M + 1)), dx1, q_mul2(q_splat(r.f(QREC_M + 0)), dx0)));
+    const float2 tm1 = q_fma2(q_splat(r.f(QREC_M + 5)), dx2, q_fma2(q_splat(r.f(QREC_M + 4)), dx1, q_mul2(q_splat(r.f(QREC_M + 3)), dx0)));
+    const float2 lx = q_fma2(q_splat(r.f(QREC_R + 2)), in.wz, q_fma2(q_splat(r.f(QREC_R + 1)), in.wy, q_mul2(q_splat(r.f(QREC_R + 0)), in.wx)));
+    const float2 ly = q_fma2(q_splat(r.f(QREC_R + 5)), in.wz, q_fma2(q_splat(r.f(QREC_R + 4)), in.wy, q_mul2(q_splat(r.f(QREC_R + 3)), in.wx)));
+    const float2 lz = q_fma2(q_splat(r.f(QREC_R + 8)), in.wz, q_fma2(q_splat(r.f(QREC_R + 7)), in.wy, q_mul2(q_splat(r.f(QREC_R + 6)), in.wx)));
+    const float2 rs = rcp_sinc_from_cos2(lz);
+    const float2 ij = make_float2((lz.x < -0.98f) ? 0.f : rs.x, (lz.y < -0.98f) ? 0.f : rs.y);
+    const float2 t0 = q_fma2(lx, rs, make_float2(-tm0.x, -tm0.y)), t1 = q_fma2(ly, rs, make_float2(-tm1.x, -tm1.y));
+    const float2 z0 = q_mul2(q_splat(r.f(QREC_WC + 0)), t0);
+    const float2 z1 = q_fma2(q_splat(r.f(QREC_WC + 2)), t1, q_mul2(q_splat(r.f(QREC_WC + 1)), t0));
+    float2 e = q_fma2(z0, z0, q_splat(r.f(QREC_NLCC)));
+    e = q_fma2(z1, z1, e);
+    return q_mul2(ij, make_float2(q_ex2(-e.x), q_ex2(-e.y)));
+}
+
+// MODE of the sample query: where the K conditional weights of a vertex pair live between the passes.
+//   QSTORE   (K <= 64): pass 1 parks them in shared memory (K x 8 B per thread; 3 CTAs = 12 warps per SM at K = 64),
+//            block-end running sums stay in registers; pass 2 and pass 3 read the stored bits.  Saves the 12 packed
+//            instructions per component that recomputing the weight costs in pass 3, and the block re-scan of pass 2.
+//   QRECOMP  (K = 128): nothing is parked but the block-end sums (`wst` = [K/8][threads]); every pass recomputes the
+//            weights with the same instruction sequence (bit-identical), full occupancy.
+// Both give the same bits: the selection depends only on the weight bits and the sequential float32 sums.
+enum { QRECOMP = 0, QSTORE = 1 };
+
+template <bool SAMPLE, int K, int MODE>
+__device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float2* __restrict__ wst, int ps,
                                            PairIn& in, PairRes& out) {
-    // ---- pass 1: sequential sum of the unnormalised conditional weights ---------------------------
     float2 total = q_splat(0.f);
-#pragma unroll 1
-    for (int b = 0; b < K / QBLOCK; ++b) {
-#pragma unroll
-        for (int j = 0; j < QBLOCK; ++j) {
-            const float2 w = pair_weight(rec, b * QBLOCK + j, in);
-            total = (b == 0 && j == 0) ? w : q_add2(total, w);
+    float2 pdf = q_splat(0.f);
+    if (!SAMPLE) {
+        // pdf-only: the direction is known up front, so one pass gives sum_k w_k and sum_k p_k w_k; the division by
+        // the total moves behind the sum (the reference normalises each weight first: a float32 rounding apart)
+#pragma unroll 2
+        for (int k = 0; k < K; ++k) {
+            const float2 wk = pair_weight(rec, k, in);
+            total = (k == 0) ? wk : q_add2(total, wk);
+            pdf = q_fma2(pair_cond_pdf(rec, k, in), wk, pdf);
         }
-        if (SAMPLE) pref[b * ps] = total;   // running sums at the block ends, for pass 2
+    } else if (MODE == QSTORE) {
+        float2 bsum[K / QBLOCK];
+#pragma unroll
+        for (int b = 0; b < K / QBLOCK; ++b) {
+#pragma unroll
+            for (int j = 0; j < QBLOCK; ++j) {
+                const float2 w = pair_weight(rec, b * QBLOCK + j, in);
+                wst[(b * QBLOCK + j) * ps] = w;
+                total = (b == 0 && j == 0) ? w : q_add2(total, w);
+            }
+            bsum[b] = total;
+        }
+        const float2 inv = make_float2(1.f / total.x, 1.f / total.y);
+        const int sel0 = select_stored<K, 0>(wst, ps, bsum, in.u0.x, inv.x);
+        const int sel1 = select_stored<K, 1>(wst, ps, bsum, in.u0.y, inv.y);
+        out.comp[0] = (uint32_t)sel0;
+        out.comp[1] = (uint32_t)sel1;
+        sample_direction<true>(rec, sel0, in.x.x, in.y.x, in.z.x, in.u1.x, in.u2.x, in.wx.x, in.wy.x, in.wz.x, out.ij.x);
+        sample_direction<true>(rec, sel1, in.x.y, in.y.y, in.z.y, in.u1.y, in.u2.y, in.wx.y, in.wy.y, in.wz.y, out.ij.y);
+#pragma unroll 4
+        for (int k = 0; k < K; ++k) pdf = q_fma2(pair_cond_pdf(rec, k, in), q_mul2(wst[k * ps], inv), pdf);
+    } else {
+        // ---- pass 1: sequential sum of the unnormalised conditional weights -----------------------
+#pragma unroll 1
+        for (int b = 0; b < K / QBLOCK; ++b) {
+#pragma unroll
+            for (int j = 0; j < QBLOCK; ++j) {
+                const float2 w = pair_weight(rec, b * QBLOCK + j, in);
+                total = (b == 0 && j == 0) ? w : q_add2(total, w);
+            }
+            wst[b * ps] = total;   // running sums at the block ends, for pass 2
+        }
+        const float2 inv = make_float2(1.f / total.x, 1.f / total.y);
+        // ---- pass 2: component select from the block prefix sums, Box-Muller + exp map per vertex ----
+        const int sel0 = select_component<K, 0>(rec, wst, ps, in.x.x, in.y.x, in.z.x, in.u0.x, inv.x);
+        const int sel1 = select_component<K, 1>(rec, wst, ps, in.x.y, in.y.y, in.z.y, in.u0.y, inv.y);
+        out.comp[0] = (uint32_t)sel0;
+        out.comp[1] = (uint32_t)sel1;
+        sample_direction<true>(rec, sel0, in.x.x, in.y.x, in.z.x, in.u1.x, in.u2.x, in.wx.x, in.wy.x, in.wz.x, out.ij.x);
+        sample_direction<true>(rec, sel1, in.x.y, in.y.y, in.z.y, in.u1.y, in.u2.y, in.wx.y, in.wy.y, in.wz.y, out.ij.y);
+        // ---- pass 3: conditional pdf at omega, summed over components -----------------------------
+#pragma unroll 2
+        for (int k = 0; k < K; ++k)
+            pdf = q_fma2(pair_cond_pdf(rec, k, in), q_mul2(pair_weight(rec, k, in), inv), pdf);
     }
     const bool v0 = total.x > 1e-20f, v1 = total.y > 1e-20f;      // R: categorical.h:97-101
     out.valid[0] = v0 ? 1 : 0;
     out.valid[1] = v1 ? 1 : 0;
-    const float2 inv = make_float2(1.f / total.x, 1.f / total.y);
-    out.comp[0] = out.comp[1] = 0u;
-    out.ij = q_splat(0.f);
-    if (SAMPLE) {
-        // ---- pass 2: component select from the block prefix sums ---------------------------------
-        const int sel0 = select_component<K, 0>(rec, pref, ps, in.x.x, in.y.x, in.z.x, in.u0.x, inv.x);
-        const int sel1 = select_component<K, 1>(rec, pref, ps, in.x.y, in.y.y, in.z.y, in.u0.y, inv.y);
-        out.comp[0] = (uint32_t)sel0;
-        out.comp[1] = (uint32_t)sel1;
-        // Box-Muller + exp map of the selected component, per vertex (scalar: once per vertex)
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const float x = h ? in.x.y : in.x.x, y = h ? in.y.y : in.y.x, z = h ? in.z.y : in.z.x;
-            const float u1 = h ? in.u1.y : in.u1.x, u2 = h ? in.u2.y : in.u2.x;
-            const int sel = h ? sel1 : sel0;
-            float wx, wy, wz, ij;
-            sample_direction<true>(rec, sel, x, y, z, u1, u2, wx, wy, wz, ij);
-            if (h) { in.wx.y = wx; in.wy.y = wy; in.wz.y = wz; out.ij.y = ij; }
-            else { in.wx.x = wx; in.wy.x = wy; in.wz.x = wz; out.ij.x = ij; }
-        }
-    }
-    // ---- pass 3: conditional pdf at omega, summed over components ---------------------------------
-    float2 pdf = q_splat(0.f);
-#pragma unroll 2
-    for (int k = 0; k < K; ++k) {
-        const float2 wk = pair_weight(rec, k, in);
-        const QRec r = load_rec<true>(rec, k);
-        const float2 dx0 = q_sub2(in.x, q_splat(r.f(QREC_MU + 0))), dx1 = q_sub2(in.y, q_splat(r.f(QREC_MU + 1))),
-                     dx2 = q_sub2(in.z, q_splat(r.f(QREC_MU + 2)));
-        const float2 tm0 = q_fma2(q_splat(r.f(QREC_M + 2)), dx2, q_fma2(q_splat(r.f(QREC_M + 1)), dx1, q_mul2(q_splat(r.f(QREC_M + 0)), dx0)));
-        const float2 tm1 = q_fma2(q_splat(r.f(QREC_M + 5)), dx2, q_fma2(q_splat(r.f(QREC_M + 4)), dx1, q_mul2(q_splat(r.f(QREC_M + 3)), dx0)));
-        const float2 lx = q_fma2(q_splat(r.f(QREC_R + 2)), in.wz, q_fma2(q_splat(r.f(QREC_R + 1)), in.wy, q_mul2(q_splat(r.f(QREC_R + 0)), in.wx)));
-        const float2 ly = q_fma2(q_splat(r.f(QREC_R + 5)), in.wz, q_fma2(q_splat(r.f(QREC_R + 4)), in.wy, q_mul2(q_splat(r.f(QREC_R + 3)), in.wx)));
-        const float2 lz = q_fma2(q_splat(r.f(QREC_R + 8)), in.wz, q_fma2(q_splat(r.f(QREC_R + 7)), in.wy, q_mul2(q_splat(r.f(QREC_R + 6)), in.wx)));
-        const float2 rs = rcp_sinc_from_cos2(lz);
-        const float2 ij = make_float2((lz.x < -0.98f) ? 0.f : rs.x, (lz.y < -0.98f) ? 0.f : rs.y);
-        const float2 t0 = q_fma2(lx, rs, make_float2(-tm0.x, -tm0.y)), t1 = q_fma2(ly, rs, make_float2(-tm1.x, -tm1.y));
-        const float2 z0 = q_mul2(q_splat(r.f(QREC_WC + 0)), t0);
-        const float2 z1 = q_fma2(q_splat(r.f(QREC_WC + 2)), t1, q_mul2(q_splat(r.f(QREC_WC + 1)), t0));
-        float2 e = q_fma2(z0, z0, q_splat(r.f(QREC_NLCC)));
-        e = q_fma2(z1, z1, e);
-        const float2 pk = q_mul2(ij, make_float2(q_ex2(-e.x), q_ex2(-e.y)));
-        pdf = q_fma2(pk, q_mul2(wk, inv), pdf);
+    if (!SAMPLE) {
+        pdf = q_mul2(pdf, make_float2(1.f / total.x, 1.f / total.y));
+        out.comp[0] = out.comp[1] = 0u;
+        out.ij = q_splat(0.f);
     }
     out.pdf = pdf;
     if (!v0) { out.pdf.x = 0.f; out.ij.x = 0.f; out.comp[0] = 0u; if (SAMPLE) { in.wx.x = in.wy.x = in.wz.x = 0.f; } }
@@ -444,11 +509,48 @@ __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* _
 //   REC = true : device-binned vertices: packed 32-byte records in (`qin`, written by the scatter pass)
 //                and out (`qout`: (dx, dy, dz, pdf) (inv_jac, comp, valid, -)), both in sorted order,
 //                i.e. coalesced; query_unpermute_kernel puts the results back in the caller's order.
+// One round's inputs of a thread: (x, y, z, in0) (in1, in2, -, -) for its two vertices -- the device-binned records
+// as they are (REC), or gathered from the caller's SoA planes.
+struct RoundIn { float4 a0, b0, a1, b1; };
+template <bool SAMPLE, bool REC>
+__device__ __forceinline__ void load_round(const QueryLaunch& q, const float4* __restrict__ qin, size_t base, size_t rend,
+                                           RoundIn& r) {
+    const size_t p0 = base + threadIdx.x, p1 = p0 + QTHREADS;
+    r.a0 = r.b0 = r.a1 = r.b1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (REC) {
+        if (p0 < rend) { r.a0 = qin[2 * p0]; r.b0 = qin[2 * p0 + 1]; }
+        if (p1 < rend) { r.a1 = qin[2 * p1]; r.b1 = qin[2 * p1 + 1]; }
+    } else {
+        const float* in3 = SAMPLE ? q.u3 : q.dir3;
+        if (p0 < rend) {
+            r.a0 = make_float4(q.pos3[p0], q.pos3[q.n + p0], q.pos3[2 * q.n + p0], in3[p0]);
+            r.b0.x = in3[q.n + p0]; r.b0.y = in3[2 * q.n + p0];
+        }
+        if (p1 < rend) {
+            r.a1 = make_float4(q.pos3[p1], q.pos3[q.n + p1], q.pos3[2 * q.n + p1], in3[p1]);
+            r.b1.x = in3[q.n + p1]; r.b1.y = in3[2 * q.n + p1];
+        }
+    }
+}
+
+template <bool SAMPLE, int K>
+struct QShape {
+    static constexpr int MODE = (SAMPLE && K <= 64) ? QSTORE : QRECOMP;
+    static constexpr int REC_F4 = K * 9 + K / 8;                                              // skewed [K][8], see qoff
+    static constexpr int W_F2 = !SAMPLE ? 0 : (MODE == QSTORE ? K : K / QBLOCK) * QTHREADS;   // [K or K/8][QTHREADS]
+    static constexpr size_t SMEM = (size_t)REC_F4 * sizeof(float4) + (size_t)W_F2 * sizeof(float2);
+    // registers: the stored mode holds K/8 block sums and unrolls pass 3 by 4; its CTAs per SM are bounded by shared
+    // memory anyway (3 at K = 64, 6 at K = 32)
+    static constexpr int MIN_CTAS = MODE == QSTORE ? (K == 64 ? 3 : (K == 32 ? 6 : 8)) : 8;
+};
+
 template <bool SAMPLE, int K, bool REC>
-__global__ void __launch_bounds__(QTHREADS)
+__global__ void __launch_bounds__(QTHREADS, (QShape<SAMPLE, K>::MIN_CTAS))
 query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restrict__ qout, int tile) {
-    __shared__ __align__(16) float4 srec[K * 9 + K / 8];                            // skewed [K][8], see qoff
-    __shared__ float2 spref[SAMPLE ? (K / QBLOCK) * QTHREADS : 1];                      // [K/8][QTHREADS]
+    using S = QShape<SAMPLE, K>;
+    extern __shared__ __align__(16) unsigned char q_smem[];
+    float4* srec = reinterpret_cast<float4*>(q_smem);
+    float2* swst = reinterpret_cast<float2*>(q_smem + (size_t)S::REC_F4 * sizeof(float4));
     __shared__ uint32_t s_cell;
     __shared__ uint32_t s_part[QTHREADS / 32];
     const size_t tbegin = (size_t)blockIdx.x * tile;
@@ -482,17 +584,17 @@ query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restr
 #pragma unroll
         for (int w = 1; w < QTHREADS / 32; ++w) run = min(run, s_part[w]);
         const size_t rend = pos + run;
+        // the inputs of round r + 1 are requested before round r is computed (12 warps per SM in the stored mode do
+        // not hide a global-memory round trip by themselves)
+        RoundIn cur, nxt;
+        load_round<SAMPLE, REC>(q, qin, pos, rend, cur);
         for (size_t base = pos; base < rend; base += 2 * QTHREADS) {
             const size_t p0 = base + threadIdx.x, p1 = p0 + QTHREADS;
-            float4 a0, b0, a1, b1;   // REC: the two vertices' input records
             const bool m0 = p0 < rend, m1 = p1 < rend;
-            if (REC) {
-                if (m0) { a0 = qin[2 * p0]; b0 = qin[2 * p0 + 1]; }
-                if (m1) { a1 = qin[2 * p1]; b1 = qin[2 * p1 + 1]; }
-            }
+            if (base + 2 * QTHREADS < rend) load_round<SAMPLE, REC>(q, qin, base + 2 * QTHREADS, rend, nxt);
+            const float4 a0 = cur.a0, b0 = cur.b0, a1 = m1 ? cur.a1 : cur.a0, b1 = m1 ? cur.b1 : cur.b0;
+            cur = nxt;
             if (m0) {   // a sorted run is contiguous: m1 implies m0
-                if (!m1) { a1 = a0; b1 = b0; }
-                const size_t i1 = m1 ? p1 : p0;
                 PairIn in;
                 PairRes res;
                 res.pdf = res.ij = make_float2(0.f, 0.f);
@@ -500,26 +602,13 @@ query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restr
                 res.valid[0] = res.valid[1] = 0;
                 in.wx = in.wy = in.wz = make_float2(0.f, 0.f);
                 if (cell_ok) {
-                    float2 c0, c1, c2;   // uniforms or direction
-                    if (REC) {
-                        in.x = make_float2(a0.x, a1.x);
-                        in.y = make_float2(a0.y, a1.y);
-                        in.z = make_float2(a0.z, a1.z);
-                        c0 = make_float2(a0.w, a1.w);
-                        c1 = make_float2(b0.x, b1.x);
-                        c2 = make_float2(b0.y, b1.y);
-                    } else {
-                        const float* in3 = SAMPLE ? q.u3 : q.dir3;
-                        in.x = make_float2(q.pos3[p0], q.pos3[i1]);
-                        in.y = make_float2(q.pos3[q.n + p0], q.pos3[q.n + i1]);
-                        in.z = make_float2(q.pos3[2 * q.n + p0], q.pos3[2 * q.n + i1]);
-                        c0 = make_float2(in3[p0], in3[i1]);
-                        c1 = make_float2(in3[q.n + p0], in3[q.n + i1]);
-                        c2 = make_float2(in3[2 * q.n + p0], in3[2 * q.n + i1]);
-                    }
+                    in.x = make_float2(a0.x, a1.x);
+                    in.y = make_float2(a0.y, a1.y);
+                    in.z = make_float2(a0.z, a1.z);
+                    const float2 c0 = make_float2(a0.w, a1.w), c1 = make_float2(b0.x, b1.x), c2 = make_float2(b0.y, b1.y);
                     if (SAMPLE) { in.u0 = c0; in.u1 = c1; in.u2 = c2; }
                     else { in.wx = c0; in.wy = c1; in.wz = c2; }
-                    query_pair<SAMPLE, K>(srec, spref + (SAMPLE ? threadIdx.x : 0), QTHREADS, in, res);
+                    query_pair<SAMPLE, K, S::MODE>(srec, swst + (SAMPLE ? threadIdx.x : 0), QTHREADS, in, res);
                 }
                 if (REC) {
                     qout[2 * p0] = make_float4(in.wx.x, in.wy.x, in.wz.x, res.pdf.x);
@@ -713,12 +802,21 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     // the per-run record staging (K * 128 B) stays negligible
     const int tile = 2048;
     const unsigned grid = (unsigned)((q.n + tile - 1) / tile);
+#define SDMMB_QLAUNCH1(S, KK, R, A, B)                                                                  \
+    do {                                                                                                \
+        auto kern = query_pair_kernel<S, KK, R>;                                                        \
+        const size_t smem = QShape<S, KK>::SMEM;                                                        \
+        /* per device, so set on every launch (a process may hold contexts on several GPUs); it is a host-side table write */ \
+        if (smem > 48 * 1024 &&                                                                         \
+            (e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e; \
+        kern<<<grid, QTHREADS, smem, st>>>(q, A, B, tile);                                              \
+    } while (0)
 #define SDMMB_QLAUNCH(KK)                                                                               \
     do {                                                                                                \
-        if (sample && qin) query_pair_kernel<true, KK, true><<<grid, QTHREADS, 0, st>>>(q, qin, qout, tile);        \
-        else if (sample) query_pair_kernel<true, KK, false><<<grid, QTHREADS, 0, st>>>(q, nullptr, nullptr, tile);  \
-        else if (qin) query_pair_kernel<false, KK, true><<<grid, QTHREADS, 0, st>>>(q, qin, qout, tile);            \
-        else query_pair_kernel<false, KK, false><<<grid, QTHREADS, 0, st>>>(q, nullptr, nullptr, tile);             \
+        if (sample && qin) SDMMB_QLAUNCH1(true, KK, true, qin, qout);                                   \
+        else if (sample) SDMMB_QLAUNCH1(true, KK, false, nullptr, nullptr);                             \
+        else if (qin) SDMMB_QLAUNCH1(false, KK, true, qin, qout);                                       \
+        else SDMMB_QLAUNCH1(false, KK, false, nullptr, nullptr);                                        \
     } while (0)
     switch (q.K) {
         case 16: SDMMB_QLAUNCH(16); break;
@@ -727,6 +825,7 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
         case 128: SDMMB_QLAUNCH(128); break;
         default: return cudaErrorInvalidValue;
     }
+#undef SDMMB_QLAUNCH1
 #undef SDMMB_QLAUNCH
     if (qin) {
         const unsigned ug = (unsigned)std::min<size_t>((q.n + 255) / 256, 148 * 16);
