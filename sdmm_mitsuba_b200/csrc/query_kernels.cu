@@ -15,6 +15,7 @@
 // unnormalised conditional weights of a vertex pair are recomputed in each of the three passes
 // (sum -> select -> pdf) instead of being parked anywhere: no per-thread storage, full occupancy.
 #include <algorithm>
+#include <cstdlib>
 
 #include "kernels.h"
 #include "sdmm_math.cuh"
@@ -194,15 +195,15 @@ __device__ __forceinline__ int select_stored(const float2* __restrict__ wst, int
                                              const float2 (&bsum)[K / QBLOCK], float u0, float inv) {
     const float* w1 = reinterpret_cast<const float*>(wst) + H;
     int b = K / QBLOCK;
+    float run = 0.f;   // running sum at the end of block b - 1 (static indices only: bsum stays in registers)
 #pragma unroll
     for (int j = K / QBLOCK - 1; j >= 0; --j)
-        if (!((H ? bsum[j].y : bsum[j].x) * inv < u0)) b = j;
+        if (!((H ? bsum[j].y : bsum[j].x) * inv < u0)) {
+            b = j;
+            run = (j > 0) ? (H ? bsum[j > 0 ? j - 1 : 0].y : bsum[j > 0 ? j - 1 : 0].x) : 0.f;
+        }
     int sel = K - 1;
     if (b < K / QBLOCK) {
-        float run = 0.f;
-#pragma unroll
-        for (int j = 0; j < K / QBLOCK - 1; ++j)
-            if (j == b - 1) run = H ? bsum[j].y : bsum[j].x;
         bool found = false;
 #pragma unroll
         for (int j = 0; j < QBLOCK; ++j) {
@@ -312,14 +313,19 @@ __device__ __forceinline__ void query_pair(const float4* __restrict__ rec, float
             pdf = q_fma2(pair_cond_pdf(rec, k, in), wk, pdf);
         }
     } else if (MODE == QSTORE) {
+        // a block of QBLOCK weights is computed before any of it is stored: a store to `wst` between the record
+        // loads would pin their order (the compiler cannot tell the two shared-memory arrays apart), and every
+        // component would pay the full LDS and MUFU latency on its own
         float2 bsum[K / QBLOCK];
 #pragma unroll
         for (int b = 0; b < K / QBLOCK; ++b) {
+            float2 w[QBLOCK];
+#pragma unroll
+            for (int j = 0; j < QBLOCK; ++j) w[j] = pair_weight(rec, b * QBLOCK + j, in);
 #pragma unroll
             for (int j = 0; j < QBLOCK; ++j) {
-                const float2 w = pair_weight(rec, b * QBLOCK + j, in);
-                wst[(b * QBLOCK + j) * ps] = w;
-                total = (b == 0 && j == 0) ? w : q_add2(total, w);
+                total = (b == 0 && j == 0) ? w[j] : q_add2(total, w[j]);
+                wst[(b * QBLOCK + j) * ps] = w[j];
             }
             bsum[b] = total;
         }
@@ -551,43 +557,51 @@ query_pair_kernel(QueryLaunch q, const float4* __restrict__ qin, float4* __restr
     extern __shared__ __align__(16) unsigned char q_smem[];
     float4* srec = reinterpret_cast<float4*>(q_smem);
     float2* swst = reinterpret_cast<float2*>(q_smem + (size_t)S::REC_F4 * sizeof(float4));
-    __shared__ uint32_t s_cell;
     __shared__ uint32_t s_part[QTHREADS / 32];
     const size_t tbegin = (size_t)blockIdx.x * tile;
     const size_t tend = (tbegin + tile < q.n) ? tbegin + tile : q.n;
     size_t pos = tbegin;
     while (pos < tend) {
-        __syncthreads();
-        if (threadIdx.x == 0) s_cell = REC ? __float_as_uint(qin[2 * pos + 1].w) : q.cell_idx[pos];
-        __syncthreads();
-        const uint32_t cell = s_cell;
+        // Start of a run of vertices of one cell.  Two global-memory round trips instead of four: every thread reads
+        // the run's cell id itself (one address: a broadcast), then the cell's records, the cell ids of the rest of
+        // the tile (to find where the run ends) and the inputs of the first round are all requested before anything
+        // is waited for.
+        const uint32_t cell = REC ? __float_as_uint(__ldg(&qin[2 * pos + 1].w)) : __ldg(q.cell_idx + pos);
         const bool cell_ok = cell < (uint32_t)q.max_cells;
+        constexpr int G4 = K * 8 / QTHREADS;
+        float4 g4[G4];
         if (cell_ok) {
             const float4* g = reinterpret_cast<const float4*>(q.qrec + (size_t)cell * K * QREC_FLOATS);
-            for (int i = threadIdx.x; i < K * 8; i += QTHREADS) srec[qoff<true>(i >> 3) + (i & 7)] = __ldg(g + i);
+#pragma unroll
+            for (int i = 0; i < G4; ++i) g4[i] = __ldg(g + threadIdx.x + i * QTHREADS);
         }
-        __syncthreads();
-        // length of this cell's run inside the tile, found once (first position whose cell differs); the rounds
-        // below then need no barrier between them.  Any order of vertices gives correct results -- unsorted input
-        // just degenerates into short runs.
-        {
-            uint32_t first = (uint32_t)(tend - pos);
-            for (size_t p = pos + threadIdx.x; p < tend; p += QTHREADS) {
-                const uint32_t c = REC ? __float_as_uint(__ldg(&qin[2 * p + 1].w)) : q.cell_idx[p];
-                if (c != cell) { first = (uint32_t)(p - pos); break; }
+        // first position whose cell differs (no early exit: the loads are independent and stay in flight together).
+        // Any order of vertices gives correct results -- unsorted input just degenerates into short runs.
+        uint32_t first = (uint32_t)(tend - pos);
+#pragma unroll 4
+        for (size_t p = pos + threadIdx.x; p < tend; p += QTHREADS) {
+            const uint32_t c = REC ? __float_as_uint(__ldg(&qin[2 * p + 1].w)) : __ldg(q.cell_idx + p);
+            if (c != cell) first = min(first, (uint32_t)(p - pos));
+        }
+        // the inputs of round r + 1 are requested before round r is computed (12 warps per SM in the stored mode do
+        // not hide a global-memory round trip by themselves); round 0's here, masked by the tile end
+        RoundIn cur, nxt;
+        load_round<SAMPLE, REC>(q, qin, pos, tend, cur);
+        first = __reduce_min_sync(0xffffffffu, first);
+        __syncthreads();   // the previous run's readers of srec and s_part are done
+        if (cell_ok) {
+#pragma unroll
+            for (int i = 0; i < G4; ++i) {
+                const int e = threadIdx.x + i * QTHREADS;
+                srec[qoff<true>(e >> 3) + (e & 7)] = g4[i];
             }
-            first = __reduce_min_sync(0xffffffffu, first);
-            if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = first;
         }
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = first;
         __syncthreads();
         uint32_t run = s_part[0];
 #pragma unroll
         for (int w = 1; w < QTHREADS / 32; ++w) run = min(run, s_part[w]);
         const size_t rend = pos + run;
-        // the inputs of round r + 1 are requested before round r is computed (12 warps per SM in the stored mode do
-        // not hide a global-memory round trip by themselves)
-        RoundIn cur, nxt;
-        load_round<SAMPLE, REC>(q, qin, pos, rend, cur);
         for (size_t base = pos; base < rend; base += 2 * QTHREADS) {
             const size_t p0 = base + threadIdx.x, p1 = p0 + QTHREADS;
             const bool m0 = p0 < rend, m1 = p1 < rend;
@@ -800,7 +814,12 @@ cudaError_t launch_query(const QueryLaunch& q, cudaStream_t st) {
     }
     // tile: multiple of 2 * QTHREADS; short enough that the last wave's tail is small, long enough that
     // the per-run record staging (K * 128 B) stays negligible
-    const int tile = 2048;
+    static const int tile_env = [] {
+        const char* s = getenv("SDMMB_QUERY_TILE");   // tuning knob (multiple of 2 * QTHREADS)
+        const int v = s ? atoi(s) : 0;
+        return (v >= 2 * QTHREADS && v % (2 * QTHREADS) == 0) ? v : 0;
+    }();
+    const int tile = tile_env ? tile_env : 2048;
     const unsigned grid = (unsigned)((q.n + tile - 1) / tile);
 #define SDMMB_QLAUNCH1(S, KK, R, A, B)                                                                  \
     do {                                                                                                \
