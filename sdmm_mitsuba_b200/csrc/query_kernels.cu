@@ -11,9 +11,11 @@
 // left-to-right float32 prefix sum the reference builds (categorical.h:92-111) -- the component chosen
 // for a given uniform then only depends on the pmf bits.  The cell's query records (K x 128 B) are
 // staged in shared memory once per run of vertices of that cell (all lanes read the same record ->
-// broadcast LDS); vertices that arrive unsorted are binned on the device first (counting sort).  The K
-// unnormalised conditional weights of a vertex pair are recomputed in each of the three passes
-// (sum -> select -> pdf) instead of being parked anywhere: no per-thread storage, full occupancy.
+// broadcast LDS); vertices that arrive unsorted are binned on the device first (counting sort).  Three
+// passes per vertex pair (sum -> select -> pdf).  For K <= 64 the K weights of the pair are parked in shared
+// memory between the passes (QSTORE: 12 warps per SM at K = 64, but pass 3 sheds a quarter of its
+// arithmetic); for K = 128 they are recomputed in each pass (QRECOMP: no per-thread storage, 32 warps per SM).
+// Either way every pass sees the same weight bits.
 #include <algorithm>
 #include <cstdlib>
 
@@ -122,10 +124,8 @@ struct PairRes {
 };
 
 // unnormalised conditional weight pi_k N3(x; mu_a, Sigma_aa) of component k for both vertices
-// (R: sdmm_conditioner.h:242-244).  Called from all three passes: recomputing the K weights costs
-// 13 packed instructions per component but needs no per-thread storage, so occupancy is bounded by
-// registers, not by a K x threads shared-memory column.  Same instruction sequence each time ->
-// bit-identical weights in every pass.
+// (R: sdmm_conditioner.h:242-244).  12 packed instructions + 2 MUFU per component.  Where a pass recomputes it
+// (QRECOMP), the same instruction sequence gives bit-identical weights every time.
 __device__ __forceinline__ float2 pair_weight(const float4* __restrict__ rec, int k, const PairIn& in) {
     const float4* rk = rec + qoff<true>(k);
     const float4 r0 = rk[0], r1 = rk[1], r2 = rk[2];
@@ -468,6 +468,7 @@ __global__ void __launch_bounds__(512) bin_count_smem_kernel(const uint32_t* __r
     __syncthreads();
     const size_t chunk = (n + gridDim.x - 1) / gridDim.x;
     const size_t begin = (size_t)blockIdx.x * chunk, end = begin + chunk < n ? begin + chunk : n;
+#pragma unroll 4
     for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
         const uint32_t c = cell_idx[i];
         atomicAdd(&sh_bins[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
@@ -489,6 +490,7 @@ __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* _
     __syncthreads();
     const size_t chunk = (n + gridDim.x - 1) / gridDim.x;
     const size_t begin = (size_t)blockIdx.x * chunk, end = begin + chunk < n ? begin + chunk : n;
+#pragma unroll 4
     for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
         const uint32_t c = cell_idx[i];
         atomicAdd(&sh_cnt[c < n_buckets - 1 ? c : n_buckets - 1], 1u);
@@ -500,11 +502,33 @@ __global__ void __launch_bounds__(512) bin_scatter_smem_kernel(const uint32_t* _
         sh_cnt[b] = 0;
     }
     __syncthreads();
-    for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
-        const uint32_t c = cell_idx[i];
-        const uint32_t b = c < n_buckets - 1 ? c : n_buckets - 1;
-        const uint32_t pos = sh_base[b] + atomicAdd(&sh_cnt[b], 1u);
-        write_sorted_record(pl, n, i, pos, c);
+    // four vertices per thread and trip: their 28 loads are independent and in flight together (one vertex per trip
+    // left the pass latency-bound at a fifth of the HBM rate)
+    constexpr int U = 4;
+    for (size_t i0 = begin + threadIdx.x; i0 < end; i0 += (size_t)U * blockDim.x) {
+        uint32_t c[U];
+        float4 a[U];
+        float2 b2[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = i0 + (size_t)u * blockDim.x;
+            if (i < end) {
+                c[u] = cell_idx[i];
+                a[u] = make_float4(pl.pos3[i], pl.pos3[n + i], pl.pos3[2 * n + i], pl.in3[i]);
+                b2[u] = make_float2(pl.in3[n + i], pl.in3[2 * n + i]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = i0 + (size_t)u * blockDim.x;
+            if (i < end) {
+                const uint32_t b = c[u] < n_buckets - 1 ? c[u] : n_buckets - 1;
+                const uint32_t pos = sh_base[b] + atomicAdd(&sh_cnt[b], 1u);
+                pl.qin[2 * (size_t)pos] = a[u];
+                pl.qin[2 * (size_t)pos + 1] = make_float4(b2[u].x, b2[u].y, __uint_as_float((uint32_t)i), __uint_as_float(c[u]));
+                pl.invperm[i] = pos;
+            }
+        }
     }
 }
 
@@ -785,7 +809,7 @@ cudaError_t launch_bin_vertices(const uint32_t* cell_idx, size_t n, int max_cell
             configured = true;
         }
         // one chunk per CTA; few, fat CTAs keep the per-bucket global atomics rare
-        const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((n + 8191) / 8192, 148 * 2));
+        const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((n + 8191) / 8192, 148 * 4));
         bin_count_smem_kernel<<<grid, 512, hist_smem / 2, st>>>(cell_idx, n, B, count);
         bin_scan_kernel<<<1, 1024, 0, st>>>(count, B, cursor);
         bin_scatter_smem_kernel<<<grid, 512, hist_smem, st>>>(cell_idx, n, B, cursor, pl);
