@@ -198,6 +198,25 @@ int sdmmb_sample_pdf_pruned(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx
                             float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac, uint32_t* d_out_comp,
                             uint8_t* d_out_valid, void* stream);
 
+/* Allocation-free variant of sdmmb_sample_pdf for vertices in ANY order (binned = 0).  It has no counterpart in
+ * the reference and was added: callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it) get the same binning + query kernels
+ * with the binning scratch in a file-scope static __device__ array instead of the per-stream grow-only buffer.
+ * The call makes no cudaMalloc / cudaFree / allocating library call; inputs and outputs are the caller's.
+ * Limits: n <= SDMMB_NOALLOC_MAX_VERTICES per call and a context of <= SDMMB_NOALLOC_MAX_CELLS cells, else
+ * SDMMB_E_LIMIT (nothing is launched).  The array (4.8 MB) is held by every GPU that loads the library until the
+ * process exits.  ALL calls, contexts and streams of a device share it: calls that overlap on the GPU race --
+ * keep them on one stream or order them with events.  Nothing in it needs clearing by the caller (the histogram
+ * words are zeroed on `stream` at the start of every call).  The first call per device looks the array's device
+ * address up (cudaGetSymbolAddress, which may load the module): make one warm-up call before a graph capture.
+ * Results are bit-identical to sdmmb_sample_pdf(..., binned = 0, ...). */
+#define SDMMB_NOALLOC_MAX_VERTICES 65536
+#define SDMMB_NOALLOC_MAX_CELLS 65536
+#define SDMMB_E_LIMIT (-10)    /* beyond the fixed limits of sdmmb_sample_pdf_noalloc */
+int sdmmb_sample_pdf_noalloc(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+                             const float* d_u3, float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
+                             uint32_t* d_out_comp, uint8_t* d_out_valid, void* stream);
+
 int sdmmb_sample_pdf_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell_idx, const float* h_pos3,
                           const float* h_u3, float* h_out_dir3, float* h_out_pdf,
                           float* h_out_inv_jac, uint32_t* h_out_comp, uint8_t* h_out_valid,

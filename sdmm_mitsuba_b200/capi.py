@@ -33,7 +33,11 @@ SYMBOLS = [
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
     "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
     "sdmmb_host_alloc", "sdmmb_host_free", "sdmmb_sample_pdf_pruned", "sdmmb_pt_set_product",
+    "sdmmb_sample_pdf_noalloc",
 ]
+NOALLOC_MAX_VERTICES = 65536   # SDMMB_NOALLOC_MAX_VERTICES
+NOALLOC_MAX_CELLS = 65536      # SDMMB_NOALLOC_MAX_CELLS
+E_LIMIT = -10
 PEER_HANDLE_BYTES = 192  # SDMMB_PEER_HANDLE_BYTES
 ITERS_INTEGRATOR = -1    # SDMMB_ITERS_INTEGRATOR: the integrator's 2|1 iteration rule per cell
 E_PEER = -9
@@ -108,6 +112,7 @@ def lib():
     L.sdmmb_download_conditioner.argtypes = [vp, i, i, fp, vp]
     L.sdmmb_sample_pdf.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]
     L.sdmmb_pdf.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
+    L.sdmmb_sample_pdf_noalloc.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.sdmmb_sample_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, fp, fp, up, bp, i, vp]
     L.sdmmb_pdf_host.argtypes = [vp, sz, up, fp, fp, fp, bp, i, vp]
     L.sdmmb_set_tree.argtypes = [vp, i, vp]

@@ -42,6 +42,7 @@ const char* sdmmb_get_error_string(int code) {
         case SDMMB_E_NCCL: return "NCCL missing or returned an error";
         case SDMMB_E_DATA_FULL: return "Data full.";
         case SDMMB_E_PEER: return "peer memory not reachable (no P2P between the devices or CUDA IPC open failed)";
+        case SDMMB_E_LIMIT: return "sdmmb_sample_pdf_noalloc: more than SDMMB_NOALLOC_MAX_VERTICES vertices per call or a context with more than SDMMB_NOALLOC_MAX_CELLS cells (fixed static scratch)";
         default: return "unknown error";
     }
 }

@@ -102,6 +102,41 @@ int query_host(sdmmb_ctx* ctx, size_t n, const uint32_t* h_cell, const float* h_
 
 }  // namespace
 
+// ---- allocation-free guided query (no counterpart in the reference) ----
+// The random-order query bins its vertices by cell on the device and needs scratch for that; the entry points
+// above take it from a grow-only cudaMalloc'ed buffer per stream.  Callers that must not allocate (CUDA graph
+// capture, tight serving loops) get the same kernels over ONE file-scope device array of a fixed size instead.
+// Layout as in query_common: count[B] | cursor[B] | invperm[n] | qin[8n] | qout[8n] words, B = max_cells + 1.
+#define NOALLOC_SCRATCH_WORDS (2 * ((size_t)SDMMB_NOALLOC_MAX_CELLS + 1) + 17 * (size_t)SDMMB_NOALLOC_MAX_VERTICES + 4)
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
+
+namespace {
+
+// In host code `g_noalloc_scratch` is only the host-side stand-in of the symbol; the device address is looked up
+// once per device, with that device current, and cached.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+uint32_t* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch_for(sdmmb_ctx* ctx, uint32_t** out) {
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return SDMMB_E_INVALID;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        int cur = -1;
+        CK(cudaGetDevice(&cur));
+        if (cur != dev) return SDMMB_E_STATE;   // the caller holds a DeviceGuard; never look the symbol up elsewhere
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return SDMMB_E_CUDA;
+        g_noalloc_ptr[dev] = (uint32_t*)p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return SDMMB_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 int sdmmb_sample_pdf(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
@@ -210,6 +245,43 @@ int sdmmb_sample_pdf_pruned(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx
     q.max_cells = ctx->max_cells;
     CK(launch_query_pruned(q, ctx->K_user, max_components, preserve_idx, (cudaStream_t)stream));
     if (n) ctx->launches += 1;
+    return SDMMB_OK;
+}
+
+// ---- allocation-free guided query: static scratch and its address look-up are above extern "C" ----
+int sdmmb_sample_pdf_noalloc(sdmmb_ctx* ctx, size_t n, const uint32_t* d_cell_idx, const float* d_pos3,
+                             const float* d_u3, float* d_out_dir3, float* d_out_pdf, float* d_out_inv_jac,
+                             uint32_t* d_out_comp, uint8_t* d_out_valid, void* stream) {
+    if (!ctx || (n && (!d_cell_idx || !d_pos3 || !d_u3 || !d_out_dir3 || !d_out_pdf || !d_out_inv_jac || !d_out_comp)))
+        return SDMMB_E_INVALID;
+    if (n > (size_t)SDMMB_NOALLOC_MAX_VERTICES || ctx->max_cells > SDMMB_NOALLOC_MAX_CELLS) return SDMMB_E_LIMIT;
+    if (n == 0) return SDMMB_OK;
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    SDMMB_NVTX("sdmmb guided query (K4, static scratch)");
+    uint32_t* scratch = nullptr;
+    int rc = noalloc_scratch_for(ctx, &scratch);
+    if (rc) return rc;
+    QueryLaunch q{};
+    q.K = ctx->K;
+    q.n = n;
+    q.qrec = ctx->d_qrec;
+    q.cell_idx = d_cell_idx;
+    q.pos3 = d_pos3;
+    q.u3 = d_u3;
+    q.dir3 = nullptr;
+    q.out_dir3 = d_out_dir3;
+    q.out_pdf = d_out_pdf;
+    q.out_inv_jac = d_out_inv_jac;
+    q.out_comp = d_out_comp;
+    q.out_valid = d_out_valid;
+    q.binned = 0;
+    q.max_cells = ctx->max_cells;
+    q.scratch = scratch;
+    // the array keeps the previous call's contents: launch_bin_vertices zeroes the histogram words (count[B]) with
+    // a memset node on `stream`; cursor / invperm / qin / qout are fully written for [0, n) before they are read
+    CK(launch_query(q, (cudaStream_t)stream));
+    ctx->launches += 5;
     return SDMMB_OK;
 }
 
