@@ -81,6 +81,25 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
                     const uint8_t* d_cell_initialized, float* d_image_sum, float* d_pool,
                     size_t pool_capacity, size_t pool_count, sdmmb_pt_stats* out, void* stream);
 
+/* First pass of optimize() over the pool that sdmmb_pt_render filled (volpath_sdmm.cpp:244-259, 140-149): for the
+ * samples [0, n) of d_pool [15][pool_capacity]: d_out_cell[i] = device slot of STree::find(key_i) (-1: none), and
+ * d_out_stats [8][max_cells] doubles (zeroed by the call) = per cell: number, sum p, sum p^2 of the MAIN pushes with
+ * index >= new_begin (the SpatialStats the renderer's push feeds, sdmm_proc.cpp:893-895; planes 0, 1-3, 4-6) and
+ * the number of all pooled samples (Data::size of canBeOptimized; plane 7).  One kernel, asynchronous on `stream`. */
+int sdmmb_pt_pool_stats(sdmmb_ctx* ctx, const float* d_pool, size_t pool_capacity, size_t n, size_t new_begin,
+                        int32_t* d_out_cell, double* d_out_stats, void* stream);
+
+/* One recursion level of optimize()'s data-driven splits for all leaves that split at that level
+ * (split_leaf_recurse -> create_child, sdmm/include/sdmm/accelerators/spatial_tree.h:169-214, 253-292): d_cell [n]
+ * (in/out, the slots sdmmb_pt_pool_stats wrote) moves every sample of a splitting leaf to the child that takes it
+ * (-1: rounding left it between the two boxes) and d_out_stats [7][max_cells] doubles (zeroed by the call) receives
+ * the children's SpatialStats (n, sum p, sum p^2 over the samples inside the child's box, :204-206).
+ * d_tab_i [3][max_cells] int32 per PARENT slot: split axis (-1 = does not split), child 0's slot, child 1's slot;
+ * d_tab_f [2][max_cells]: child 0's min and child 1's max along the axis; d_box [2][3][max_cells]: min / max corner
+ * of the box per CHILD slot.  The host decides which leaves split and where (HostTree, the reference's rule). */
+int sdmmb_pt_rebucket(sdmmb_ctx* ctx, const float* d_pool, size_t pool_capacity, size_t n, int32_t* d_cell,
+                      const int32_t* d_tab_i, const float* d_tab_f, const float* d_box, double* d_out_stats, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

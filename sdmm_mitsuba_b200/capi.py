@@ -33,7 +33,7 @@ SYMBOLS = [
     "sdmmb_copy_cells", "sdmmb_sample_pdf_product", "sdmmb_pdf_product", "sdmmb_pt_create", "sdmmb_pt_destroy", "sdmmb_pt_render",
     "sdmmb_set_samples_borrowed", "sdmmb_set_em_overlap", "sdmmb_peer_export", "sdmmb_peer_attach", "sdmmb_peer_detach", "sdmmb_peer_wait", "sdmmb_peer_status",
     "sdmmb_host_alloc", "sdmmb_host_free", "sdmmb_sample_pdf_pruned", "sdmmb_pt_set_product",
-    "sdmmb_sample_pdf_noalloc",
+    "sdmmb_sample_pdf_noalloc", "sdmmb_pt_pool_stats", "sdmmb_pt_rebucket",
 ]
 NOALLOC_MAX_VERTICES = 65536   # SDMMB_NOALLOC_MAX_VERTICES
 NOALLOC_MAX_CELLS = 65536      # SDMMB_NOALLOC_MAX_CELLS
@@ -144,6 +144,8 @@ def lib():
     L.sdmmb_sample_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp, vp, vp, vp]
     L.sdmmb_pdf_product.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp, i, fp, vp, vp, vp]
     L.sdmmb_pt_set_product.argtypes = [vp, i, fp]
+    L.sdmmb_pt_pool_stats.argtypes = [vp, vp, sz, sz, sz, vp, vp, vp]
+    L.sdmmb_pt_rebucket.argtypes = [vp, vp, sz, sz, vp, vp, vp, vp, vp, vp]
     L.sdmmb_pt_render.argtypes = [vp, i, C.c_uint64, i, i, vp, fp, fp, sz, sz, C.POINTER(PtStats), vp]
     for name in SYMBOLS:
         if name not in ("sdmmb_get_error_string", "sdmmb_last_cuda_error"):

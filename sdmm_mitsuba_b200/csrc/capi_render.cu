@@ -2,6 +2,8 @@
 // the progressive training loop's render pass with device-resident mixtures (rows F1 of SURVEY.md section 8f).
 #include "capi_internal.h"
 
+#include <vector>
+
 using namespace sdmmb;
 using namespace sdmmb_capi;
 
@@ -56,6 +58,81 @@ void pt_carve_lists(sdmmb_pt* pt, size_t n, PtLists& L) {
     L.pdfB = (float*)take(n * 4); L.validB = (uint8_t*)take(n);
     L.nrmA = (float*)take(3 * n * 4); L.nrmB = (float*)take(3 * n * 4);
     L.counters = pt->d_counters;
+}
+
+// Bottom-up clustering of the scene's quads for the bounce kernel's culling: start from one cluster per quad and keep
+// merging the two clusters whose common bounding box has the smallest surface area, clusters of at most 6 quads, until
+// about n / 4 clusters are left (the faces of a small box end up together, a wall spanning the scene stays alone).
+// The quads are then stored in cluster order; boxes are enlarged by 1e-4 of the scene's extent.
+void cluster_quads(PtScene& s) {
+    const int n = s.n_quads;
+    struct Box { float lo[3], hi[3]; };
+    auto area = [](const Box& b) {
+        const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+        return 2.f * (dx * dy + dy * dz + dz * dx);
+    };
+    auto join = [](const Box& a, const Box& b) {
+        Box r;
+        for (int c = 0; c < 3; ++c) { r.lo[c] = std::min(a.lo[c], b.lo[c]); r.hi[c] = std::max(a.hi[c], b.hi[c]); }
+        return r;
+    };
+    std::vector<std::vector<int>> members(n);
+    std::vector<Box> box(n);
+    Box scene{{3e38f, 3e38f, 3e38f}, {-3e38f, -3e38f, -3e38f}};
+    for (int q = 0; q < n; ++q) {
+        members[q] = {q};
+        const PtQuad& Q = s.quads[q];
+        Box b{{3e38f, 3e38f, 3e38f}, {-3e38f, -3e38f, -3e38f}};
+        for (int corner = 0; corner < 4; ++corner)
+            for (int c = 0; c < 3; ++c) {
+                const float v = Q.p0[c] + ((corner & 1) ? Q.e1[c] : 0.f) + ((corner & 2) ? Q.e2[c] : 0.f);
+                b.lo[c] = std::min(b.lo[c], v);
+                b.hi[c] = std::max(b.hi[c], v);
+            }
+        box[q] = b;
+        scene = join(scene, b);
+    }
+    // SDMMB_PT_NO_CULL=1 (tests): one cluster holding every quad in the caller's order = the plain loop over all quads
+    const char* no_cull = getenv("SDMMB_PT_NO_CULL");
+    if (no_cull && atoi(no_cull) != 0) {
+        members.assign(1, std::vector<int>());
+        for (int q = 0; q < n; ++q) members[0].push_back(q);
+        box.assign(1, scene);
+    }
+    const size_t target = (size_t)std::max(1, (n + 3) / 4);
+    while (members.size() > target) {
+        int bi = -1, bj = -1;
+        float best = 3e38f;
+        for (size_t i = 0; i < members.size(); ++i)
+            for (size_t j = i + 1; j < members.size(); ++j) {
+                if (members[i].size() + members[j].size() > 6) continue;
+                const float a = area(join(box[i], box[j]));
+                if (a < best) { best = a; bi = (int)i; bj = (int)j; }
+            }
+        if (bi < 0) break;
+        members[bi].insert(members[bi].end(), members[bj].begin(), members[bj].end());
+        box[bi] = join(box[bi], box[bj]);
+        members.erase(members.begin() + bj);
+        box.erase(box.begin() + bj);
+    }
+    float extent = 0.f;
+    for (int c = 0; c < 3; ++c) extent = std::max(extent, scene.hi[c] - scene.lo[c]);
+    const float margin = 1e-4f * extent + 1e-6f;
+    PtQuad sorted[PT_MAX_QUADS];
+    int at = 0;
+    s.n_groups = (int)members.size();
+    for (size_t g = 0; g < members.size(); ++g) {
+        std::sort(members[g].begin(), members[g].end());
+        PtGroup& G = s.groups[g];
+        G.first = at;
+        G.count = (int)members[g].size();
+        for (int c = 0; c < 3; ++c) { G.bmin[c] = box[g].lo[c] - margin; G.bmax[c] = box[g].hi[c] + margin; }
+        for (int q : members[g]) {
+            s.orig[at] = q;
+            sorted[at++] = s.quads[q];
+        }
+    }
+    for (int q = 0; q < n; ++q) s.quads[q] = sorted[q];
 }
 
 // one product-guiding query launch over a list of the tracer (the BSDF table already lives on the device)
@@ -140,6 +217,7 @@ int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, i
         Q.n[0] = nx / len; Q.n[1] = ny / len; Q.n[2] = nz / len;
         Q.inv_len2[0] = 1.f / l1; Q.inv_len2[1] = 1.f / l2;
     }
+    cluster_quads(s);
     for (int c = 0; c < 3; ++c) {
         s.cam_origin[c] = cam->origin[c]; s.cam_right[c] = cam->right[c]; s.cam_up[c] = cam->up[c];
         s.cam_forward[c] = cam->forward[c];
@@ -167,6 +245,32 @@ int sdmmb_pt_destroy(sdmmb_pt* pt) {
     return SDMMB_OK;
 }
 
+int sdmmb_pt_pool_stats(sdmmb_ctx* ctx, const float* d_pool, size_t pool_capacity, size_t n, size_t new_begin,
+                        int32_t* d_out_cell, double* d_out_stats, void* stream) {
+    if (!ctx || !d_out_stats || n > pool_capacity || (n && (!d_pool || !d_out_cell))) return SDMMB_E_INVALID;
+    if (!ctx->d_tree) return SDMMB_E_STATE;
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    SDMMB_NVTX("sdmmb pool cells + SpatialStats");
+    CK(pt_launch_pool_stats(ctx->d_tree, ctx->n_tree_nodes, d_pool, pool_capacity, n, new_begin, (uint32_t)ctx->max_cells,
+                            d_out_cell, d_out_stats, (cudaStream_t)stream));
+    if (n) ctx->launches += 1;
+    return SDMMB_OK;
+}
+
+int sdmmb_pt_rebucket(sdmmb_ctx* ctx, const float* d_pool, size_t pool_capacity, size_t n, int32_t* d_cell,
+                      const int32_t* d_tab_i, const float* d_tab_f, const float* d_box, double* d_out_stats, void* stream) {
+    if (!ctx || !d_out_stats || !d_tab_i || !d_tab_f || !d_box || n > pool_capacity || (n && (!d_pool || !d_cell)))
+        return SDMMB_E_INVALID;
+    CTX_LOCK(ctx);
+    DeviceGuard g(ctx->device);
+    SDMMB_NVTX("sdmmb split level: re-bucket + child SpatialStats");
+    CK(pt_launch_rebucket(d_pool, pool_capacity, n, d_cell, d_tab_i, d_tab_f, d_box, (uint32_t)ctx->max_cells, d_out_stats,
+                          (cudaStream_t)stream));
+    if (n) ctx->launches += 1;
+    return SDMMB_OK;
+}
+
 int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collect,
                     const uint8_t* d_cell_initialized, float* d_image_sum, float* d_pool,
                     size_t pool_capacity, size_t pool_count, sdmmb_pt_stats* out, void* stream) {
@@ -178,23 +282,23 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t n = (size_t)pt->h_scene.width * pt->h_scene.height * (size_t)spp;
-    if (n >= (1u << 27)) return SDMMB_E_DATA_FULL;   // push-sequence ids are path * 32 + ... in 32 bits
-    if (n > pt->paths_cap) {
+    const size_t n_total = (size_t)pt->h_scene.width * pt->h_scene.height * (size_t)spp;
+    if (n_total >= (1u << 27)) return SDMMB_E_DATA_FULL;   // push-sequence ids are path * 32 + ... in 32 bits
+    // A pass is traced in batches of at most `batch` paths: the per-path state (628 B) and the query lists (184 B) are
+    // allocated once for a batch instead of growing with spp; a path's pixel, random stream and push-sequence ids
+    // follow its GLOBAL index, so the result does not depend on the batch size.
+    static const size_t batch_env = [] { const char* v = getenv("SDMMB_PT_BATCH"); return v ? (size_t)atoll(v) : (size_t)0; }();
+    const size_t batch = std::min(n_total, batch_env ? batch_env : ((size_t)16 << 20));
+    if (batch > pt->paths_cap) {
         cudaFree(pt->d_paths); pt->d_paths = nullptr; pt->paths_cap = 0;
-        CK(cudaMalloc(&pt->d_paths, n * pt_path_bytes() + 64 * 256));
-        pt->paths_cap = n;
+        CK(cudaMalloc(&pt->d_paths, batch * pt_path_bytes() + 64 * 256));
+        pt->paths_cap = batch;
     }
-    if (guided && n > pt->lists_cap) {
+    if (guided && batch > pt->lists_cap) {
         cudaFree(pt->d_lists); pt->d_lists = nullptr; pt->lists_cap = 0;
-        CK(cudaMalloc(&pt->d_lists, n * 184 + 64 * 256));  // 174 B of records + query planes per path
-        pt->lists_cap = n;
+        CK(cudaMalloc(&pt->d_lists, batch * 184 + 64 * 256));  // 174 B of records + query planes per path
+        pt->lists_cap = batch;
     }
-    PtPaths P{};
-    pt_carve_paths(pt, n, P);
-    PtLists L{};
-    if (guided) pt_carve_lists(pt, n, L);
-    L.counters = pt->d_counters;
     PtFrame F{};
     F.tree = ctx->d_tree;
     F.n_tree_nodes = ctx->n_tree_nodes;
@@ -212,54 +316,63 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     CK(cudaMemcpyAsync(pt->d_counters, h_cnt, sizeof(h_cnt), cudaMemcpyHostToDevice, st));
     uint64_t launches = 0, qa = 0, qb = 0;   // `launches` = this tracer's own kernels (K4's are counted by query_common)
     const uint64_t ctx_before = ctx->launches;
-    CK(pt_launch_generate(pt->d_scene, P, F, st));
-    ++launches;
-    size_t nA = 0, nB = 0;
-    for (int bounce = 0; bounce < pt->h_scene.max_depth; ++bounce) {
-        CK(cudaMemsetAsync(pt->d_counters, 0, 8, st));
-        CK(pt_launch_bounce(pt->d_scene, P, L, F, bounce == 0 ? 1 : 0, nA, nB, st));
+    for (size_t base = 0; base < n_total; base += batch) {
+        const size_t n = std::min(batch, n_total - base);
+        PtPaths P{};
+        pt_carve_paths(pt, n, P);
+        PtLists L{};
+        if (guided) pt_carve_lists(pt, n, L);
+        L.counters = pt->d_counters;
+        F.path_base = base;
+        CK(pt_launch_generate(pt->d_scene, P, F, st));
         ++launches;
-        nA = nB = 0;
-        if (!guided) continue;
-        uint32_t c2[2];
-        CK(cudaMemcpyAsync(c2, pt->d_counters, 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        nA = c2[0];
-        nB = c2[1];
-        if (nA + nB == 0) continue;
-        CK(pt_launch_pack_lists(pt->d_scene, L, nA, nB, st));
-        ++launches;
-        if (pt->n_bsdf > 0) {
-            // sampleProduct: conditional x learned-BSDF mixture, component 0 re-centred on the shading normal
-            // (every surface here is diffuse: sdmm_proc.cpp:335-339), sampled / evaluated per vertex (:375-381, 409-417)
-            if (nA) {
-                int rc = product_query(ctx, pt, nA, L.cellA, L.posA, L.uA, nullptr, L.nrmA, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, st);
-                if (rc) return rc;
+        size_t nA = 0, nB = 0;
+        for (int bounce = 0; bounce < pt->h_scene.max_depth; ++bounce) {
+            CK(cudaMemsetAsync(pt->d_counters, 0, 8, st));
+            CK(pt_launch_bounce(pt->d_scene, P, L, F, bounce == 0 ? 1 : 0, nA, nB, st));
+            ++launches;
+            nA = nB = 0;
+            if (!guided) continue;
+            uint32_t c2[2];
+            CK(cudaMemcpyAsync(c2, pt->d_counters, 8, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            nA = c2[0];
+            nB = c2[1];
+            if (nA + nB == 0) continue;
+            CK(pt_launch_pack_lists(pt->d_scene, L, nA, nB, st));
+            ++launches;
+            if (pt->n_bsdf > 0) {
+                // sampleProduct: conditional x learned-BSDF mixture, component 0 re-centred on the shading normal
+                // (every surface here is diffuse: sdmm_proc.cpp:335-339), sampled / evaluated per vertex (:375-381, 409-417)
+                if (nA) {
+                    int rc = product_query(ctx, pt, nA, L.cellA, L.posA, L.uA, nullptr, L.nrmA, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, st);
+                    if (rc) return rc;
+                }
+                if (nB) {
+                    int rc = product_query(ctx, pt, nB, L.cellB, L.posB, nullptr, L.dirB, L.nrmB, nullptr, L.pdfB, nullptr, nullptr, L.validB, st);
+                    if (rc) return rc;
+                }
+            } else {
+                if (nA) {
+                    int rc = query_common(ctx, nA, L.cellA, L.posA, L.uA, nullptr, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, 0, st);
+                    if (rc) return rc;
+                }
+                if (nB) {
+                    int rc = query_common(ctx, nB, L.cellB, L.posB, nullptr, L.dirB, nullptr, L.pdfB, nullptr, nullptr, L.validB, 0, st);
+                    if (rc) return rc;
+                }
             }
-            if (nB) {
-                int rc = product_query(ctx, pt, nB, L.cellB, L.posB, nullptr, L.dirB, L.nrmB, nullptr, L.pdfB, nullptr, nullptr, L.validB, st);
-                if (rc) return rc;
-            }
-        } else {
-            if (nA) {
-                int rc = query_common(ctx, nA, L.cellA, L.posA, L.uA, nullptr, L.dirA, L.pdfA, L.ijA, L.compA, L.validA, 0, st);
-                if (rc) return rc;
-            }
-            if (nB) {
-                int rc = query_common(ctx, nB, L.cellB, L.posB, nullptr, L.dirB, nullptr, L.pdfB, nullptr, nullptr, L.validB, 0, st);
-                if (rc) return rc;
-            }
+            qa += nA;
+            qb += nB;
         }
-        qa += nA;
-        qb += nB;
+        CK(pt_launch_finish(pt->d_scene, P, L, F, st));
+        ++launches;
     }
-    CK(pt_launch_finish(pt->d_scene, P, L, F, st));
-    ++launches;
     CK(cudaMemcpyAsync(h_cnt, pt->d_counters, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     ctx->launches += launches;
     if (out) {
-        out->paths = n;
+        out->paths = n_total;
         out->guided_queries = qa;
         out->mis_queries = qb;
         out->pool_count = h_cnt[2] < pool_capacity ? h_cnt[2] : pool_capacity;

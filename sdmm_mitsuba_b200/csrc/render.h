@@ -19,9 +19,20 @@ struct PtQuad {
     float emission[3];
 };
 
+// Quads clustered by proximity on the host (sdmmb_pt_create); a ray tests a cluster's quads only when it passes
+// the cluster's (slightly enlarged) bounding box.  quads[] is stored in cluster order; orig[] is the caller's index
+// of each quad: ties in the hit distance go to the lowest ORIGINAL index, as a loop over the caller's order gives.
+struct PtGroup {
+    float bmin[3], bmax[3];
+    int first, count;
+};
+
 struct PtScene {
     PtQuad quads[PT_MAX_QUADS];
     int n_quads;
+    PtGroup groups[PT_MAX_QUADS];
+    int n_groups;
+    int orig[PT_MAX_QUADS];
     // perspective camera: ray dir = forward + (1 - 2 sx / w) tan_x right + (1 - 2 sy / h) tan_y up
     float cam_origin[3], cam_right[3], cam_up[3], cam_forward[3];
     float tan_x, tan_y;
@@ -75,12 +86,17 @@ struct PtFrame {
     float* image;     // [3][w*h] running sums
     float* pool;      // [PT_POOL_PLANES][pool_cap]
     size_t pool_cap;
+    size_t path_base; // a pass is traced in batches of paths: global path id = path_base + index in the batch
 };
 
 cudaError_t pt_launch_generate(const PtScene* d_scene, const PtPaths& P, const PtFrame& F, cudaStream_t st);
 cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, int first,
                              size_t nA, size_t nB, cudaStream_t st);
 cudaError_t pt_launch_pack_lists(const PtScene* d_scene, const PtLists& L, size_t nA, size_t nB, cudaStream_t st);
+cudaError_t pt_launch_pool_stats(const TreeNode* nodes, int n_nodes, const float* pool, size_t cap, size_t n, size_t new_begin,
+                                 uint32_t max_cells, int32_t* out_cell, double* stats, cudaStream_t st);
+cudaError_t pt_launch_rebucket(const float* pool, size_t cap, size_t n, int32_t* cell_of, const int32_t* tab_i, const float* tab_f,
+                               const float* box, uint32_t max_cells, double* stats, cudaStream_t st);
 cudaError_t pt_launch_finish(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, cudaStream_t st);
 
 }  // namespace sdmmb

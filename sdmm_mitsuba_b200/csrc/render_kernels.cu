@@ -60,24 +60,70 @@ __device__ __forceinline__ V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y *
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
 
-// nearest quad along (o, d); returns quad index or -1
-__device__ int intersect(const PtScene& sc, V3 o, V3 d, float& t_hit) {
-    int best = -1;
-    float tb = 3.0e38f;
-    for (int q = 0; q < sc.n_quads; ++q) {
+// The scene's quads and clusters as the bounce kernel stages them in shared memory (one copy per CTA):
+//   quad q    : 4 float4 = (n, p0.x) (p0.yz, e1.xy) (e1.z, e2) (1/|e1|^2, 1/|e2|^2, original index, -)
+//   cluster g : 2 float4 = (bmin, first) (bmax, count)
+constexpr int PT_SQ_F4 = 4;
+struct SceneSmem {
+    float4 quad[PT_MAX_QUADS * PT_SQ_F4];
+    float4 group[PT_MAX_QUADS * 2];
+};
+
+__device__ __forceinline__ void stage_scene(const PtScene& sc, SceneSmem& S) {
+    for (int q = threadIdx.x; q < sc.n_quads; q += blockDim.x) {
         const PtQuad& Q = sc.quads[q];
-        const V3 n = ld3(Q.n);
-        const float dn = dot(n, d);
-        if (dn == 0.f) continue;
-        const V3 p0 = ld3(Q.p0);
-        const float t = dot(n, p0 - o) / dn;
-        if (!(t > PT_RAY_EPS && t < tb)) continue;
-        const V3 h = o + d * t - p0;
-        const float u = dot(h, ld3(Q.e1)) * Q.inv_len2[0];
-        const float v = dot(h, ld3(Q.e2)) * Q.inv_len2[1];
-        if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) continue;
-        tb = t;
-        best = q;
+        S.quad[q * PT_SQ_F4 + 0] = make_float4(Q.n[0], Q.n[1], Q.n[2], Q.p0[0]);
+        S.quad[q * PT_SQ_F4 + 1] = make_float4(Q.p0[1], Q.p0[2], Q.e1[0], Q.e1[1]);
+        S.quad[q * PT_SQ_F4 + 2] = make_float4(Q.e1[2], Q.e2[0], Q.e2[1], Q.e2[2]);
+        S.quad[q * PT_SQ_F4 + 3] = make_float4(Q.inv_len2[0], Q.inv_len2[1], __int_as_float(sc.orig[q]), 0.f);
+    }
+    for (int g = threadIdx.x; g < sc.n_groups; g += blockDim.x) {
+        const PtGroup& G = sc.groups[g];
+        S.group[2 * g + 0] = make_float4(G.bmin[0], G.bmin[1], G.bmin[2], __int_as_float(G.first));
+        S.group[2 * g + 1] = make_float4(G.bmax[0], G.bmax[1], G.bmax[2], __int_as_float(G.count));
+    }
+}
+
+// nearest quad along (o, d); returns the quad's index (cluster order) or -1.  Per quad the arithmetic is the plain
+// ray / parallelogram test; the cluster boxes only decide which quads are looked at (they are enlarged on the host
+// by 1e-4 of the scene's extent, far above the rounding of a hit point that passed the (u, v) test), and a tie in t
+// goes to the lowest original index -- the result equals a loop over all quads in the caller's order.
+__device__ int intersect(const SceneSmem& S, int n_groups, V3 o, V3 d, float& t_hit) {
+    int best = -1, best_orig = 0x7fffffff;
+    float tb = 3.0e38f;
+    const V3 inv = v3(__fdividef(1.f, d.x), __fdividef(1.f, d.y), __fdividef(1.f, d.z));   // culling only: 2 ulp is far inside the margin
+    for (int g = 0; g < n_groups; ++g) {
+        const float4 g0 = S.group[2 * g], g1 = S.group[2 * g + 1];
+        // slab test.  For an axis the ray is parallel to (inv = +-inf) the two planes give -inf / +inf when the origin
+        // lies between them (never culls) and the same infinity twice when it does not (culls, correctly); 0 * inf =
+        // NaN (origin exactly on a plane) is dropped by fminf / fmaxf.  (The one-FMA form g * inv - o * inv is NOT
+        // used: with inv = inf it turns "origin inside" into inf - inf.)
+        const float ax = (g0.x - o.x) * inv.x, bx = (g1.x - o.x) * inv.x;
+        const float ay = (g0.y - o.y) * inv.y, by = (g1.y - o.y) * inv.y;
+        const float az = (g0.z - o.z) * inv.z, bz = (g1.z - o.z) * inv.z;
+        const float t_in = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+        const float t_out = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        if (t_in > t_out || t_out < 0.f || t_in > tb) continue;
+        const int first = __float_as_int(g0.w), last = first + __float_as_int(g1.w);
+        for (int q = first; q < last; ++q) {
+            const float4 a = S.quad[q * PT_SQ_F4 + 0], b = S.quad[q * PT_SQ_F4 + 1];
+            const V3 n = v3(a.x, a.y, a.z);
+            const float dn = dot(n, d);
+            if (dn == 0.f) continue;
+            const V3 p0 = v3(a.w, b.x, b.y);
+            const float t = dot(n, p0 - o) / dn;
+            if (!(t > PT_RAY_EPS && t <= tb)) continue;
+            const float4 c = S.quad[q * PT_SQ_F4 + 2], e = S.quad[q * PT_SQ_F4 + 3];
+            const V3 h = o + d * t - p0;
+            const float u = dot(h, v3(b.z, b.w, c.x)) * e.x;
+            const float v = dot(h, v3(c.y, c.z, c.w)) * e.y;
+            if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) continue;
+            const int orig = __float_as_int(e.z);
+            if (t == tb && orig > best_orig) continue;
+            tb = t;
+            best = q;
+            best_orig = orig;
+        }
     }
     t_hit = tb;
     return best;
@@ -106,17 +152,35 @@ __device__ V3 cosine_hemisphere(float u1, float u2) {
 // rebuilt during the descent: child 0 is the upper half (its min[axis] = split), child 1 the lower half.
 __device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, int n_nodes, V3 p, const float* root_min,
                                    const float* root_max, float* amin, float* amax, uint32_t miss) {
-    for (int i = 0; i < 3; ++i) { amin[i] = root_min[i]; amax[i] = root_max[i]; }
+    // the box lives in scalars updated with selects: an array indexed by the split axis would sit in local memory
+    float lo0 = root_min[0], lo1 = root_min[1], lo2 = root_min[2], hi0 = root_max[0], hi1 = root_max[1], hi2 = root_max[2];
+    uint32_t node = 0, found = miss;
+    for (int depth = 0; depth < 96; ++depth) {
+        if (node >= (uint32_t)n_nodes) break;
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
+        const int axis = raw.x;
+        if (axis < 0) { found = (uint32_t)raw.z; break; }
+        const float split = __int_as_float(raw.y);
+        const float c = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
+        const bool up = split < c;
+        node = up ? (uint32_t)raw.z : (uint32_t)raw.w;
+        lo0 = (up && axis == 0) ? split : lo0; lo1 = (up && axis == 1) ? split : lo1; lo2 = (up && axis == 2) ? split : lo2;
+        hi0 = (!up && axis == 0) ? split : hi0; hi1 = (!up && axis == 1) ? split : hi1; hi2 = (!up && axis == 2) ? split : hi2;
+    }
+    amin[0] = lo0; amin[1] = lo1; amin[2] = lo2;
+    amax[0] = hi0; amax[1] = hi1; amax[2] = hi2;
+    return found;
+}
+
+// STree::find without the box (the bounce kernel only needs the cell)
+__device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes, int n_nodes, V3 p, uint32_t miss) {
     uint32_t node = 0;
     for (int depth = 0; depth < 96; ++depth) {
         if (node >= (uint32_t)n_nodes) return miss;
         const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
-        const int axis = raw.x;
-        if (axis < 0) return (uint32_t)raw.z;
-        const float split = __int_as_float(raw.y);
-        const float c = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
-        if (split < c) { node = (uint32_t)raw.z; amin[axis] = split; }
-        else { node = (uint32_t)raw.w; amax[axis] = split; }
+        if (raw.x < 0) return (uint32_t)raw.z;
+        const float c = raw.x == 0 ? p.x : (raw.x == 1 ? p.y : p.z);
+        node = (__int_as_float(raw.y) < c) ? (uint32_t)raw.z : (uint32_t)raw.w;
     }
     return miss;
 }
@@ -131,10 +195,10 @@ __global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, P
     if (i >= P.n) return;
     const PtScene& sc = *scp;
     const size_t npix = (size_t)sc.width * sc.height;
-    const size_t pix = i % npix;
+    const size_t pix = (F.path_base + i) % npix;
     const int px = (int)(pix % sc.width), py = (int)(pix / sc.width);
     Rng rng;
-    rng.seed(F.seed, (uint64_t)i);
+    rng.seed(F.seed, (uint64_t)(F.path_base + i));
     const float sx = (float)px + rng.next(), sy = (float)py + rng.next();
     const float cx = (1.f - 2.f * sx / (float)sc.width) * sc.tan_x;
     const float cy = (1.f - 2.f * sy / (float)sc.height) * sc.tan_y;
@@ -155,11 +219,15 @@ __global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, P
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
                                                         int first, size_t nA, size_t nB) {
+    __shared__ SceneSmem S;
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P.n) return;
-    int depth = P.depth[i];
-    if (depth <= 0) return;
+    int depth = (i < P.n) ? P.depth[i] : 0;
+    if (!__syncthreads_or(depth > 0)) return;   // a CTA of finished paths leaves at once
     const PtScene& sc = *scp;
+    stage_scene(sc, S);
+    __syncthreads();
+    if (depth <= 0) return;
+    const int n_groups = sc.n_groups;
     const size_t n = P.n;
     Rng rng{P.rng[i], P.rng[n + i]};
     V3 thr = v3(P.thr[i], P.thr[n + i], P.thr[2 * n + i]);
@@ -217,7 +285,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
             thr = thr * weight;
             o = p;
             d = wo;
-            hq = intersect(sc, o, d, t_hit);            // rayIntersectAndLookForEmitter      R: 796-798
+            hq = intersect(S, n_groups, o, d, t_hit);   // rayIntersectAndLookForEmitter      R: 796-798
             V3 value = v3(0.f, 0.f, 0.f);
             if (hq >= 0) {
                 const PtQuad& H = sc.quads[hq];
@@ -254,7 +322,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
     } else {
         o = v3(P.o[i], P.o[n + i], P.o[2 * n + i]);
         d = v3(P.d[i], P.d[n + i], P.d[2 * n + i]);
-        hq = intersect(sc, o, d, t_hit);
+        hq = intersect(S, n_groups, o, d, t_hit);
         if (hq < 0) alive = false;
         else {
             const PtQuad& H = sc.quads[hq];              // emitted radiance seen directly   R: 672-675
@@ -278,9 +346,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
         int mode = 0;
         uint32_t slot = 0;
         if (F.guided) {
-            float amin[3], amax[3];
-            const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, npos, sc.root_min, sc.root_max, amin, amax,
-                                                 0xffffffffu);
+            const uint32_t cell = find_leaf(F.tree, F.n_tree_nodes, npos, 0xffffffffu);
             if (cell < F.max_cells && F.cell_initialized[cell]) {
                 if (u_mis <= F.w_bsdf) {                 // heuristicConditionalWeight       R: 383-392
                     mode = 1;
@@ -341,11 +407,22 @@ __global__ void pt_pack_lists_kernel(const PtScene* __restrict__ scp, PtLists L,
     }
 }
 
-__device__ void pool_push(const PtLists& L, const PtFrame& F, const float* vp, size_t n, float w, V3 key, float is_main,
-                          uint32_t seq) {
-    const uint32_t idx = atomicAdd(&L.counters[2], 1u);
+// One push site of the collection, executed by the WHOLE warp: the lanes that push reserve consecutive pool
+// slots with one atomic per warp (the pool counter is a single word: per-lane atomics on it serialise across the
+// GPU) and write them coalesced.  "Data full." (R: sdmm/include/sdmm/opt/data.h:60-66) is counted per sample.
+__device__ __forceinline__ void pool_push_warp(bool pred, const PtLists& L, const PtFrame& F, const float* vp, size_t n,
+                                               float w, V3 key, float is_main, uint32_t seq) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&L.counters[2], (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (!pred) return;
+    const uint32_t idx = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
     if (idx >= F.pool_cap) {
-        atomicAdd(&L.counters[3], 1u);   // "Data full." (R: sdmm/include/sdmm/opt/data.h:60-66)
+        atomicAdd(&L.counters[3], 1u);
         return;
     }
     float* o = F.pool + idx;
@@ -357,47 +434,179 @@ __device__ void pool_push(const PtLists& L, const PtFrame& F, const float* vp, s
     o[14 * S] = __uint_as_float(seq);   // order a single-threaded reference would push in: path, vertex, jitter
 }
 
-// end of every path: film accumulation + the sample collection of Li's tail (R: 862-965)
+// end of every path: film accumulation + the sample collection of Li's tail (R: 862-965).  The vertex loop is
+// warp-uniform (a lane without a vertex at this step idles) so that every push site is reached by all 32 lanes.
 __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P.n) return;
+    const bool in = i < P.n;
     const PtScene& sc = *scp;
     const size_t n = P.n;
     const size_t npix = (size_t)sc.width * sc.height;
-    const size_t pix = i % npix;
-    for (int c = 0; c < 3; ++c) atomicAdd(&F.image[c * npix + pix], P.li[c * n + i]);
-    const int depth = min(P.vcount[i], PT_MAX_VERTS);
-    if (depth == 0 || !F.collect) return;
-    Rng rng{P.rng[i], P.rng[n + i]};
-    const int first_saved = max(depth - sc.saved_per_path, 0);
-    for (int dv = depth - 1; dv >= first_saved; --dv) {
-        const float* vp = P.verts + ((size_t)dv * PT_VERT_FLOATS) * n + i;
-        const float w = (vp[9 * n] + vp[10 * n] + vp[11 * n]) * (1.f / 3.f);   // weight.average()
-        const bool valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);         // is_valid_sample
-        const V3 pos = v3(vp[0], vp[n], vp[2 * n]);
-        float smin[3], smax[3];
-        const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
-        if (cell >= F.max_cells) continue;   // the reference throws here; positions are inside the root AABB
-        const uint32_t seq0 = ((uint32_t)i << 5) | ((uint32_t)(depth - 1 - dv) << 2);
-        if (valid) pool_push(L, F, vp, n, w, pos, 1.f, seq0);
-        uint32_t pushed = 0;
-        int n_jitters = (dv >= depth - 1) ? 1 : 0;
-        if (w > 1000.f) ++n_jitters;
-        int attempts = 0;
-        for (int j = 0; j < n_jitters; ++j) {
-            const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next();
-            const V3 key = v3(pos.x + (u0 - 0.5f) * (smax[0] - smin[0]), pos.y + (u1 - 0.5f) * (smax[1] - smin[1]),
-                              pos.z + (u2 - 0.5f) * (smax[2] - smin[2]));
-            float jmin[3], jmax[3];
-            const uint32_t jc = find_leaf_aabb(F.tree, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
-            // find() never fails for a point outside the root box (it lands in a boundary leaf), as in the reference
-            if (jc >= F.max_cells || (jmin[0] == smin[0] && jmin[1] == smin[1] && jmin[2] == smin[2])) {
-                ++attempts;
-                if (attempts < 8) --j;
-                continue;
-            }
-            if (valid) pool_push(L, F, vp, n, w, key, 0.f, seq0 + (++pushed));
+    int depth = 0;
+    Rng rng{0, 1};
+    if (in) {
+        const size_t pix = (F.path_base + i) % npix;
+        for (int c = 0; c < 3; ++c) atomicAdd(&F.image[c * npix + pix], P.li[c * n + i]);
+        if (F.collect) {
+            depth = min(P.vcount[i], PT_MAX_VERTS);
+            rng.state = P.rng[i];
+            rng.inc = P.rng[n + i];
         }
+    }
+    if (!F.collect) return;
+    const int first_saved = max(depth - sc.saved_per_path, 0);
+    for (int dv = depth - 1;; --dv) {
+        const bool act = dv >= first_saved && dv >= 0;
+        if (!__any_sync(0xffffffffu, act)) break;
+        const float* vp = P.verts + ((size_t)(act ? dv : 0) * PT_VERT_FLOATS) * n + (in ? i : 0);
+        float w = 0.f;
+        bool valid = false, cell_ok = false;
+        V3 pos = v3(0.f, 0.f, 0.f);
+        float smin[3] = {0.f, 0.f, 0.f}, smax[3] = {0.f, 0.f, 0.f};
+        int n_jitters = 0;
+        if (act) {
+            w = (vp[9 * n] + vp[10 * n] + vp[11 * n]) * (1.f / 3.f);    // weight.average()
+            valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);           // is_valid_sample
+            pos = v3(vp[0], vp[n], vp[2 * n]);
+            const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
+            cell_ok = cell < F.max_cells;   // the reference throws otherwise; positions are inside the root AABB
+            n_jitters = (dv >= depth - 1) ? 1 : 0;
+            if (w > 1000.f) ++n_jitters;
+        }
+        const uint32_t seq0 = ((uint32_t)(F.path_base + i) << 5) | ((uint32_t)(depth - 1 - dv) << 2);
+        pool_push_warp(act && cell_ok && valid, L, F, vp, n, w, pos, 1.f, seq0);
+        uint32_t pushed = 0;
+        int attempts = 0;
+        for (int j = 0; j < 2; ++j) {
+            bool want = act && cell_ok && j < n_jitters, got = false;
+            V3 key = pos;
+            while (want && !got) {
+                const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next();
+                key = v3(pos.x + (u0 - 0.5f) * (smax[0] - smin[0]), pos.y + (u1 - 0.5f) * (smax[1] - smin[1]),
+                         pos.z + (u2 - 0.5f) * (smax[2] - smin[2]));
+                float jmin[3], jmax[3];
+                const uint32_t jc = find_leaf_aabb(F.tree, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
+                // find() never fails for a point outside the root box (it lands in a boundary leaf), as in the reference
+                if (jc >= F.max_cells || (jmin[0] == smin[0] && jmin[1] == smin[1] && jmin[2] == smin[2])) {
+                    if (++attempts >= 8) want = false;   // this jitter is given up; a later one fails at its first miss
+                } else {
+                    got = true;
+                }
+            }
+            const bool push = got && valid;
+            if (push) ++pushed;
+            pool_push_warp(push, L, F, vp, n, w, key, 0.f, seq0 + pushed);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// optimize(), first pass over the pool: cell of every pooled sample (STree::find of its key), per-cell sample
+// counts (Data::size of canBeOptimized, volpath_sdmm.cpp:140-149) and the SpatialStats of the leaves -- count,
+// sum p, sum p^2 of the MAIN pushes of this pass only (R: 893-895) -- in double.  A warp whose lanes all fall
+// into one cell (neighbouring paths: the common case) reduces first and issues one atomic per quantity.
+// stats: [8][max_cells] doubles = n_main, sum xyz, sum sq xyz, n_all.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pt_pool_stats_kernel(const TreeNode* __restrict__ nodes, int n_nodes,
+                                                            const float* __restrict__ pool, size_t cap, size_t n,
+                                                            size_t new_begin, uint32_t max_cells, int32_t* __restrict__ out_cell,
+                                                            double* __restrict__ stats) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = i < n;
+    uint32_t cell = 0xffffffffu;
+    bool is_main = false;
+    double px = 0.0, py = 0.0, pz = 0.0;
+    if (in) {
+        const V3 key = v3(pool[10 * cap + i], pool[11 * cap + i], pool[12 * cap + i]);
+        uint32_t node = 0;
+        for (int depth = 0; depth < 96 && node < (uint32_t)n_nodes; ++depth) {
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
+            if (raw.x < 0) { cell = (uint32_t)raw.z; break; }
+            const float c = raw.x == 0 ? key.x : (raw.x == 1 ? key.y : key.z);
+            node = (__int_as_float(raw.y) < c) ? (uint32_t)raw.z : (uint32_t)raw.w;
+        }
+        if (cell >= max_cells) cell = 0xffffffffu;
+        out_cell[i] = (int32_t)cell;
+        is_main = cell != 0xffffffffu && i >= new_begin && (((int)pool[13 * cap + i]) & 1);   // plane 13 = is_main + 2 * pass (integrator.py)
+        if (is_main) { px = pool[i]; py = pool[cap + i]; pz = pool[2 * cap + i]; }
+    }
+    const unsigned full = 0xffffffffu;
+    const bool counted = in && cell != 0xffffffffu;
+    const unsigned mc = __ballot_sync(full, counted);
+    if (mc == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mc) - 1;
+    const uint32_t cell0 = __shfl_sync(full, cell, leader);
+    const bool uniform = __all_sync(full, !counted || cell == cell0);
+    const size_t C = max_cells;
+    if (uniform) {
+        const unsigned mm = __ballot_sync(full, is_main);
+        double v[6] = {px, py, pz, px * px, py * py, pz * pz};
+        if (mm) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(full, v[k], off);
+        }
+        if (lane == leader) {
+            atomicAdd(&stats[7 * C + cell0], (double)__popc(mc));
+            if (mm) {
+                atomicAdd(&stats[0 * C + cell0], (double)__popc(mm));
+#pragma unroll
+                for (int k = 0; k < 6; ++k) atomicAdd(&stats[(1 + k) * C + cell0], v[k]);
+            }
+        }
+    } else if (counted) {
+        atomicAdd(&stats[7 * C + cell], 1.0);
+        if (is_main) {
+            atomicAdd(&stats[0 * C + cell], 1.0);
+            atomicAdd(&stats[1 * C + cell], px);
+            atomicAdd(&stats[2 * C + cell], py);
+            atomicAdd(&stats[3 * C + cell], pz);
+            atomicAdd(&stats[4 * C + cell], px * px);
+            atomicAdd(&stats[5 * C + cell], py * py);
+            atomicAdd(&stats[6 * C + cell], pz * pz);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// optimize(), one recursion level of the data-driven splits (split_leaf_recurse -> create_child,
+// R: sdmm/include/sdmm/accelerators/spatial_tree.h:169-214) for ALL leaves that split at this level: a sample of a
+// splitting leaf moves to child 0 (position above the child's min along the split axis) or child 1 (at or below
+// the child's max), or to -1 when rounding left it between the two boxes; the children's SpatialStats count the
+// samples inside their boxes (AABB::contains, :204-206).  tab_i [3][C]: axis (-1: the slot does not split), slot of
+// child 0, slot of child 1, per PARENT slot; tab_f [2][C]: child 0's min, child 1's max along the axis;
+// box [2][3][C]: the children's boxes per CHILD slot.  stats [7][C] doubles: n, sum p, sum p^2.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pt_rebucket_kernel(const float* __restrict__ pool, size_t cap, size_t n,
+                                                          int32_t* __restrict__ cell_of, const int32_t* __restrict__ tab_i,
+                                                          const float* __restrict__ tab_f, const float* __restrict__ box,
+                                                          uint32_t max_cells, double* __restrict__ stats) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t c = cell_of[i];
+    const size_t C = max_cells;
+    if (c < 0 || (uint32_t)c >= max_cells) return;
+    const int axis = tab_i[c];
+    if (axis < 0) return;
+    const float p[3] = {pool[i], pool[cap + i], pool[2 * cap + i]};
+    const float pa = axis == 0 ? p[0] : (axis == 1 ? p[1] : p[2]);
+    int32_t nc = -1;
+    if (pa > tab_f[c]) nc = tab_i[C + c];
+    else if (pa <= tab_f[C + c]) nc = tab_i[2 * C + c];
+    cell_of[i] = nc;
+    if (nc < 0) return;
+    bool inside = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) inside = inside && p[k] >= box[k * C + nc] && p[k] <= box[(3 + k) * C + nc];
+    if (!inside) return;
+    atomicAdd(&stats[nc], 1.0);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double v = (double)p[k];
+        atomicAdd(&stats[(1 + k) * C + nc], v);
+        atomicAdd(&stats[(4 + k) * C + nc], v * v);
     }
 }
 
@@ -425,6 +634,22 @@ cudaError_t pt_launch_pack_lists(const PtScene* d_scene, const PtLists& L, size_
 
 cudaError_t pt_launch_finish(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, cudaStream_t st) {
     pt_finish_kernel<<<blocks_for(P.n, 256), 256, 0, st>>>(d_scene, P, L, F);
+    return cudaGetLastError();
+}
+
+cudaError_t pt_launch_pool_stats(const TreeNode* nodes, int n_nodes, const float* pool, size_t cap, size_t n, size_t new_begin,
+                                 uint32_t max_cells, int32_t* out_cell, double* stats, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(stats, 0, (size_t)8 * max_cells * sizeof(double), st);
+    if (e != cudaSuccess || n == 0) return e;
+    pt_pool_stats_kernel<<<blocks_for(n, 256), 256, 0, st>>>(nodes, n_nodes, pool, cap, n, new_begin, max_cells, out_cell, stats);
+    return cudaGetLastError();
+}
+
+cudaError_t pt_launch_rebucket(const float* pool, size_t cap, size_t n, int32_t* cell_of, const int32_t* tab_i, const float* tab_f,
+                               const float* box, uint32_t max_cells, double* stats, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(stats, 0, (size_t)7 * max_cells * sizeof(double), st);
+    if (e != cudaSuccess || n == 0) return e;
+    pt_rebucket_kernel<<<blocks_for(n, 256), 256, 0, st>>>(pool, cap, n, cell_of, tab_i, tab_f, box, max_cells, stats);
     return cudaGetLastError();
 }
 

@@ -77,6 +77,10 @@ class SDMMIntegrator:
         self.iteration = 0
         self.total_spp = 0
         self.stats = []
+        self._acc_size = np.zeros(max_cells, np.int64)          # SpatialStats not yet written into the host tree, per slot
+        self._acc_sum = np.zeros((3, max_cells), np.float64)
+        self._acc_sqr = np.zeros((3, max_cells), np.float64)
+        self._leaf_version = -1
 
     def set_product(self, bsdf):
         """sampleProduct (sdmm_proc.cpp:326-392): guided vertices sample conditional x learned-BSDF mixture; `bsdf` =
@@ -112,18 +116,36 @@ class SDMMIntegrator:
         new = (self.pool_count, int(st.pool_count))
         self.pool_count = int(st.pool_count)
         if collect and new[1] > new[0]:
-            # canonical order: the pool is filled in scheduling order; put this pass's samples in the order a
-            # single-threaded reference would have pushed them (older passes stay in front)
-            seg = self.pool[:, new[0]:new[1]]
-            order = torch.argsort(seg[14].contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF)
-            self.pool[:, new[0]:new[1]] = seg.index_select(1, order)
+            self.pool[13, new[0]:new[1]] += 2.0 * (self.iteration & 0xFF)   # plane 13 = is_main + 2 * pass number
+        # the pool is filled in scheduling order; optimize() sorts the training samples of a cell by their push
+        # sequence number (plane 14), the order a single-threaded reference would have pushed them in
         return st, new
 
     # ---- optimize() -------------------------------------------------------------------------------
-    def _pool_cells(self, lo=0, hi=None):
-        hi = self.pool_count if hi is None else hi
-        key = self.pool[10:13, lo:hi].contiguous()
-        return self.cells.find_cells(key).to(self.torch.int64)
+    def _refresh_leaf_cache(self):
+        """Per-slot views of the host tree's leaves (SpatialStats size, largest box extent); rebuilt when the tree grew."""
+        t, C_ = self.tree, self.cells.max_cells
+        self._st_base = np.zeros(C_, np.int64)
+        self._diag = np.zeros(C_, np.float32)
+        for node in t.leaves():
+            self._st_base[t.slot[node]] = t.st_size[node]
+            self._diag[t.slot[node]] = float((t.amax[node] - t.amin[node]).max())
+        self._leaf_version = t.size()
+
+    def _flush_leaf_stats(self):
+        """Write the per-slot SpatialStats accumulated since the last flush into the tree's leaves."""
+        t = self.tree
+        if self._acc_size.any():
+            for node in t.leaves():
+                sl = t.slot[node]
+                if self._acc_size[sl]:
+                    t.st_size[node] += int(self._acc_size[sl])
+                    t.st_sum[node] = t.st_sum[node] + self._acc_sum[:, sl]
+                    t.st_sqr[node] = t.st_sqr[node] + self._acc_sqr[:, sl]
+            self._acc_size[:] = 0
+            self._acc_sum[:] = 0
+            self._acc_sqr[:] = 0
+        self._leaf_version = -1     # st_size changed: the per-slot base is rebuilt before its next use
 
     def optimize(self, new_range):
         torch = self.torch
@@ -131,36 +153,39 @@ class SDMMIntegrator:
         n = self.pool_count
         if n == 0:
             return dict(trained=0, leaves=t.n_leaves)
-        # cell of every pooled sample = the Data it was pushed into (key = vertex or its jittered copy)
-        cell_of = self._pool_cells()
-        # SpatialStats of the leaves: only the main pushes of this pass feed them (sdmm_proc.cpp:893-895)
+        # cell of every pooled sample = the Data it was pushed into (key = vertex or its jittered copy), the per-cell
+        # sample counts and the SpatialStats of the leaves (only the main pushes of this pass feed them,
+        # sdmm_proc.cpp:893-895): one kernel over the pool, one read-back
         lo, hi = new_range
+        cell32 = torch.empty(n, dtype=torch.int32, device=self.dev)
+        stats_d = torch.empty((8, self.cells.max_cells), dtype=torch.float64, device=self.dev)
+        check(self.cells._L.sdmmb_pt_pool_stats(self.cells._h, C.c_void_p(self.pool.data_ptr()), self.pool.shape[1], n,
+                                                min(lo, n), C.c_void_p(cell32.data_ptr()), C.c_void_p(stats_d.data_ptr()),
+                                                C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
+              "sdmmb_pt_pool_stats", self.cells._h)
+        stats_h = stats_d.cpu().numpy()
+        data_size = np.rint(stats_h[7]).astype(np.int64)
+        # The SpatialStats are accumulated per SLOT (vector adds) and only written into the host tree's per-node records
+        # when a split is still possible: a loop over thousands of leaves per iteration is otherwise the largest host cost.
         if hi > lo:
-            main = self.pool[13, lo:hi] > 0.5
-            pos = self.pool[0:3, lo:hi].to(torch.float64)
-            cm = cell_of[lo:hi][main]
-            size = torch.bincount(cm, minlength=self.cells.max_cells).cpu().numpy()
-            s1 = torch.zeros((3, self.cells.max_cells), dtype=torch.float64, device=self.dev).index_add_(1, cm, pos[:, main])
-            s2 = torch.zeros((3, self.cells.max_cells), dtype=torch.float64, device=self.dev).index_add_(1, cm, pos[:, main] ** 2)
-            s1, s2 = s1.cpu().numpy(), s2.cpu().numpy()
-            for node in t.leaves():
-                sl = t.slot[node]
-                if size[sl]:
-                    t.st_size[node] += int(size[sl])
-                    t.st_sum[node] = t.st_sum[node] + s1[:, sl]
-                    t.st_sqr[node] = t.st_sqr[node] + s2[:, sl]
-        # data-driven splits (volpath_sdmm.cpp:253-259); children inherit the parent's state
+            self._acc_size += np.rint(stats_h[0]).astype(np.int64)
+            self._acc_sum += stats_h[1:4]
+            self._acc_sqr += stats_h[4:7]
         if t.n_leaves <= MAX_LEAF_NODES:
-            ppos = self.pool[0:3, :n]
-            # Level-synchronous: the host decides which leaves split (HostTree, the reference's rule) and the device
-            # re-buckets the samples of ALL leaves of a recursion level and reduces their children's SpatialStats in
-            # one pass; HostTree then renumbers the new nodes into the reference's depth-first creation order.
-            C = self.cells.max_cells
+            self._flush_leaf_stats()
+        # data-driven splits (volpath_sdmm.cpp:253-259); children inherit the parent's state
+        if t.n_leaves <= MAX_LEAF_NODES and any(t.st_size[node] > self.split_threshold for node in t.leaves()):
+            # Level-synchronous: the host decides which leaves split (HostTree, the reference's rule) and ONE kernel per
+            # recursion level re-buckets the samples of all splitting leaves and reduces their children's SpatialStats;
+            # HostTree then renumbers the new nodes into the reference's depth-first creation order.
+            NC = self.cells.max_cells
+            L, h = self.cells._L, self.cells._h
+            ptr = lambda x: C.c_void_p(x.data_ptr())
 
             def rebucket(level):
-                tab_i = np.full((3, C), -1, np.int64)             # per parent slot: axis, slot0, slot1
-                tab_f = np.zeros((2, C), np.float32)              # c0_min, c1_max
-                box = np.zeros((2, 3, C), np.float32)             # per CHILD slot: aabb min / max
+                tab_i = np.full((3, NC), -1, np.int32)            # per parent slot: axis, slot0, slot1
+                tab_f = np.zeros((2, NC), np.float32)             # c0_min, c1_max
+                box = np.zeros((2, 3, NC), np.float32)            # per CHILD slot: aabb min / max
                 for e in level:
                     ps = e["parent_slot"]
                     tab_i[:, ps] = (e["axis"], e["slot0"], e["slot1"])
@@ -170,34 +195,21 @@ class SDMMIntegrator:
                 tab_i_t = torch.as_tensor(tab_i, device=self.dev)
                 tab_f_t = torch.as_tensor(tab_f, device=self.dev)
                 box_t = torch.as_tensor(box, device=self.dev)
-                ok = (cell_of >= 0) & (cell_of < C)
-                safe = torch.where(ok, cell_of, torch.zeros_like(cell_of))
-                idx = torch.nonzero(ok & (tab_i_t[0][safe] >= 0)).squeeze(1)
-                c = cell_of[idx]
-                p = ppos[:, idx]
-                pa = p.gather(0, tab_i_t[0][c][None])[0]
-                upper = pa > tab_f_t[0][c]                        # create_child (spatial_tree.h:190-203): child 0 takes
-                lower = pa <= tab_f_t[1][c]                       # min < p, child 1 takes max >= p
-                newc = torch.where(upper, tab_i_t[1][c], torch.where(lower, tab_i_t[2][c], torch.full_like(c, -1)))
-                cell_of[idx] = newc                               # -1: fell between the two boxes (rounding gap)
-                keep = newc >= 0
-                cc, pp = newc[keep], p[:, keep]
-                inside = ((pp >= box_t[0][:, cc]) & (pp <= box_t[1][:, cc])).all(dim=0)      # AABB::contains (:204-206)
-                ci, q = cc[inside], pp[:, inside].to(torch.float64)
-                size = torch.bincount(ci, minlength=C).cpu().numpy()
-                s1 = torch.zeros((3, C), dtype=torch.float64, device=self.dev).index_add_(1, ci, q).cpu().numpy()
-                s2 = torch.zeros((3, C), dtype=torch.float64, device=self.dev).index_add_(1, ci, q * q).cpu().numpy()
-                return [tuple((int(size[sl]), s1[:, sl].copy(), s2[:, sl].copy()) for sl in (e["slot0"], e["slot1"]))
+                st_d = torch.empty((7, NC), dtype=torch.float64, device=self.dev)
+                check(L.sdmmb_pt_rebucket(h, ptr(self.pool), self.pool.shape[1], n, ptr(cell32), ptr(tab_i_t), ptr(tab_f_t),
+                                          ptr(box_t), ptr(st_d), C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
+                      "sdmmb_pt_rebucket", h)
+                sh = st_d.cpu().numpy()
+                return [tuple((int(round(sh[0, sl])), sh[1:4, sl].copy(), sh[4:7, sl].copy()) for sl in (e["slot0"], e["slot1"]))
                         for e in level]
 
             splits, slot_map = t.split_leaves_levels(self.split_threshold, rebucket)
             if slot_map:
-                lut = np.arange(C, dtype=np.int64)
+                lut = np.arange(NC, dtype=np.int32)
                 for a_, b_ in slot_map.items():
                     lut[a_] = b_
-                ok = cell_of >= 0
-                cell_of = torch.where(ok, torch.as_tensor(lut, device=self.dev)[torch.where(ok, cell_of, torch.zeros_like(cell_of))],
-                                      cell_of)
+                lut_t = torch.as_tensor(lut, device=self.dev)
+                cell32 = torch.where(cell32 >= 0, lut_t[cell32.clamp(min=0).long()], cell32)
             if splits:
                 src = [s[0] for s in splits]
                 dst = [s[2] for s in splits]                              # child 0 keeps the parent's slot
@@ -210,40 +222,51 @@ class SDMMIntegrator:
                 self.cells.set_tree(t.flatten())
                 # keep find(key) consistent with the re-bucketing: move the key of a sample whose key now resolves to
                 # a different leaf to the centre of the leaf that owns it
-                found = self._pool_cells()
-                centre = np.zeros((self.cells.max_cells, 3), np.float32)
+                found = self.cells.find_cells(self.pool[10:13, :n].contiguous())
+                centre = np.zeros((NC, 3), np.float32)
                 for node in t.leaves():
                     centre[t.slot[node]] = 0.5 * (t.amin[node] + t.amax[node])
-                bad = (found != cell_of) & (cell_of >= 0)
+                bad = (found != cell32) & (cell32 >= 0)
                 if bool(bad.any()):
-                    self.pool[10:13, :n][:, bad] = torch.as_tensor(centre, device=self.dev)[cell_of[bad]].t()
-                dropped = cell_of < 0
+                    self.pool[10:13, :n][:, bad] = torch.as_tensor(centre, device=self.dev)[cell32[bad].long()].t()
+                dropped = cell32 < 0
                 if bool(dropped.any()):
                     keepm = ~dropped
                     kept0 = self.pool[:, :n][:, keepm]
                     n = int(kept0.shape[1])
                     self.pool[:, :n] = kept0
                     self.pool_count = n
-                    cell_of = cell_of[keepm]
+                    cell32 = cell32[keepm]
+                data_size = torch.bincount(cell32.long(), minlength=NC).cpu().numpy()
         # canBeOptimized (volpath_sdmm.cpp:140-149)
-        cells_all = cell_of
-        data_size = torch.bincount(cells_all, minlength=self.cells.max_cells).cpu().numpy()
-        stats_size = np.zeros(self.cells.max_cells, np.int64)
-        diag = np.zeros(self.cells.max_cells, np.float32)
-        for node in t.leaves():
-            stats_size[t.slot[node]] = t.st_size[node]
-            diag[t.slot[node]] = float((t.amax[node] - t.amin[node]).max())
+        cells_all = cell32[:n].to(torch.int64)
+        if self._leaf_version != t.size():
+            self._refresh_leaf_cache()
+        stats_size = self._st_base + self._acc_size
+        diag = self._diag
         can = ((self.total_spp > 12) | (data_size > 1000)) & (stats_size >= 64) & (data_size >= 8)
         if not can.any():
             return dict(trained=0, leaves=t.n_leaves)
         can_t = torch.as_tensor(can, device=self.dev)
-        sel = can_t[cells_all]
-        order = torch.argsort(cells_all[sel], stable=True)
-        idx = torch.nonzero(sel).squeeze(1)[order]
-        train = self.pool[:, :n].index_select(1, idx).contiguous()       # sorted by cell: the swapped training_data
         counts = np.where(can, data_size, 0)
+        all_train = int(counts.sum()) == n              # every pooled sample belongs to a cell that trains now
+        # the swapped training_data of every cell: ONE sort of the pool indices by (cell, pass, push sequence) -- older
+        # passes first, then the order a single-threaded reference would have pushed in -- and one gather of the ten
+        # planes the fit reads
+        seq = self.pool[14, :n].view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+        passno = (self.pool[13, :n] * 0.5).to(torch.int64)
+        key = (cells_all << 40) | (passno << 32) | seq
+        if all_train:
+            sel = None
+            idx = torch.sort(key)[1]
+        else:
+            sel = (cells_all >= 0) & can_t[cells_all.clamp(min=0)]
+            base = torch.nonzero(sel).squeeze(1)
+            idx = base[torch.sort(key[base])[1]]
+        del key, seq, passno
+        train = self.pool[0:10, :n].index_select(1, idx)                 # sorted by cell
         off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
-        point6, normal3, weight = train[0:6].contiguous(), train[6:9].contiguous(), train[9].contiguous()
+        point6, normal3, weight = train[0:6], train[6:9], train[9]
         # async schedule: the fit runs on its own stream, ordered after everything queued so far, and is joined in
         # publish_pending() after the next pass; the training copies must outlive it
         if self.optimize_async:
@@ -274,10 +297,12 @@ class SDMMIntegrator:
         else:
             self.initialized[can_t] = 1
         # data.clear() for the optimised cells; everything else stays in the pool
-        keep = ~sel
-        kept = self.pool[:, :n][:, keep]
-        self.pool_count = int(kept.shape[1])
-        self.pool[:, :self.pool_count] = kept
+        if all_train:
+            self.pool_count = 0
+        else:
+            kept = self.pool[:, :n][:, ~sel]
+            self.pool_count = int(kept.shape[1])
+            self.pool[:, :self.pool_count] = kept
         return dict(trained=int(can.sum()), leaves=t.n_leaves, fresh=int(fresh.size), train_samples=int(off[-1]))
 
     def publish_pending(self):
@@ -313,6 +338,7 @@ class SDMMIntegrator:
             rendered += spp
             if schedule == "doubling":
                 spp *= 2
+        self._flush_leaf_stats()      # the host tree's SpatialStats are complete again when render() returns
         return self.image()
 
     def save_checkpoint(self, experiment_path):

@@ -2,8 +2,12 @@
 of the reference integrator built on the reference's own sdmm headers (oracle/ref_render.inc), on the Cornell
 box of test-suite/scenes/cornell-box (BASELINE.json configs[0]).  Both sides draw from identical per-path PCG32
 streams, so paths, collected samples, tree splits and fitted mixtures are comparable one to one."""
+import os
+
 import numpy as np
 import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 from parity import PARAM_RTOL, joint_param_errs
 
@@ -334,3 +338,48 @@ def test_render_writes_a_reference_layout_checkpoint(tmp_path):
     for i in trained:
         # upload normalises the (already normalised) weights once more, like the reference's from_json -> prepare
         assert torch.allclose(r_old[gi.tree.slot[i]], r_new[tree.slot[i]], rtol=2e-5, atol=2e-6), i
+
+
+def _pool_sorted_by_seq(scene, env, spp=64, batch=None):
+    """One unguided collecting pass in a fresh process (the tracer reads its switches once); returns the pooled
+    samples sorted by their push sequence number (the pool itself is filled in scheduling order)."""
+    import os
+    import subprocess
+    import sys
+    import tempfile
+    out = tempfile.mktemp(suffix=".npy")
+    code = (
+        "import sys, numpy as np, torch\n"
+        "sys.path.insert(0, %r)\n"
+        "from sdmm_mitsuba_b200 import scenes\n"
+        "from sdmm_mitsuba_b200.integrator import SDMMIntegrator\n"
+        "quads, cam = getattr(scenes, %r)(160, 90)\n"
+        "g = SDMMIntegrator(quads, cam, K=16, max_depth=6, samples_per_iteration=%d, seed=7, pool_capacity=4_000_000)\n"
+        "st, new = g.render_pass(%d, collect=True)\n"
+        "p = g.pool[:, :g.pool_count].cpu().numpy()\n"
+        "order = np.argsort(p[14].view(np.uint32), kind='stable')\n"
+        "np.save(%r, np.concatenate([p[:, order], g.image_sum.cpu().numpy().sum(0, keepdims=True)[:, :1].repeat(15, 0)], axis=1))\n"
+        % (ROOT, scene, spp, spp, out))
+    e = dict(os.environ, **env)
+    if batch:
+        e["SDMMB_PT_BATCH"] = str(batch)
+    subprocess.check_call([sys.executable, "-c", code], env=e)
+    a = np.load(out)
+    os.remove(out)
+    return a[:, :-1], float(a[0, -1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene", ["interior", "cornell_box"])
+def test_cluster_culling_and_batching_do_not_change_a_single_vertex(scene):
+    """The bounce kernel only looks at the quads of clusters whose (enlarged) box the ray passes, and a pass is traced
+    in batches of paths; both are pure reorganisations: every pooled vertex (position, direction, normal, weight, key)
+    is bit-identical to the plain loop over all quads in the caller's order, traced in one batch."""
+    plain, img_plain = _pool_sorted_by_seq(scene, {"SDMMB_PT_NO_CULL": "1"})
+    culled, img_culled = _pool_sorted_by_seq(scene, {"SDMMB_PT_NO_CULL": "0"})
+    batched, img_batched = _pool_sorted_by_seq(scene, {"SDMMB_PT_NO_CULL": "0"}, batch=50000)
+    assert plain.shape[1] > 1000
+    assert plain.shape == culled.shape == batched.shape
+    assert np.array_equal(plain.view(np.uint32), culled.view(np.uint32))
+    assert np.array_equal(plain.view(np.uint32), batched.view(np.uint32))
+    assert abs(img_culled - img_plain) <= 1e-5 * abs(img_plain) and abs(img_batched - img_plain) <= 1e-5 * abs(img_plain)

@@ -4,7 +4,7 @@ import torch
 from sdmm_mitsuba_b200 import scenes
 from sdmm_mitsuba_b200.integrator import SDMMIntegrator
 quads, cam = scenes.interior(640, 360)
-g = SDMMIntegrator(quads, cam, K=16, max_depth=6, samples_per_iteration=8, seed=5)
+g = SDMMIntegrator(quads, cam, K=16, max_depth=6, samples_per_iteration=8, seed=5, pool_capacity=96_000_000)
 spp = 8
 pr = cProfile.Profile()
 for it in range(4):
@@ -16,4 +16,4 @@ for it in range(4):
     torch.cuda.synchronize()
     pr.disable()
     g.iteration += 1; g.total_spp += spp; spp *= 2
-pstats.Stats(pr).sort_stats("cumulative").print_stats(28)
+pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
