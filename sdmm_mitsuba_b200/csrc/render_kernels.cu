@@ -232,7 +232,10 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
     Rng rng{P.rng[i], P.rng[n + i]};
     V3 thr = v3(P.thr[i], P.thr[n + i], P.thr[2 * n + i]);
     V3 li = v3(P.li[i], P.li[n + i], P.li[2 * n + i]);
-    int vc = P.vcount[i];
+    // vcount word: stored vertices in the low byte, above it one bit per vertex whose outgoing ray found an emitter
+    const int vword = P.vcount[i];
+    int vc = vword & 0xff;
+    uint32_t emit_mask = (uint32_t)vword >> 8;
     V3 o, d;
     int hq;
     float t_hit;
@@ -291,27 +294,20 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
                 const PtQuad& H = sc.quads[hq];
                 if (dot(ld3(H.n), d) < 0.f) value = ld3(H.emission);
             }
-            if (value.x > 0.f || value.y > 0.f || value.z > 0.f) {   // recordRadiance     R: 628-637, 810-812
-                const V3 rad = thr * value;
-                li = li + rad;
-                for (int v = 0; v < vc && v < PT_MAX_VERTS; ++v) {
-                    float* vp = P.verts + ((size_t)v * PT_VERT_FLOATS) * n + i;
-                    const float vpdf = vp[15 * n];
-                    const float r3[3] = {rad.x, rad.y, rad.z};
-                    for (int c = 0; c < 3; ++c) {
-                        const float vthr = vp[(12 + c) * n];
-                        if (vthr > PT_SPEC_EPS) vp[(9 + c) * n] += r3[c] / (vthr * vpdf);
-                    }
-                }
+            // recordRadiance (R: 628-637, 810-812) adds thr * value / (thr_v * pdf_v) to the weight of EVERY earlier vertex
+            // v.  That read-modify-write walk over the path's records does not happen here: the record of this vertex
+            // keeps `value` and its throughput, and pt_finish_kernel replays the same sums in the same order.
+            if (value.x > 0.f || value.y > 0.f || value.z > 0.f) {
+                li = li + thr * value;
+                if (vc < PT_MAX_VERTS) emit_mask |= 1u << vc;
             }
             if (vc < PT_MAX_VERTS) {                     // the cacheable vertex               R: 814-840
                 float* vp = P.verts + ((size_t)vc * PT_VERT_FLOATS) * n + i;
                 const float clamped = fmaxf(misPdf, 0.1f);
-                const float inv = 1.f / clamped;
                 vp[0] = npos.x; vp[n] = npos.y; vp[2 * n] = npos.z;
                 vp[3 * n] = wo.x; vp[4 * n] = wo.y; vp[5 * n] = wo.z;
                 vp[6 * n] = nrm.x; vp[7 * n] = nrm.y; vp[8 * n] = nrm.z;
-                vp[9 * n] = value.x * inv; vp[10 * n] = value.y * inv; vp[11 * n] = value.z * inv;
+                vp[9 * n] = value.x; vp[10 * n] = value.y; vp[11 * n] = value.z;   // emitted radiance found from here
                 vp[12 * n] = thr.x; vp[13 * n] = thr.y; vp[14 * n] = thr.z;
                 vp[15 * n] = clamped;
             }
@@ -380,7 +376,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
     P.rng[i] = rng.state;
     P.thr[i] = thr.x; P.thr[n + i] = thr.y; P.thr[2 * n + i] = thr.z;
     P.li[i] = li.x; P.li[n + i] = li.y; P.li[2 * n + i] = li.z;
-    P.vcount[i] = vc;
+    P.vcount[i] = vc | (int)(emit_mask << 8);
     P.depth[i] = alive ? depth : 0;
 }
 
@@ -443,12 +439,15 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
     const size_t n = P.n;
     const size_t npix = (size_t)sc.width * sc.height;
     int depth = 0;
+    uint32_t emit_mask = 0u;   // vertices whose outgoing ray found an emitter: usually none, or only the path's last one
     Rng rng{0, 1};
     if (in) {
         const size_t pix = (F.path_base + i) % npix;
         for (int c = 0; c < 3; ++c) atomicAdd(&F.image[c * npix + pix], P.li[c * n + i]);
         if (F.collect) {
-            depth = min(P.vcount[i], PT_MAX_VERTS);
+            const int vword = P.vcount[i];   // vertex count | emitter bits (pt_bounce_kernel)
+            depth = min(vword & 0xff, PT_MAX_VERTS);
+            emit_mask = (uint32_t)vword >> 8;
             rng.state = P.rng[i];
             rng.inc = P.rng[n + i];
         }
@@ -465,7 +464,25 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
         float smin[3] = {0.f, 0.f, 0.f}, smax[3] = {0.f, 0.f, 0.f};
         int n_jitters = 0;
         if (act) {
-            w = (vp[9 * n] + vp[10 * n] + vp[11 * n]) * (1.f / 3.f);    // weight.average()
+            // the vertex's sample weight: its own emitted term value / pdf (R: 836-838) plus, for every LATER vertex k of
+            // the path that found an emitter, thr_k value_k / (thr_v pdf_v) per channel with thr_v above Mitsuba's Epsilon
+            // (recordRadiance, R: 615-637) -- summed in path order, as the per-bounce updates were
+            const float vpdf = vp[15 * n];
+            const float inv = 1.f / vpdf;
+            float w3[3] = {vp[9 * n] * inv, vp[10 * n] * inv, vp[11 * n] * inv};
+            if ((emit_mask >> (dv + 1)) != 0u) {
+                const float vthr[3] = {vp[12 * n], vp[13 * n], vp[14 * n]};
+                for (int k = dv + 1; k < depth; ++k) {
+                    if (!((emit_mask >> k) & 1u)) continue;
+                    const float* kp = P.verts + ((size_t)k * PT_VERT_FLOATS) * n + i;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const float rad = kp[(12 + c) * n] * kp[(9 + c) * n];
+                        if (vthr[c] > PT_SPEC_EPS) w3[c] += rad / (vthr[c] * vpdf);
+                    }
+                }
+            }
+            w = (w3[0] + w3[1] + w3[2]) * (1.f / 3.f);                  // weight.average()
             valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);           // is_valid_sample
             pos = v3(vp[0], vp[n], vp[2 * n]);
             const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
