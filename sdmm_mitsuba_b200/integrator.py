@@ -81,6 +81,7 @@ class SDMMIntegrator:
         self._acc_sum = np.zeros((3, max_cells), np.float64)
         self._acc_sqr = np.zeros((3, max_cells), np.float64)
         self._leaf_version = -1
+        self.capture_fit = None     # optional callable(dict) invoked right before a fit with its samples (tests)
 
     def set_product(self, bsdf):
         """sampleProduct (sdmm_proc.cpp:326-392): guided vertices sample conditional x learned-BSDF mixture; `bsdf` =
@@ -290,6 +291,8 @@ class SDMMIntegrator:
             # 2 em_steps while iterations_run < 4, else 1 (volpath_sdmm.cpp:299-305): the rule is applied per cell ON
             # the device (SDMMB_ITERS_INTEGRATOR), no read-back of the iteration counters and no second gather of the
             # young cells' samples; optimize_async_run: always 1 (:217)
+            if self.capture_fit is not None:   # test hook: the inputs of this fit (state is read through self.cells)
+                self.capture_fit(dict(point6=point6, weight=weight, offsets=off, can=can))
             self.cells.set_samples(point6, weight, off)
             self.cells.em_step(1 if self.optimize_async else capi.ITERS_INTEGRATOR, with_conditioner=True)
         if self.optimize_async:
