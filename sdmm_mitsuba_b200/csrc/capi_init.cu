@@ -2,6 +2,8 @@
 // and cell copies (a split's children inherit the parent's mixture and EM state, spatial_tree.h:187-196).
 #include "capi_internal.h"
 
+#include <vector>
+
 using namespace sdmmb;
 using namespace sdmmb_capi;
 
@@ -98,24 +100,53 @@ int sdmmb_copy_cells(sdmmb_ctx* ctx, int n, const int32_t* h_src, const int32_t*
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t K = (size_t)ctx->K;
-    for (int i = 0; i < n; ++i) {
-        const size_t s = (size_t)h_src[i], d = (size_t)h_dst[i];
-        if (s == d) continue;
-        CK(cudaMemcpyAsync(ctx->d_joint + d * JOINT_PLANES * K, ctx->d_joint + s * JOINT_PLANES * K, JOINT_PLANES * K * 4,
-                           cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_em + d * EM_PLANES * K, ctx->d_em + s * EM_PLANES * K, EM_PLANES * K * 4,
-                           cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_scal + d * SCALAR_WORDS, ctx->d_scal + s * SCALAR_WORDS, SCALAR_WORDS * 4,
-                           cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_cdf + d * K, ctx->d_cdf + s * K, K * 4, cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_erec + d * EREC_PLANES * K, ctx->d_erec + s * EREC_PLANES * K, EREC_PLANES * K * 4,
-                           cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(ctx->d_qrec + d * K * QREC_FLOATS, ctx->d_qrec + s * K * QREC_FLOATS, K * QREC_FLOATS * 4,
-                           cudaMemcpyDeviceToDevice, st));
-        if (ctx->d_qrec_back)
-            CK(cudaMemcpyAsync(ctx->d_qrec_back + d * K * QREC_FLOATS, ctx->d_qrec_back + s * K * QREC_FLOATS,
-                               K * QREC_FLOATS * 4, cudaMemcpyDeviceToDevice, st));
+    if (n == 0) return SDMMB_OK;
+    // The copies are sequential by contract (a fresh child can be split again in the same pass: its slot is then the
+    // source of a later copy).  Resolve every destination to the cell whose ORIGINAL content it ends up with; when no
+    // such origin is itself overwritten -- always the case for splits, which only write fresh slots -- all copies run
+    // in one kernel.
+    std::map<int32_t, int32_t> origin;   // slot -> slot whose original content it holds now
+    auto holds = [&](int32_t slot) { auto it = origin.find(slot); return it == origin.end() ? slot : it->second; };
+    for (int i = 0; i < n; ++i) origin[h_dst[i]] = holds(h_src[i]);
+    bool parallel_ok = true;
+    for (const auto& kv : origin)
+        if (kv.second != kv.first && origin.count(kv.second) && origin[kv.second] != kv.second) { parallel_ok = false; break; }
+    CopyCellsArgs a{};
+    int na = 0;
+    auto add = [&](void* base, size_t floats) { a.base[na] = (uint32_t*)base; a.floats_per_cell[na] = floats; ++na; };
+    add(ctx->d_joint, JOINT_PLANES * K);
+    add(ctx->d_em, EM_PLANES * K);
+    add(ctx->d_scal, SCALAR_WORDS);
+    add(ctx->d_cdf, K);
+    add(ctx->d_erec, EREC_PLANES * K);
+    add(ctx->d_qrec, K * QREC_FLOATS);
+    if (ctx->d_qrec_back) add(ctx->d_qrec_back, K * QREC_FLOATS);
+    a.n_arrays = na;
+    std::vector<int32_t> pairs;
+    if (parallel_ok) {
+        for (const auto& kv : origin)
+            if (kv.second != kv.first) { pairs.push_back(kv.second); pairs.push_back(kv.first); }
     }
+    const int launches = parallel_ok ? 1 : n;
+    const size_t words = parallel_ok ? pairs.size() : (size_t)2 * n;
+    int rc = ensure(ctx, &ctx->d_stage2, &ctx->stage2_cap, words * 4 + 16);
+    if (rc) return rc;
+    if (!parallel_ok) {
+        pairs.clear();
+        for (int i = 0; i < n; ++i) { pairs.push_back(h_src[i]); pairs.push_back(h_dst[i]); }
+    }
+    if (pairs.empty()) return SDMMB_OK;
+    CK(cudaMemcpyAsync(ctx->d_stage2, pairs.data(), pairs.size() * 4, cudaMemcpyHostToDevice, st));
+    if (parallel_ok) {
+        a.pairs = (const int32_t*)ctx->d_stage2;
+        CK(launch_copy_cells(a, (int)(pairs.size() / 2), st));
+    } else {
+        for (int i = 0; i < n; ++i) {      // one pair per launch, in order
+            a.pairs = (const int32_t*)ctx->d_stage2 + 2 * i;
+            CK(launch_copy_cells(a, 1, st));
+        }
+    }
+    ctx->launches += launches;
     CK(cudaStreamSynchronize(st));
     return SDMMB_OK;
 }

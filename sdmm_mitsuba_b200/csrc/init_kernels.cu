@@ -266,6 +266,25 @@ __global__ void __launch_bounds__(INIT_THREADS) init_cells_kernel(InitArgs a) {
     }
 }
 
+// Children inherit their parent's complete state on a split (R: accelerators/spatial_tree.h:187-196): one CTA per
+// (source, destination) pair copies the cell's block of every per-cell array.  The sources must not be destinations
+// of the same launch (the host resolves copy chains to their original cell first).
+__global__ void copy_cells_kernel(CopyCellsArgs a) {
+    const size_t s = (size_t)a.pairs[2 * blockIdx.x], d = (size_t)a.pairs[2 * blockIdx.x + 1];
+    if (s == d) return;
+    for (int arr = 0; arr < a.n_arrays; ++arr) {
+        const size_t len = a.floats_per_cell[arr];
+        uint32_t* base = a.base[arr];
+        for (size_t i = threadIdx.x; i < len; i += blockDim.x) base[d * len + i] = base[s * len + i];
+    }
+}
+
+cudaError_t launch_copy_cells(const CopyCellsArgs& a, int n_pairs, cudaStream_t st) {
+    if (n_pairs <= 0) return cudaSuccess;
+    copy_cells_kernel<<<n_pairs, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_init_cells(const InitArgs& a, cudaStream_t st) {
     if (a.n_cells <= 0) return cudaSuccess;
     init_cells_kernel<<<a.n_cells, INIT_THREADS, 0, st>>>(a);

@@ -160,6 +160,14 @@ struct InitArgs {
     int32_t* out_seed_idx;            // nullable, device, [n_cells][K_user/8]
 };
 cudaError_t launch_init_cells(const InitArgs& a, cudaStream_t st);
+// batched cell-to-cell copy of all per-cell state (sdmmb_copy_cells): pairs = [n][2] device words (source, destination)
+struct CopyCellsArgs {
+    const int32_t* pairs;
+    int n_arrays;
+    uint32_t* base[8];
+    size_t floats_per_cell[8];
+};
+cudaError_t launch_copy_cells(const CopyCellsArgs& a, int n_pairs, cudaStream_t st);
 
 cudaError_t launch_find_cells(const TreeNode* nodes, int n_nodes, const float* pos3, size_t stride, size_t n,
                               uint32_t* out, uint32_t miss, cudaStream_t st);

@@ -128,3 +128,32 @@ def test_find_cells_in_a_65536_leaf_tree():
     centres = np.array([0.5 * (t.amin[n] + t.amax[n]) for n in t.leaves()], np.float32).T.copy()
     hit = cells.find_cells(centres).astype(np.int64)
     np.testing.assert_array_equal(hit, np.array([t.slot[n] for n in t.leaves()]))
+
+
+def test_copy_cells_is_sequential_whatever_path_it_takes():
+    """sdmmb_copy_cells: children inherit the parent's complete state on a split (spatial_tree.h:187-196).  The
+    copies are sequential by contract (a fresh child can be the source of a later copy); the library resolves chains
+    and runs them as one kernel when no origin is overwritten, else pair by pair -- same result as a host loop."""
+    from sdmm_mitsuba_b200 import synth
+    from sdmm_mitsuba_b200.mixture import SDMMCells
+    C, K = 12, 16
+    joint, em, scal = synth.make_initial_model(C, K, seed=3)
+    scal[:, 1] = np.arange(C)            # make the scalar words distinguishable too
+    for src, dst in (([0, 8, 1, 9], [8, 9, 10, 11]),        # chains through fresh slots: one kernel
+                     ([1, 0], [2, 1]),                      # an origin is overwritten later: ordered launches
+                     ([3, 3, 5], [3, 4, 4])):               # self copy, a destination written twice
+        cells = SDMMCells(C, K)
+        cells.upload(joint, em, scal)
+        cells.prepare()
+        j0, e0, s0 = cells.download()
+        q0 = cells.query_records().clone().cpu().numpy().reshape(C, -1)
+        cells.copy_cells(src, dst)
+        j1, e1, s1 = cells.download()
+        q1 = cells.query_records().clone().cpu().numpy().reshape(C, -1)
+        jw, ew, sw, qw = j0.copy(), e0.copy(), s0.copy(), q0.copy()
+        for a, b in zip(src, dst):
+            jw[b], ew[b], sw[b], qw[b] = jw[a], ew[a], sw[a], qw[a]
+        np.testing.assert_array_equal(j1, jw)
+        np.testing.assert_array_equal(e1, ew)
+        np.testing.assert_array_equal(s1, sw)
+        np.testing.assert_array_equal(q1, qw)
