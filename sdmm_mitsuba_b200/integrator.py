@@ -187,12 +187,17 @@ class SDMMIntegrator:
                 tab_i = np.full((3, NC), -1, np.int32)            # per parent slot: axis, slot0, slot1
                 tab_f = np.zeros((2, NC), np.float32)             # c0_min, c1_max
                 box = np.zeros((2, 3, NC), np.float32)            # per CHILD slot: aabb min / max
-                for e in level:
-                    ps = e["parent_slot"]
-                    tab_i[:, ps] = (e["axis"], e["slot0"], e["slot1"])
-                    tab_f[:, ps] = (e["c0_min"], e["c1_max"])
-                    box[0, :, e["slot0"]], box[1, :, e["slot0"]] = e["amin0"], e["amax0"]
-                    box[0, :, e["slot1"]], box[1, :, e["slot1"]] = e["amin1"], e["amax1"]
+                ps = np.fromiter((e["parent_slot"] for e in level), np.int64, len(level))
+                sl0 = np.fromiter((e["slot0"] for e in level), np.int64, len(level))
+                sl1 = np.fromiter((e["slot1"] for e in level), np.int64, len(level))
+                tab_i[0, ps] = np.fromiter((e["axis"] for e in level), np.int32, len(level))
+                tab_i[1, ps], tab_i[2, ps] = sl0, sl1
+                tab_f[0, ps] = np.fromiter((e["c0_min"] for e in level), np.float32, len(level))
+                tab_f[1, ps] = np.fromiter((e["c1_max"] for e in level), np.float32, len(level))
+                box[0][:, sl0] = np.array([e["amin0"] for e in level], np.float32).T
+                box[1][:, sl0] = np.array([e["amax0"] for e in level], np.float32).T
+                box[0][:, sl1] = np.array([e["amin1"] for e in level], np.float32).T
+                box[1][:, sl1] = np.array([e["amax1"] for e in level], np.float32).T
                 tab_i_t = torch.as_tensor(tab_i, device=self.dev)
                 tab_f_t = torch.as_tensor(tab_f, device=self.dev)
                 box_t = torch.as_tensor(box, device=self.dev)
@@ -201,8 +206,9 @@ class SDMMIntegrator:
                                           ptr(box_t), ptr(st_d), C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)),
                       "sdmmb_pt_rebucket", h)
                 sh = st_d.cpu().numpy()
-                return [tuple((int(round(sh[0, sl])), sh[1:4, sl].copy(), sh[4:7, sl].copy()) for sl in (e["slot0"], e["slot1"]))
-                        for e in level]
+                size = np.rint(sh[0]).astype(np.int64)
+                ssum, ssqr = np.ascontiguousarray(sh[1:4].T), np.ascontiguousarray(sh[4:7].T)    # [slot][3]
+                return [((int(size[a]), ssum[a], ssqr[a]), (int(size[b]), ssum[b], ssqr[b])) for a, b in zip(sl0, sl1)]
 
             splits, slot_map = t.split_leaves_levels(self.split_threshold, rebucket)
             if slot_map:

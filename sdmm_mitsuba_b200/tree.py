@@ -201,7 +201,7 @@ class HostTree:
             frontier = []
             for (node, ch), st in zip(nodes, stats):
                 for c, (size, ssum, ssqr) in zip(ch, st):
-                    self.st_size[c], self.st_sum[c], self.st_sqr[c] = int(size), np.asarray(ssum, np.float64), np.asarray(ssqr, np.float64)
+                    self.st_size[c], self.st_sum[c], self.st_sqr[c] = int(size), ssum, ssqr
                     frontier.append(c)
                 self.st_size[node] = 0
         if not created:
