@@ -85,17 +85,21 @@ def run_b200(args, cfg):
     del live
     S.torch.cuda.empty_cache()
     cfg5 = None if args.no_cfg5 else cfg5_leg.run(S, args)
-    render = None
+    render = refbench = None
     if S.rank == 0 and S.world == 1 and not args.no_render:
         from benchlegs.render_leg import run_render
         render = run_render(S.torch, cpu=not args.no_cpu_baseline)
+    if S.rank == 0 and S.world == 1 and not args.no_cpu_baseline:
+        from benchlegs import refbench_leg
+        refbench = refbench_leg.run(S.torch, S.local)
     if S.rank == 0:
         line = dict(
             metric="EM sample-component updates/s", value=head["value"], unit="updates/s", n_gpus=S.world,
             steps=args.steps, warmup=args.warmup, ms_per_step=head["ms_per_step"], higher_is_better=True,
             scaling="weak", vs_baseline=None, dtype="f32", data="synthetic", config=head["config"],
             clocks=head["clocks"], e2e=e2e, gpu_launches=head["launches"], roofline=head["roofline"],
-            cpu_baseline=cb, parity=parity, cfg5=cfg5, queries=queries, progressive_render=render)
+            cpu_baseline=cb, parity=parity, cfg5=cfg5, queries=queries, progressive_render=render,
+            reference_benchmark_shape=refbench)
         print(json.dumps(line), flush=True)
     S.close()
 

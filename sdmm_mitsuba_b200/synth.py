@@ -148,3 +148,30 @@ def make_queries(n, n_cells, seed=2, binned=True):
     u3 = rng.uniform(0, 1, (3, n)).astype(np.float32)
     u3 = np.minimum(u3, np.float32(1.0 - 2 ** -24))
     return cell, np.ascontiguousarray(pos3), np.ascontiguousarray(u3)
+
+
+def make_reference_benchmark(n_points=1_000_000, K=64):
+    """The input of the reference's own EM micro-benchmark (sdmm/benchmarks/em.cpp:99-157): ONE cell, K = 64
+    components that all sit at mean (1, 1, 1 | 1, 0, 0) with cov = I and pmf = 1/K, and N = 10^6 identical samples
+    (1, 1, 1 | 1, 0, 0) of weight 1 -- every sample lies exactly on every component's mean (theta = 0, the
+    `sin < 1e-4 -> 1` guard of spaces/spatio_directional.h:105-108); priors as em.cpp:124-149.
+    Returns point6 [6, N], weight [N], offsets [2], joint, em, scal."""
+    point6 = np.zeros((6, n_points), np.float32)
+    point6[0:4] = 1.0
+    weight = np.ones(n_points, np.float32)
+    off = np.array([0, n_points], np.uint32)
+    joint = np.zeros((1, JOINT_PLANES, K), np.float32)
+    joint[:, 0, :] = 1.0 / K
+    joint[:, 1:5, :] = 1.0
+    for i in range(5):
+        joint[:, 7 + 6 * i, :] = 1.0
+    em = np.zeros((1, EM_PLANES, K), np.float32)
+    for i, v in enumerate([2e-3, 2e-3, 2e-3, 2e-4, 2e-4]):
+        em[:, 31 + 6 * i, :] = v
+    scal = np.zeros((1, SCALAR_WORDS), np.uint32)
+    f = scal.view(np.float32)
+    f[:, 3] = 1.0 / K
+    f[:, 4] = 5.0 / K
+    f[:, 5] = 0.2
+    f[:, 6] = 0.5
+    return point6, weight, off, joint, em, scal

@@ -451,3 +451,30 @@ def test_rebinding_an_identical_layout_reuses_the_item_table():
         np.testing.assert_array_equal(e, out[0][1])
         np.testing.assert_array_equal(s, out[0][2])
     assert np.isfinite(out[0][0]).all()
+
+
+def test_reference_benchmark_input_all_samples_on_every_mean():
+    """The input of the reference's own EM micro-benchmark (sdmm/benchmarks/em.cpp:99-157): 64 identical components
+    and N identical samples that sit exactly on every mean (theta = 0: the `sin < 1e-4 -> 1` guard of
+    spaces/spatio_directional.h:105-108, gamma = 1/K everywhere, covariances collapse onto the priors).  Three steps of
+    the benchmark's loop against the oracle, strict tolerances."""
+    from sdmm_mitsuba_b200 import synth
+    K, N = 64, 20000
+    point6, weight, off, joint, em, scal = synth.make_reference_benchmark(N, K)
+    cells = _gpu_cells(1, K, joint, em, scal)
+    cells.set_samples(point6, weight, off)
+    ll_gpu = cells.em_step(3, with_conditioner=True, want_loglik=True).cpu().numpy()
+    jg, eg, sg = cells.download()
+    assert (sg[:, 7] == 0).all() and np.isfinite(jg).all()
+    for name, cls in _oracles():
+        o = cls(1, K)
+        o.set(joint, em, scal)
+        ll = np.concatenate(o.em_step(off, point6, weight, 3, want_loglik=True), axis=1)
+        j, e, s = o.get()
+        err, mism = loglik_err(ll_gpu, ll)
+        assert mism == 0.0 and err <= LL_RTOL, (name, err)
+        assert_joint_close(jg, j, PARAM_RTOL, name + " benchmark input")
+        assert (sg[:, 1] == s[:, 1]).all() and (sg[:, 2] == s[:, 2]).all()
+    # every component saw the same data: identical parameters, equal weights
+    assert np.abs(jg[0, 0] - 1.0 / K).max() < 1e-6
+    assert np.abs(jg[0, 7:32] - jg[0, 7:32, :1]).max() <= 1e-6 * np.abs(jg[0, 7:32]).max()
