@@ -35,6 +35,10 @@ def flatten(is_leaf, axis, child0, child1, aabb_min, leaf_slot=None):
     return nodes, leaf_slot
 
 
+_ZERO3 = np.zeros(3)
+_ZERO3.flags.writeable = False
+
+
 class HostTree:
     """Host restatement of the reference's STree bookkeeping (sdmm/include/sdmm/accelerators/spatial_tree.h):
     node table, split_to_depth (:216-252), data-driven split_leaf_recurse (:254-292) with the split position at
@@ -174,27 +178,68 @@ class HostTree:
         S0 = self.size()
         created, created_slots, popped = {}, {}, []
         frontier = [n for n in range(S0) if self.is_leaf[n] and self.st_size[n] > threshold]
+        f32, f64 = np.float32, np.float64
         while frontier:
+            # One recursion level.  The arithmetic of split_location() and _create_child() for all candidates at once
+            # (same float32 / float64 operations, element by element); only the bookkeeping stays a Python loop.
+            cand = [n for n in frontier if self.st_size[n] > threshold]
             level, nodes = [], []
-            for node in frontier:
-                if self.st_size[node] <= threshold:
-                    continue
-                ax, loc = self.split_location(node)
-                if not (0.0 < loc < 1.0):
-                    continue
-                parent_slot = self.slot[node]
-                self.axis[node] = ax
-                ch = self._split(node, loc)
-                if ch is None:
-                    continue
-                popped.append(self.slot[ch[1]])
-                created[node] = ch
-                created_slots[node] = (self.slot[ch[0]], self.slot[ch[1]])   # a later split clears slot[child]
-                nodes.append((node, ch))
-                level.append(dict(parent_slot=parent_slot, slot0=self.slot[ch[0]], slot1=self.slot[ch[1]], axis=ax,
-                                  c0_min=float(self.amin[ch[0]][ax]), c1_max=float(self.amax[ch[1]][ax]),
-                                  amin0=self.amin[ch[0]], amax0=self.amax[ch[0]], amin1=self.amin[ch[1]],
-                                  amax1=self.amax[ch[1]]))
+            if cand:
+                m = len(cand)
+                rows = np.arange(m)
+                cnt = np.array([self.st_size[n] for n in cand], f64)[:, None]
+                mean = np.array([self.st_sum[n] for n in cand], f64).reshape(m, 3)
+                sqr = np.array([self.st_sqr[n] for n in cand], f64).reshape(m, 3)
+                lo = np.array([self.amin[n] for n in cand], f32).reshape(m, 3)
+                hi = np.array([self.amax[n] for n in cand], f32).reshape(m, 3)
+                with np.errstate(all="ignore"):
+                    var = (sqr - (mean / cnt) ** 2 * cnt) / (cnt - 1.0)
+                    ax = np.zeros(m, np.int64)
+                    for i in (1, 2):
+                        ax = np.where(var[:, i] > var[rows, ax], i, ax)
+                    lo_ax, hi_ax = lo[rows, ax], hi[rows, ax]
+                    loc = ((mean[rows, ax] / cnt[:, 0] - lo_ax.astype(f64)) / (hi_ax - lo_ax).astype(f64)).astype(f32)
+                    ok = (loc > 0.0) & (loc < 1.0)
+                    diag = hi_ax - lo_ax                                               # float32
+                    c0_min = lo_ax + loc * diag                                        # child 0: min raised
+                    c1_max = hi_ax - (f32(1.0) - loc) * diag                           # child 1: max lowered
+                lo0, hi1 = lo.copy(), hi.copy()
+                lo0[rows, ax] = c0_min
+                hi1[rows, ax] = c1_max
+                for r, node in enumerate(cand):
+                    if not ok[r]:
+                        continue
+                    a_ = int(ax[r])
+                    self.axis[node] = a_
+                    if not self.free_slots:       # out of cells: the leaf stays (its axis is already the split's)
+                        continue
+                    parent_slot = self.slot[node]
+                    c0 = len(self.is_leaf)
+                    c1 = c0 + 1
+                    s1 = self.free_slots.pop()
+                    d1 = self.depth[node] + 1
+                    self.is_leaf[node] = False
+                    self.children[node] = (c0, c1)
+                    self.slot[node] = -1
+                    self.is_leaf += (True, True)
+                    self.axis += ((a_ + 1) % 3, (a_ + 1) % 3)
+                    self.children += ((0, 0), (0, 0))
+                    self.amin += (lo0[r], lo[r])
+                    self.amax += (hi[r], hi1[r])
+                    self.depth += (d1, d1)
+                    self.slot += (parent_slot, s1)
+                    self.st_size += (0, 0)
+                    self.st_sum += (_ZERO3, _ZERO3)
+                    self.st_sqr += (_ZERO3, _ZERO3)
+                    self.n_leaves += 1
+                    ch = (c0, c1)
+                    popped.append(s1)
+                    created[node] = ch
+                    created_slots[node] = (parent_slot, s1)   # a later split clears slot[child]
+                    nodes.append((node, ch))
+                    level.append(dict(parent_slot=parent_slot, slot0=parent_slot, slot1=s1, axis=a_,
+                                      c0_min=float(c0_min[r]), c1_max=float(c1_max[r]),
+                                      amin0=lo0[r], amax0=hi[r], amin1=lo[r], amax1=hi1[r]))
             if not level:
                 break
             stats = rebucket(level)
