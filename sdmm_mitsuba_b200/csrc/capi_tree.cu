@@ -4,6 +4,8 @@
 // mitsuba/src/integrators/sdmm/sdmm_proc.cpp:880-928.
 #include "capi_internal.h"
 
+#include <vector>
+
 using namespace sdmmb;
 using namespace sdmmb_capi;
 
@@ -18,15 +20,42 @@ int sdmmb_set_tree(sdmmb_ctx* ctx, int n_nodes, const sdmmb_tree_node* h_nodes) 
         if (nd.axis >= 0 && (nd.child0 >= (uint32_t)n_nodes || nd.child1 >= (uint32_t)n_nodes)) return SDMMB_E_INVALID;
         if (nd.axis < 0 && nd.child0 >= (uint32_t)ctx->max_cells) return SDMMB_E_RANGE;
     }
+    // The device copy is stored BREADTH-FIRST (node 0 = root, then level by level): a descent is a chain of dependent
+    // node loads, and the kernels that descend per path vertex stage the first nodes -- the top levels -- in shared
+    // memory.  Node indices never leave the library (a find returns the leaf's cell slot), so the order is free.
+    // Nodes not reachable from the root are dropped.
+    std::vector<sdmmb_tree_node> bfs;
+    bfs.reserve((size_t)n_nodes);
+    {
+        std::vector<int> order, new_id((size_t)n_nodes, -1);
+        order.reserve((size_t)n_nodes);
+        order.push_back(0);
+        new_id[0] = 0;
+        for (size_t at = 0; at < order.size(); ++at) {
+            const sdmmb_tree_node& nd = h_nodes[order[at]];
+            if (nd.axis < 0) continue;
+            for (uint32_t c : {nd.child0, nd.child1}) {
+                if (new_id[c] >= 0) return SDMMB_E_INVALID;   // a node with two parents: not a tree
+                new_id[c] = (int)order.size();
+                order.push_back((int)c);
+            }
+        }
+        for (int old : order) {
+            sdmmb_tree_node nd = h_nodes[old];
+            if (nd.axis >= 0) { nd.child0 = (uint32_t)new_id[nd.child0]; nd.child1 = (uint32_t)new_id[nd.child1]; }
+            bfs.push_back(nd);
+        }
+    }
+    const int n_bfs = (int)bfs.size();
     CTX_LOCK(ctx);
     DeviceGuard g(ctx->device);
     CK(cudaDeviceSynchronize());
     cudaFree(ctx->d_tree);
     ctx->d_tree = nullptr;
     ctx->n_tree_nodes = 0;
-    CK(cudaMalloc(&ctx->d_tree, (size_t)n_nodes * sizeof(TreeNode)));
-    CK(cudaMemcpy(ctx->d_tree, h_nodes, (size_t)n_nodes * sizeof(TreeNode), cudaMemcpyHostToDevice));
-    ctx->n_tree_nodes = n_nodes;
+    CK(cudaMalloc(&ctx->d_tree, (size_t)n_bfs * sizeof(TreeNode)));
+    CK(cudaMemcpy(ctx->d_tree, bfs.data(), (size_t)n_bfs * sizeof(TreeNode), cudaMemcpyHostToDevice));
+    ctx->n_tree_nodes = n_bfs;
     return SDMMB_OK;
 }
 

@@ -63,7 +63,7 @@ __device__ __forceinline__ V3 ld3(const float* p) { return v3(p[0], p[1], p[2]);
 // The scene's quads and clusters as the bounce kernel stages them in shared memory (one copy per CTA):
 //   quad q    : 4 float4 = (n, p0.x) (p0.yz, e1.xy) (e1.z, e2) (1/|e1|^2, 1/|e2|^2, original index, -)
 //   cluster g : 2 float4 = (bmin, first) (bmax, count)
-constexpr int PT_SQ_F4 = 4;
+constexpr int PT_SQ_F4 = 5;   // 4 used + 1 of padding: lanes read DIFFERENT quads, a 64-byte stride would put them all in two bank groups
 struct SceneSmem {
     float4 quad[PT_MAX_QUADS * PT_SQ_F4];
     float4 group[PT_MAX_QUADS * 2];
@@ -88,10 +88,13 @@ __device__ __forceinline__ void stage_scene(const PtScene& sc, SceneSmem& S) {
 // ray / parallelogram test; the cluster boxes only decide which quads are looked at (they are enlarged on the host
 // by 1e-4 of the scene's extent, far above the rounding of a hit point that passed the (u, v) test), and a tie in t
 // goes to the lowest original index -- the result equals a loop over all quads in the caller's order.
+// Two phases, because the rays of a warp are incoherent after the first bounce: (1) every lane tests ALL cluster
+// boxes and collects its own candidate quads in a 64-bit mask; (2) every lane walks its OWN candidates.  A loop
+// "for each cluster: if my ray passes: for each quad" serialises the union of all lanes' clusters with a few lanes
+// active in each (ncu: 3.3 of 32 lanes on the quad-test lines); here a warp does max_lane(#candidates) quad tests.
 __device__ int intersect(const SceneSmem& S, int n_groups, V3 o, V3 d, float& t_hit) {
-    int best = -1, best_orig = 0x7fffffff;
-    float tb = 3.0e38f;
     const V3 inv = v3(__fdividef(1.f, d.x), __fdividef(1.f, d.y), __fdividef(1.f, d.z));   // culling only: 2 ulp is far inside the margin
+    unsigned long long cand = 0ull;
     for (int g = 0; g < n_groups; ++g) {
         const float4 g0 = S.group[2 * g], g1 = S.group[2 * g + 1];
         // slab test.  For an axis the ray is parallel to (inv = +-inf) the two planes give -inf / +inf when the origin
@@ -103,27 +106,32 @@ __device__ int intersect(const SceneSmem& S, int n_groups, V3 o, V3 d, float& t_
         const float az = (g0.z - o.z) * inv.z, bz = (g1.z - o.z) * inv.z;
         const float t_in = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
         const float t_out = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-        if (t_in > t_out || t_out < 0.f || t_in > tb) continue;
-        const int first = __float_as_int(g0.w), last = first + __float_as_int(g1.w);
-        for (int q = first; q < last; ++q) {
-            const float4 a = S.quad[q * PT_SQ_F4 + 0], b = S.quad[q * PT_SQ_F4 + 1];
-            const V3 n = v3(a.x, a.y, a.z);
-            const float dn = dot(n, d);
-            if (dn == 0.f) continue;
-            const V3 p0 = v3(a.w, b.x, b.y);
-            const float t = dot(n, p0 - o) / dn;
-            if (!(t > PT_RAY_EPS && t <= tb)) continue;
-            const float4 c = S.quad[q * PT_SQ_F4 + 2], e = S.quad[q * PT_SQ_F4 + 3];
-            const V3 h = o + d * t - p0;
-            const float u = dot(h, v3(b.z, b.w, c.x)) * e.x;
-            const float v = dot(h, v3(c.y, c.z, c.w)) * e.y;
-            if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) continue;
-            const int orig = __float_as_int(e.z);
-            if (t == tb && orig > best_orig) continue;
-            tb = t;
-            best = q;
-            best_orig = orig;
-        }
+        if (t_in > t_out || t_out < 0.f) continue;
+        const int first = __float_as_int(g0.w), count = __float_as_int(g1.w);
+        cand |= ((count >= 64 ? ~0ull : ((1ull << count) - 1ull)) << first);
+    }
+    int best = -1, best_orig = 0x7fffffff;
+    float tb = 3.0e38f;
+    while (cand) {
+        const int q = __ffsll((long long)cand) - 1;
+        cand &= cand - 1ull;
+        const float4 a = S.quad[q * PT_SQ_F4 + 0], b = S.quad[q * PT_SQ_F4 + 1];
+        const V3 n = v3(a.x, a.y, a.z);
+        const float dn = dot(n, d);
+        if (dn == 0.f) continue;
+        const V3 p0 = v3(a.w, b.x, b.y);
+        const float t = dot(n, p0 - o) / dn;
+        if (!(t > PT_RAY_EPS && t <= tb)) continue;
+        const float4 c = S.quad[q * PT_SQ_F4 + 2], e = S.quad[q * PT_SQ_F4 + 3];
+        const V3 h = o + d * t - p0;
+        const float u = dot(h, v3(b.z, b.w, c.x)) * e.x;
+        const float v = dot(h, v3(c.y, c.z, c.w)) * e.y;
+        if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) continue;
+        const int orig = __float_as_int(e.z);
+        if (t == tb && orig > best_orig) continue;
+        tb = t;
+        best = q;
+        best_orig = orig;
     }
     t_hit = tb;
     return best;
@@ -148,16 +156,29 @@ __device__ V3 cosine_hemisphere(float u1, float u2) {
     return v3(x, y, sqrtf(fmaxf(0.f, 1.f - x * x - y * y)));
 }
 
+// The first PT_TREE_TOP nodes of the device tree -- it is stored breadth-first (sdmmb_set_tree), so these are its top
+// eight levels -- are staged in shared memory: a descent is a chain of DEPENDENT node loads, and the path state
+// streaming through L1 keeps evicting the table.  Measured over the interior loop: pt_bounce_kernel 123 -> 89 ms with
+// 256 nodes staged; 1024 nodes (ten levels) bring nothing more, so the cheap staging stays.
+constexpr int PT_TREE_TOP = 256;
+__device__ __forceinline__ void stage_tree_top(const TreeNode* __restrict__ nodes, int n_nodes, int4* s_top) {
+    const int m = n_nodes < PT_TREE_TOP ? n_nodes : PT_TREE_TOP;
+    for (int k = threadIdx.x; k < m; k += blockDim.x) s_top[k] = __ldg(reinterpret_cast<const int4*>(nodes) + k);
+}
+__device__ __forceinline__ int4 tree_node(const TreeNode* __restrict__ nodes, const int4* s_top, uint32_t node) {
+    return node < (uint32_t)PT_TREE_TOP ? s_top[node] : __ldg(reinterpret_cast<const int4*>(nodes) + node);
+}
+
 // STree::find with the leaf's AABB (R: sdmm/include/sdmm/accelerators/spatial_tree.h:19-51); the AABB is
 // rebuilt during the descent: child 0 is the upper half (its min[axis] = split), child 1 the lower half.
-__device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, int n_nodes, V3 p, const float* root_min,
+__device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, const int4* s_top, int n_nodes, V3 p, const float* root_min,
                                    const float* root_max, float* amin, float* amax, uint32_t miss) {
     // the box lives in scalars updated with selects: an array indexed by the split axis would sit in local memory
     float lo0 = root_min[0], lo1 = root_min[1], lo2 = root_min[2], hi0 = root_max[0], hi1 = root_max[1], hi2 = root_max[2];
     uint32_t node = 0, found = miss;
     for (int depth = 0; depth < 96; ++depth) {
         if (node >= (uint32_t)n_nodes) break;
-        const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
+        const int4 raw = tree_node(nodes, s_top, node);
         const int axis = raw.x;
         if (axis < 0) { found = (uint32_t)raw.z; break; }
         const float split = __int_as_float(raw.y);
@@ -173,11 +194,11 @@ __device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, int n_nod
 }
 
 // STree::find without the box (the bounce kernel only needs the cell)
-__device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes, int n_nodes, V3 p, uint32_t miss) {
+__device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes, const int4* s_top, int n_nodes, V3 p, uint32_t miss) {
     uint32_t node = 0;
     for (int depth = 0; depth < 96; ++depth) {
         if (node >= (uint32_t)n_nodes) return miss;
-        const int4 raw = __ldg(reinterpret_cast<const int4*>(nodes) + node);
+        const int4 raw = tree_node(nodes, s_top, node);
         if (raw.x < 0) return (uint32_t)raw.z;
         const float c = raw.x == 0 ? p.x : (raw.x == 1 ? p.y : p.z);
         node = (__int_as_float(raw.y) < c) ? (uint32_t)raw.z : (uint32_t)raw.w;
@@ -220,11 +241,13 @@ __global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, P
 __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
                                                         int first, size_t nA, size_t nB) {
     __shared__ SceneSmem S;
+    __shared__ int4 s_top[PT_TREE_TOP];
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     int depth = (i < P.n) ? P.depth[i] : 0;
     if (!__syncthreads_or(depth > 0)) return;   // a CTA of finished paths leaves at once
     const PtScene& sc = *scp;
     stage_scene(sc, S);
+    if (F.guided) stage_tree_top(F.tree, F.n_tree_nodes, s_top);
     __syncthreads();
     if (depth <= 0) return;
     const int n_groups = sc.n_groups;
@@ -342,7 +365,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
         int mode = 0;
         uint32_t slot = 0;
         if (F.guided) {
-            const uint32_t cell = find_leaf(F.tree, F.n_tree_nodes, npos, 0xffffffffu);
+            const uint32_t cell = find_leaf(F.tree, s_top, F.n_tree_nodes, npos, 0xffffffffu);
             if (cell < F.max_cells && F.cell_initialized[cell]) {
                 if (u_mis <= F.w_bsdf) {                 // heuristicConditionalWeight       R: 383-392
                     mode = 1;
@@ -453,6 +476,9 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
         }
     }
     if (!F.collect) return;
+    __shared__ int4 s_top[PT_TREE_TOP];
+    stage_tree_top(F.tree, F.n_tree_nodes, s_top);
+    __syncthreads();
     const int first_saved = max(depth - sc.saved_per_path, 0);
     for (int dv = depth - 1;; --dv) {
         const bool act = dv >= first_saved && dv >= 0;
@@ -485,7 +511,7 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
             w = (w3[0] + w3[1] + w3[2]) * (1.f / 3.f);                  // weight.average()
             valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);           // is_valid_sample
             pos = v3(vp[0], vp[n], vp[2 * n]);
-            const uint32_t cell = find_leaf_aabb(F.tree, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
+            const uint32_t cell = find_leaf_aabb(F.tree, s_top, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
             cell_ok = cell < F.max_cells;   // the reference throws otherwise; positions are inside the root AABB
             n_jitters = (dv >= depth - 1) ? 1 : 0;
             if (w > 1000.f) ++n_jitters;
@@ -502,7 +528,7 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
                 key = v3(pos.x + (u0 - 0.5f) * (smax[0] - smin[0]), pos.y + (u1 - 0.5f) * (smax[1] - smin[1]),
                          pos.z + (u2 - 0.5f) * (smax[2] - smin[2]));
                 float jmin[3], jmax[3];
-                const uint32_t jc = find_leaf_aabb(F.tree, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
+                const uint32_t jc = find_leaf_aabb(F.tree, s_top, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
                 // find() never fails for a point outside the root box (it lands in a boundary leaf), as in the reference
                 if (jc >= F.max_cells || (jmin[0] == smin[0] && jmin[1] == smin[1] && jmin[2] == smin[2])) {
                     if (++attempts >= 8) want = false;   // this jitter is given up; a later one fails at its first miss
