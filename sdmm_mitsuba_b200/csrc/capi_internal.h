@@ -67,8 +67,10 @@ struct sdmmb_ctx {
     size_t stage_cap = 0;
     void* d_stage2 = nullptr;
     size_t stage2_cap = 0;
-    sdmmb::TreeNode* d_tree = nullptr;  // flattened STree
+    sdmmb::TreeNode* d_tree = nullptr;  // flattened STree (breadth-first order)
     int n_tree_nodes = 0;
+    std::vector<sdmmb::TreeNode> h_tree;   // host copy of d_tree (the tracer derives the leaves' boxes from it)
+    uint64_t tree_version = 0;             // bumped by every sdmmb_set_tree
     uint32_t min_samples = 0;    // canBeOptimized threshold applied by the M-step
     void* d_qscratch = nullptr;  // binning scratch of the tree / product paths
     size_t qscratch_cap = 0;

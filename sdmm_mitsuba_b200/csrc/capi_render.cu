@@ -19,6 +19,9 @@ struct sdmmb_pt {
     // sampleProduct: scene-wide learned-BSDF mixture [n_bsdf][7] on the device (0 = plain conditional guiding)
     float* d_bsdf = nullptr;
     int n_bsdf = 0;
+    // per leaf (cell slot): the box STree::find arrives at, [2][max_cells] float4, rebuilt when the context's tree changed
+    float4* d_leaf_box = nullptr;
+    uint64_t box_version = 0;
 };
 
 namespace {
@@ -135,6 +138,45 @@ void cluster_quads(PtScene& s) {
     for (int q = 0; q < n; ++q) s.quads[q] = sorted[q];
 }
 
+// The box of every leaf as the descent of STree::find rebuilds it from the root box (spatial_tree.h:19-51: child 0 is
+// the upper half, its min along the split axis = the split; child 1 the lower half, its max = the split) -- pure
+// copies of split values, so the table holds exactly what a per-vertex rebuild during the descent would produce.
+int update_leaf_boxes(sdmmb_ctx* ctx, sdmmb_pt* pt, cudaStream_t st) {
+    if (pt->d_leaf_box && pt->box_version == ctx->tree_version) return SDMMB_OK;
+    const size_t C = (size_t)ctx->max_cells;
+    if (!pt->d_leaf_box) CK(cudaMalloc(&pt->d_leaf_box, 2 * C * sizeof(float4)));
+    std::vector<float4> box(2 * C, make_float4(0.f, 0.f, 0.f, 0.f));
+    struct Item { uint32_t node; float lo[3], hi[3]; };
+    std::vector<Item> stack;
+    Item root{};
+    for (int c = 0; c < 3; ++c) { root.lo[c] = pt->h_scene.root_min[c]; root.hi[c] = pt->h_scene.root_max[c]; }
+    stack.push_back(root);
+    while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        if (it.node >= ctx->h_tree.size()) continue;
+        const TreeNode& nd = ctx->h_tree[it.node];
+        if (nd.axis < 0) {
+            if (nd.child0 < C) {
+                box[nd.child0] = make_float4(it.lo[0], it.lo[1], it.lo[2], 0.f);
+                box[C + nd.child0] = make_float4(it.hi[0], it.hi[1], it.hi[2], 0.f);
+            }
+            continue;
+        }
+        Item up = it, down = it;
+        up.node = nd.child0;
+        up.lo[nd.axis] = nd.split;
+        down.node = nd.child1;
+        down.hi[nd.axis] = nd.split;
+        stack.push_back(up);
+        stack.push_back(down);
+    }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(pt->d_leaf_box, box.data(), 2 * C * sizeof(float4), cudaMemcpyHostToDevice));
+    pt->box_version = ctx->tree_version;
+    return SDMMB_OK;
+}
+
 // one product-guiding query launch over a list of the tracer (the BSDF table already lives on the device)
 int product_query(sdmmb_ctx* ctx, sdmmb_pt* pt, size_t n, const uint32_t* cell, const float* pos3, const float* u3,
                   const float* dir3, const float* normal3, float* out_dir3, float* out_pdf, float* out_ij,
@@ -240,7 +282,7 @@ int sdmmb_pt_create(sdmmb_ctx* ctx, sdmmb_pt** out, const sdmmb_quad* h_quads, i
 int sdmmb_pt_destroy(sdmmb_pt* pt) {
     if (!pt) return SDMMB_OK;
     DeviceGuard g(pt->ctx->device);
-    cudaFree(pt->d_scene); cudaFree(pt->d_paths); cudaFree(pt->d_lists); cudaFree(pt->d_counters); cudaFree(pt->d_bsdf);
+    cudaFree(pt->d_scene); cudaFree(pt->d_paths); cudaFree(pt->d_lists); cudaFree(pt->d_counters); cudaFree(pt->d_bsdf); cudaFree(pt->d_leaf_box);
     delete pt;
     return SDMMB_OK;
 }
@@ -299,7 +341,12 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
         CK(cudaMalloc(&pt->d_lists, batch * 184 + 64 * 256));  // 174 B of records + query planes per path
         pt->lists_cap = batch;
     }
+    if (collect) {
+        int rc = update_leaf_boxes(ctx, pt, st);
+        if (rc) return rc;
+    }
     PtFrame F{};
+    F.leaf_box = pt->d_leaf_box;
     F.tree = ctx->d_tree;
     F.n_tree_nodes = ctx->n_tree_nodes;
     F.cell_initialized = d_cell_initialized;

@@ -56,6 +56,9 @@ int sdmmb_set_tree(sdmmb_ctx* ctx, int n_nodes, const sdmmb_tree_node* h_nodes) 
     CK(cudaMalloc(&ctx->d_tree, (size_t)n_bfs * sizeof(TreeNode)));
     CK(cudaMemcpy(ctx->d_tree, bfs.data(), (size_t)n_bfs * sizeof(TreeNode), cudaMemcpyHostToDevice));
     ctx->n_tree_nodes = n_bfs;
+    ctx->h_tree.resize((size_t)n_bfs);
+    std::memcpy(ctx->h_tree.data(), bfs.data(), (size_t)n_bfs * sizeof(TreeNode));
+    ++ctx->tree_version;
     return SDMMB_OK;
 }
 

@@ -76,6 +76,7 @@ struct PtLists {
 struct PtFrame {
     const TreeNode* tree;
     int n_tree_nodes;
+    const float4* leaf_box;           // [2][max_cells]: min / max corner of every leaf's box as STree::find rebuilds it
     const uint8_t* cell_initialized;  // [max_cells]
     uint32_t max_cells;
     int guided;

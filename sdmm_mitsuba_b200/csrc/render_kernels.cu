@@ -169,31 +169,8 @@ __device__ __forceinline__ int4 tree_node(const TreeNode* __restrict__ nodes, co
     return node < (uint32_t)PT_TREE_TOP ? s_top[node] : __ldg(reinterpret_cast<const int4*>(nodes) + node);
 }
 
-// STree::find with the leaf's AABB (R: sdmm/include/sdmm/accelerators/spatial_tree.h:19-51); the AABB is
-// rebuilt during the descent: child 0 is the upper half (its min[axis] = split), child 1 the lower half.
-__device__ uint32_t find_leaf_aabb(const TreeNode* __restrict__ nodes, const int4* s_top, int n_nodes, V3 p, const float* root_min,
-                                   const float* root_max, float* amin, float* amax, uint32_t miss) {
-    // the box lives in scalars updated with selects: an array indexed by the split axis would sit in local memory
-    float lo0 = root_min[0], lo1 = root_min[1], lo2 = root_min[2], hi0 = root_max[0], hi1 = root_max[1], hi2 = root_max[2];
-    uint32_t node = 0, found = miss;
-    for (int depth = 0; depth < 96; ++depth) {
-        if (node >= (uint32_t)n_nodes) break;
-        const int4 raw = tree_node(nodes, s_top, node);
-        const int axis = raw.x;
-        if (axis < 0) { found = (uint32_t)raw.z; break; }
-        const float split = __int_as_float(raw.y);
-        const float c = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
-        const bool up = split < c;
-        node = up ? (uint32_t)raw.z : (uint32_t)raw.w;
-        lo0 = (up && axis == 0) ? split : lo0; lo1 = (up && axis == 1) ? split : lo1; lo2 = (up && axis == 2) ? split : lo2;
-        hi0 = (!up && axis == 0) ? split : hi0; hi1 = (!up && axis == 1) ? split : hi1; hi2 = (!up && axis == 2) ? split : hi2;
-    }
-    amin[0] = lo0; amin[1] = lo1; amin[2] = lo2;
-    amax[0] = hi0; amax[1] = hi1; amax[2] = hi2;
-    return found;
-}
-
-// STree::find without the box (the bounce kernel only needs the cell)
+// STree::find (R: sdmm/include/sdmm/accelerators/spatial_tree.h:19-51): the leaf's cell slot.  The leaf's box, which the
+// reference rebuilds during the descent, comes from the per-leaf table F.leaf_box where it is needed.
 __device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes, const int4* s_top, int n_nodes, V3 p, uint32_t miss) {
     uint32_t node = 0;
     for (int depth = 0; depth < 96; ++depth) {
@@ -471,6 +448,9 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
             const int vword = P.vcount[i];   // vertex count | emitter bits (pt_bounce_kernel)
             depth = min(vword & 0xff, PT_MAX_VERTS);
             emit_mask = (uint32_t)vword >> 8;
+            // a path that never found an emitter carries only zero weights: nothing of it is ever pushed, and the jitter
+            // draws it would make feed nothing else (the path's random stream ends here)
+            if (emit_mask == 0u) depth = 0;
             rng.state = P.rng[i];
             rng.inc = P.rng[n + i];
         }
@@ -493,28 +473,39 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
             // the vertex's sample weight: its own emitted term value / pdf (R: 836-838) plus, for every LATER vertex k of
             // the path that found an emitter, thr_k value_k / (thr_v pdf_v) per channel with thr_v above Mitsuba's Epsilon
             // (recordRadiance, R: 615-637) -- summed in path order, as the per-bounce updates were
-            const float vpdf = vp[15 * n];
-            const float inv = 1.f / vpdf;
-            float w3[3] = {vp[9 * n] * inv, vp[10 * n] * inv, vp[11 * n] * inv};
-            if ((emit_mask >> (dv + 1)) != 0u) {
-                const float vthr[3] = {vp[12 * n], vp[13 * n], vp[14 * n]};
-                for (int k = dv + 1; k < depth; ++k) {
-                    if (!((emit_mask >> k) & 1u)) continue;
-                    const float* kp = P.verts + ((size_t)k * PT_VERT_FLOATS) * n + i;
+            // No emitter at or after this vertex: every term is exactly 0, the sample is invalid (is_valid_sample).
+            if ((emit_mask >> dv) != 0u) {
+                const float vpdf = vp[15 * n];
+                const float inv = 1.f / vpdf;
+                float w3[3] = {vp[9 * n] * inv, vp[10 * n] * inv, vp[11 * n] * inv};
+                if ((emit_mask >> (dv + 1)) != 0u) {
+                    const float vthr[3] = {vp[12 * n], vp[13 * n], vp[14 * n]};
+                    for (int k = dv + 1; k < depth; ++k) {
+                        if (!((emit_mask >> k) & 1u)) continue;
+                        const float* kp = P.verts + ((size_t)k * PT_VERT_FLOATS) * n + i;
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const float rad = kp[(12 + c) * n] * kp[(9 + c) * n];
-                        if (vthr[c] > PT_SPEC_EPS) w3[c] += rad / (vthr[c] * vpdf);
+                        for (int c = 0; c < 3; ++c) {
+                            const float rad = kp[(12 + c) * n] * kp[(9 + c) * n];
+                            if (vthr[c] > PT_SPEC_EPS) w3[c] += rad / (vthr[c] * vpdf);
+                        }
                     }
                 }
+                w = (w3[0] + w3[1] + w3[2]) * (1.f / 3.f);                  // weight.average()
+                valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);           // is_valid_sample
             }
-            w = (w3[0] + w3[1] + w3[2]) * (1.f / 3.f);                  // weight.average()
-            valid = (w >= 1e-8f) && (w <= 3.402823466e+38f);           // is_valid_sample
-            pos = v3(vp[0], vp[n], vp[2 * n]);
-            const uint32_t cell = find_leaf_aabb(F.tree, s_top, F.n_tree_nodes, pos, sc.root_min, sc.root_max, smin, smax, 0xffffffffu);
-            cell_ok = cell < F.max_cells;   // the reference throws otherwise; positions are inside the root AABB
             n_jitters = (dv >= depth - 1) ? 1 : 0;
             if (w > 1000.f) ++n_jitters;
+            // the cell (and its box) is only needed by a push or by a jitter draw
+            if (valid || n_jitters > 0) {
+                pos = v3(vp[0], vp[n], vp[2 * n]);
+                const uint32_t cell = find_leaf(F.tree, s_top, F.n_tree_nodes, pos, 0xffffffffu);
+                cell_ok = cell < F.max_cells;   // the reference throws otherwise; positions are inside the root AABB
+                if (cell_ok) {                  // the leaf's box from the per-leaf table (what the descent would rebuild)
+                    const float4 lo = __ldg(F.leaf_box + cell), hi = __ldg(F.leaf_box + F.max_cells + cell);
+                    smin[0] = lo.x; smin[1] = lo.y; smin[2] = lo.z;
+                    smax[0] = hi.x; smax[1] = hi.y; smax[2] = hi.z;
+                }
+            }
         }
         const uint32_t seq0 = ((uint32_t)(F.path_base + i) << 5) | ((uint32_t)(depth - 1 - dv) << 2);
         pool_push_warp(act && cell_ok && valid, L, F, vp, n, w, pos, 1.f, seq0);
@@ -527,10 +518,11 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
                 const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next();
                 key = v3(pos.x + (u0 - 0.5f) * (smax[0] - smin[0]), pos.y + (u1 - 0.5f) * (smax[1] - smin[1]),
                          pos.z + (u2 - 0.5f) * (smax[2] - smin[2]));
-                float jmin[3], jmax[3];
-                const uint32_t jc = find_leaf_aabb(F.tree, s_top, F.n_tree_nodes, key, sc.root_min, sc.root_max, jmin, jmax, 0xffffffffu);
+                const uint32_t jc = find_leaf(F.tree, s_top, F.n_tree_nodes, key, 0xffffffffu);
+                float4 jlo = make_float4(smin[0], smin[1], smin[2], 0.f);
+                if (jc < F.max_cells) jlo = __ldg(F.leaf_box + jc);
                 // find() never fails for a point outside the root box (it lands in a boundary leaf), as in the reference
-                if (jc >= F.max_cells || (jmin[0] == smin[0] && jmin[1] == smin[1] && jmin[2] == smin[2])) {
+                if (jc >= F.max_cells || (jlo.x == smin[0] && jlo.y == smin[1] && jlo.z == smin[2])) {
                     if (++attempts >= 8) want = false;   // this jitter is given up; a later one fails at its first miss
                 } else {
                     got = true;
