@@ -30,6 +30,7 @@
 #include "sdmm/distributions/sdmm_context.h"
 #include "sdmm/opt/data.h"
 #include "sdmm/opt/em.h"
+#include "sdmm/opt/init.h"
 #include "sdmm/spaces/euclidian.h"
 #include "sdmm/spaces/offset_directional.h"
 #include "sdmm/spaces/spatio_directional.h"
@@ -299,6 +300,45 @@ int main(int argc, char** argv) {
                     counts ? "equal" : "DIFFER");
         ok = ok && counts && e2 <= 3e-3;   // two free-running calls: float32 drift of two implementations compounds
         worst = std::max(worst, e2);
+    }
+    {   // (d) sdmm::initialize with the reference's signature through the shim, against the reference's own
+        //     (opt/init.h:17-193): same generator passed by value, same seeds, same mixture and priors
+        std::mt19937 g1(900), g2(900);
+        auto a = make_cell(K, N, 0, g1), b = make_cell(K, N, 0, g2);
+        for (auto* c : {a.get(), b.get()})
+            for (int n = 0; n < N; ++n) {                  // normals that differ from sample to sample
+                float v[3] = {std::sin(0.37f * n), std::cos(0.91f * n), 0.4f + 0.5f * std::sin(0.13f * n)};
+                const float len = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+                for (int i = 0; i < 3; ++i) c->training_data.normal.coeff(i).coeff(n) = v[i] / len;
+            }
+        RNG rng;
+        for (int i = 0; i < 5; ++i) rng.next_float32();    // a generator that has been used: not in its seeded state
+        const float dist = 3.f * 1.7f / (float)(K / 8);
+        sdmm::initialize(a->sdmm, a->em, a->training_data, rng, (size_t)(K / 8), dist);
+        double e3 = 0;
+        try {
+            sdmm_b200::initialize(dev, 0, b->sdmm, b->em, b->training_data, rng, (size_t)(K / 8), dist);
+            e3 = std::max(e3, max_rel(b->sdmm.weight.pmf, a->sdmm.weight.pmf, K, 1e-12));
+            for (int i = 0; i < 6; ++i)
+                e3 = std::max(e3, max_rel(b->sdmm.tangent_space.mean.coeff(i), a->sdmm.tangent_space.mean.coeff(i), K, 1.0));
+            for (int r = 0; r < 5; ++r)
+                for (int col = 0; col < 5; ++col) {
+                    double scale = 1e-12;
+                    for (int rr = 0; rr < 5; ++rr)
+                        for (int k = 0; k < K; ++k) scale = std::max(scale, (double)std::abs(a->sdmm.cov(rr, rr).coeff(k)));
+                    e3 = std::max(e3, max_rel(b->sdmm.cov(r, col), a->sdmm.cov(r, col), K, scale));
+                    e3 = std::max(e3, max_rel(b->em.cov_prior(r, col), a->em.cov_prior(r, col), K, 2e-3));
+                    e3 = std::max(e3, max_rel(b->em.depth_prior(r, col), a->em.depth_prior(r, col), K, 1e-6));
+                }
+            const bool scalars = b->em.weight_prior == a->em.weight_prior && b->em.cov_prior_strength == a->em.cov_prior_strength &&
+                                 b->em.iterations_run == a->em.iterations_run && b->em.samples_seen == a->em.samples_seen;
+            std::printf("sdmm_b200::initialize (reference signature, generator by value): worst %.3e, priors %s\n", e3,
+                        scalars ? "equal" : "DIFFER");
+            ok = ok && scalars && e3 <= 1e-4;
+        } catch (const std::exception& e) {
+            std::printf("FAIL exception in initialize: %s\n", e.what());
+            ok = false;
+        }
     }
     std::printf("%s worst %.3e (tolerance 1e-3 per call)\n", ok ? "PASS" : "FAIL", worst);
     return ok ? 0 : 1;

@@ -196,6 +196,21 @@ void unpack_em(EM& em, int K, const float* e, const uint32_t* scal) {
     em.samples_seen = (int)scal[2];
 }
 
+// what sdmm::initialize sets besides the statistics: the priors (opt/init.h:88, 178-192)
+template <typename EM>
+void unpack_em_priors(EM& em, int K, const float* e, const uint32_t* scal) {
+    for (int r = 0; r < 5; ++r)
+        for (int c = 0; c < 5; ++c)
+            for (int k = 0; k < K; ++k) {
+                em.cov_prior(r, c).coeff(k) = e[(31 + 5 * r + c) * K + k];
+                em.depth_prior(r, c).coeff(k) = e[(56 + 5 * r + c) * K + k];
+            }
+    em.weight_prior = w2f(scal[3]);
+    em.cov_prior_strength = w2f(scal[4]);
+    em.learning_rate = w2f(scal[5]);
+    em.alpha = w2f(scal[6]);
+}
+
 // ---- sample staging: the reference keeps one Data<> object per cell (opt/data.h:25-57); the device
 // wants one SoA block per call.  Planes of all cells are gathered into one host block. --------------
 struct SampleBlock {
@@ -242,6 +257,46 @@ void em_step(Device& dev, int slot, SDMM_& distribution, EM_& em, Data_& data, i
     check(sdmmb_download_cells(dev.ctx(), slot, 1, joint.data(), e.data(), scal, nullptr), "sdmmb_download_cells", dev.ctx());
     unpack_joint(distribution, K, joint.data());
     unpack_em(em, K, e.data(), scal);
+}
+
+// ---- sdmm::initialize (opt/init.h:17-193) for ONE cell held in device slot `slot` -----------------
+// The reference takes the generator BY VALUE (initializeSDMMContext passes the context's rng, volpath_sdmm.cpp:132-137):
+// the copy's (state, inc) is turned back into the (initstate, initseq) pair of PCG32::seed that the C ABI takes,
+//   state = (inc + initstate) * M + inc   =>   initstate = (state - inc) * M^-1 - inc,  initseq = inc >> 1,
+// so the device replays exactly the draws the reference's copy would make.
+inline uint64_t pcg32_mult_inverse() {
+    const uint64_t m = 0x5851f42d4c957f2dULL;
+    uint64_t x = m;                                   // Newton iteration for the inverse modulo 2^64
+    for (int i = 0; i < 6; ++i) x *= 2 - m * x;
+    return x;
+}
+template <typename SDMM_, typename EM_, typename Data_, typename RNG_>
+void initialize(Device& dev, int slot, SDMM_& distribution, EM_& em, Data_& data, RNG_ rng, size_t n_spatial_components,
+                float spatial_distance) {
+    const int K = dev.K();
+    if ((size_t)K != 8 * n_spatial_components)
+        throw std::runtime_error("sdmm_b200::initialize: the device context holds K = 8 x n_spatial_components components");
+    const size_t n = data.size;
+    PinnedBuffer<float> point6, normal3, weight;
+    point6.resize(6 * n);
+    normal3.resize(3 * n);
+    weight.resize(n);
+    for (int i = 0; i < 6; ++i) std::memcpy(point6.data() + i * n, data.point.coeff(i).data(), n * sizeof(float));
+    for (int i = 0; i < 3; ++i) std::memcpy(normal3.data() + i * n, data.normal.coeff(i).data(), n * sizeof(float));
+    std::memcpy(weight.data(), data.weight.data(), n * sizeof(float));
+    const uint32_t offsets[2] = {0u, (uint32_t)n};
+    const uint64_t state = (uint64_t)rng.state, inc = (uint64_t)rng.inc;
+    const uint64_t initstate = (state - inc) * pcg32_mult_inverse() - inc, initseq = inc >> 1;
+    check(sdmmb_initialize_host(dev.ctx(), slot, 1, point6.data(), normal3.data(), n, weight.data(), offsets,
+                                &spatial_distance, initstate, initseq, nullptr, nullptr), "sdmmb_initialize_host", dev.ctx());
+    std::vector<float> joint(32 * (size_t)K), e(81 * (size_t)K);
+    uint32_t scal[8];
+    check(sdmmb_download_cells(dev.ctx(), slot, 1, joint.data(), e.data(), scal, nullptr), "sdmmb_download_cells", dev.ctx());
+    enoki::set_slices(distribution, K);
+    enoki::set_slices(em, K);
+    unpack_joint(distribution, K, joint.data());
+    unpack_em(em, K, e.data(), scal);
+    unpack_em_priors(em, K, e.data(), scal);
 }
 
 // ---- sdmm::prepare(conditioner, joint) (distributions/sdmm_conditioner.h:89-100) ------------------
@@ -329,6 +384,12 @@ template <typename SDMM_, typename EM_, typename Data_>
 void em_step(SDMM_& distribution, EM_& em, Data_& data) {
     Device& dev = default_device();
     em_step(dev, dev.slot_of(&distribution), distribution, em, data, 1);
+}
+// void sdmm::initialize(SDMM&, EM&, Data&, RNG, size_t n_spatial_components, float spatial_distance)   opt/init.h:17-24
+template <typename SDMM_, typename EM_, typename Data_, typename RNG_>
+void initialize(SDMM_& distribution, EM_& em, Data_& data, RNG_ rng, size_t n_spatial_components, float spatial_distance) {
+    Device& dev = default_device();
+    initialize(dev, dev.slot_of(&distribution), distribution, em, data, rng, n_spatial_components, spatial_distance);
 }
 // void sdmm::prepare(Conditioner&, JointSDMM&)                 distributions/sdmm_conditioner.h:89-93
 template <typename Conditioner, typename SDMM_>
