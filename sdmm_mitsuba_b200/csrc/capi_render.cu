@@ -27,8 +27,8 @@ struct sdmmb_pt {
 namespace {
 
 size_t pt_path_bytes() {
-    // o d thr li (12 f) + rng (2 u64) + depth vcount quad mode slot (5 w) + pend (8 f) + verts
-    return (12 + 4 + 5 + 8 + (size_t)PT_MAX_VERTS * PT_VERT_FLOATS) * 4;
+    // thr li (6 f) + rng (2 u64) + depth vcount quad mode slot (5 w) + pend (8 f) + verts
+    return (6 + 4 + 5 + 8 + (size_t)PT_MAX_VERTS * PT_VERT_FLOATS) * 4;
 }
 
 void pt_carve_paths(sdmmb_pt* pt, size_t n, PtPaths& P) {
@@ -36,8 +36,6 @@ void pt_carve_paths(sdmmb_pt* pt, size_t n, PtPaths& P) {
     auto take = [&](size_t bytes) { char* r = b; b += (bytes + 255) / 256 * 256; return r; };
     P.n = n;
     P.rng = (uint64_t*)take(2 * n * 8);
-    P.o = (float*)take(3 * n * 4);
-    P.d = (float*)take(3 * n * 4);
     P.thr = (float*)take(3 * n * 4);
     P.li = (float*)take(3 * n * 4);
     P.depth = (int32_t*)take(n * 4);
@@ -326,7 +324,7 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n_total = (size_t)pt->h_scene.width * pt->h_scene.height * (size_t)spp;
     if (n_total >= (1u << 27)) return SDMMB_E_DATA_FULL;   // push-sequence ids are path * 32 + ... in 32 bits
-    // A pass is traced in batches of at most `batch` paths: the per-path state (628 B) and the query lists (184 B) are
+    // A pass is traced in batches of at most `batch` paths: the per-path state (604 B) and the query lists (184 B) are
     // allocated once for a batch instead of growing with spp; a path's pixel, random stream and push-sequence ids
     // follow its GLOBAL index, so the result does not depend on the batch size.
     static const size_t batch_env = [] { const char* v = getenv("SDMMB_PT_BATCH"); return v ? (size_t)atoll(v) : (size_t)0; }();
@@ -371,8 +369,6 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
         if (guided) pt_carve_lists(pt, n, L);
         L.counters = pt->d_counters;
         F.path_base = base;
-        CK(pt_launch_generate(pt->d_scene, P, F, st));
-        ++launches;
         size_t nA = 0, nB = 0;
         for (int bounce = 0; bounce < pt->h_scene.max_depth; ++bounce) {
             CK(cudaMemsetAsync(pt->d_counters, 0, 8, st));

@@ -48,8 +48,6 @@ struct PtScene {
 // per-path state, SoA over n_paths
 struct PtPaths {
     size_t n;
-    float* o;        // [3][n]
-    float* d;        // [3][n]
     float* thr;      // [3][n]
     float* li;       // [3][n]
     uint64_t* rng;   // [2][n]
@@ -90,7 +88,6 @@ struct PtFrame {
     size_t path_base; // a pass is traced in batches of paths: global path id = path_base + index in the batch
 };
 
-cudaError_t pt_launch_generate(const PtScene* d_scene, const PtPaths& P, const PtFrame& F, cudaStream_t st);
 cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, int first,
                              size_t nA, size_t nB, cudaStream_t st);
 cudaError_t pt_launch_pack_lists(const PtScene* d_scene, const PtLists& L, size_t nA, size_t nB, cudaStream_t st);

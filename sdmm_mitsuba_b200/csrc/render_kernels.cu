@@ -186,33 +186,6 @@ __device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
-// camera rays (process(): samplePos = pixel + next2D, sensor ray; R: 146-176)
-// ------------------------------------------------------------------------------------------------
-__global__ void pt_generate_kernel(const PtScene* __restrict__ scp, PtPaths P, PtFrame F) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P.n) return;
-    const PtScene& sc = *scp;
-    const size_t npix = (size_t)sc.width * sc.height;
-    const size_t pix = (F.path_base + i) % npix;
-    const int px = (int)(pix % sc.width), py = (int)(pix / sc.width);
-    Rng rng;
-    rng.seed(F.seed, (uint64_t)(F.path_base + i));
-    const float sx = (float)px + rng.next(), sy = (float)py + rng.next();
-    const float cx = (1.f - 2.f * sx / (float)sc.width) * sc.tan_x;
-    const float cy = (1.f - 2.f * sy / (float)sc.height) * sc.tan_y;
-    V3 d = ld3(sc.cam_forward) + ld3(sc.cam_right) * cx + ld3(sc.cam_up) * cy;
-    d = d * rsqrtf(dot(d, d));
-    const size_t n = P.n;
-    P.o[i] = sc.cam_origin[0]; P.o[n + i] = sc.cam_origin[1]; P.o[2 * n + i] = sc.cam_origin[2];
-    P.d[i] = d.x; P.d[n + i] = d.y; P.d[2 * n + i] = d.z;
-    for (int c = 0; c < 3; ++c) { P.thr[c * n + i] = 1.f; P.li[c * n + i] = 0.f; }
-    P.rng[i] = rng.state; P.rng[n + i] = rng.inc;
-    P.depth[i] = 1;   // rRec.newQuery: depth = 1 at the first intersection
-    P.vcount[i] = 0;
-    P.mode[i] = 0;
-}
-
-// ------------------------------------------------------------------------------------------------
 // one bounce of every live path
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __restrict__ scp, PtPaths P, PtLists L, PtFrame F,
@@ -220,7 +193,8 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
     __shared__ SceneSmem S;
     __shared__ int4 s_top[PT_TREE_TOP];
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int depth = (i < P.n) ? P.depth[i] : 0;
+    // first bounce: the path starts here (rRec.newQuery: depth = 1 at the first intersection), nothing to read
+    int depth = (i < P.n) ? (first ? 1 : P.depth[i]) : 0;
     if (!__syncthreads_or(depth > 0)) return;   // a CTA of finished paths leaves at once
     const PtScene& sc = *scp;
     stage_scene(sc, S);
@@ -229,13 +203,22 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
     if (depth <= 0) return;
     const int n_groups = sc.n_groups;
     const size_t n = P.n;
-    Rng rng{P.rng[i], P.rng[n + i]};
-    V3 thr = v3(P.thr[i], P.thr[n + i], P.thr[2 * n + i]);
-    V3 li = v3(P.li[i], P.li[n + i], P.li[2 * n + i]);
+    Rng rng;
+    V3 thr = v3(1.f, 1.f, 1.f), li = v3(0.f, 0.f, 0.f);
     // vcount word: stored vertices in the low byte, above it one bit per vertex whose outgoing ray found an emitter
-    const int vword = P.vcount[i];
-    int vc = vword & 0xff;
-    uint32_t emit_mask = (uint32_t)vword >> 8;
+    int vc = 0;
+    uint32_t emit_mask = 0u;
+    if (first) {
+        rng.seed(F.seed, (uint64_t)(F.path_base + i));
+    } else {
+        rng.state = P.rng[i];
+        rng.inc = P.rng[n + i];
+        thr = v3(P.thr[i], P.thr[n + i], P.thr[2 * n + i]);
+        li = v3(P.li[i], P.li[n + i], P.li[2 * n + i]);
+        const int vword = P.vcount[i];
+        vc = vword & 0xff;
+        emit_mask = (uint32_t)vword >> 8;
+    }
     V3 o, d;
     int hq;
     float t_hit;
@@ -316,8 +299,16 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
             if (hq < 0) alive = false;
         }
     } else {
-        o = v3(P.o[i], P.o[n + i], P.o[2 * n + i]);
-        d = v3(P.d[i], P.d[n + i], P.d[2 * n + i]);
+        // camera ray (process(): samplePos = pixel + next2D, sensor ray; R: 146-176)
+        const size_t npix = (size_t)sc.width * sc.height;
+        const size_t pix = (F.path_base + i) % npix;
+        const int px = (int)(pix % sc.width), py = (int)(pix / sc.width);
+        const float sx = (float)px + rng.next(), sy = (float)py + rng.next();
+        const float cx = (1.f - 2.f * sx / (float)sc.width) * sc.tan_x;
+        const float cy = (1.f - 2.f * sy / (float)sc.height) * sc.tan_y;
+        o = ld3(sc.cam_origin);
+        d = ld3(sc.cam_forward) + ld3(sc.cam_right) * cx + ld3(sc.cam_up) * cy;
+        d = d * rsqrtf(dot(d, d));
         hq = intersect(S, n_groups, o, d, t_hit);
         if (hq < 0) alive = false;
         else {
@@ -374,6 +365,7 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
         P.pend[5 * n + i] = npos.x; P.pend[6 * n + i] = npos.y; P.pend[7 * n + i] = npos.z;
     }
     P.rng[i] = rng.state;
+    if (first) P.rng[n + i] = rng.inc;
     P.thr[i] = thr.x; P.thr[n + i] = thr.y; P.thr[2 * n + i] = thr.z;
     P.li[i] = li.x; P.li[n + i] = li.y; P.li[2 * n + i] = li.z;
     P.vcount[i] = vc | (int)(emit_mask << 8);
@@ -648,11 +640,6 @@ __global__ void __launch_bounds__(256) pt_rebucket_kernel(const float* __restric
 namespace {
 unsigned blocks_for(size_t n, int t) { return (unsigned)((n + t - 1) / t); }
 }  // namespace
-
-cudaError_t pt_launch_generate(const PtScene* d_scene, const PtPaths& P, const PtFrame& F, cudaStream_t st) {
-    pt_generate_kernel<<<blocks_for(P.n, 256), 256, 0, st>>>(d_scene, P, F);
-    return cudaGetLastError();
-}
 
 cudaError_t pt_launch_bounce(const PtScene* d_scene, const PtPaths& P, const PtLists& L, const PtFrame& F, int first,
                              size_t nA, size_t nB, cudaStream_t st) {
