@@ -27,8 +27,8 @@ struct sdmmb_pt {
 namespace {
 
 size_t pt_path_bytes() {
-    // thr li (6 f) + rng (2 u64) + depth vcount quad mode slot (5 w) + pend (8 f) + verts
-    return (6 + 4 + 5 + 8 + (size_t)PT_MAX_VERTS * PT_VERT_FLOATS) * 4;
+    // thr li (6 f) + rng (2 u64) + depth vcount pword (3 w) + pend (5 f) + verts
+    return (6 + 4 + 3 + 5 + (size_t)PT_MAX_VERTS * PT_VERT_FLOATS) * 4;
 }
 
 void pt_carve_paths(sdmmb_pt* pt, size_t n, PtPaths& P) {
@@ -40,10 +40,8 @@ void pt_carve_paths(sdmmb_pt* pt, size_t n, PtPaths& P) {
     P.li = (float*)take(3 * n * 4);
     P.depth = (int32_t*)take(n * 4);
     P.vcount = (int32_t*)take(n * 4);
-    P.quad = (int32_t*)take(n * 4);
-    P.mode = (int32_t*)take(n * 4);
-    P.slot = (uint32_t*)take(n * 4);
-    P.pend = (float*)take(8 * n * 4);
+    P.pword = (uint32_t*)take(n * 4);
+    P.pend = (float*)take(5 * n * 4);
     P.verts = (float*)take((size_t)PT_MAX_VERTS * PT_VERT_FLOATS * n * 4);
 }
 
@@ -328,7 +326,7 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
     // allocated once for a batch instead of growing with spp; a path's pixel, random stream and push-sequence ids
     // follow its GLOBAL index, so the result does not depend on the batch size.
     static const size_t batch_env = [] { const char* v = getenv("SDMMB_PT_BATCH"); return v ? (size_t)atoll(v) : (size_t)0; }();
-    const size_t batch = std::min(n_total, batch_env ? batch_env : ((size_t)16 << 20));
+    const size_t batch = std::min(std::min(n_total, batch_env ? batch_env : ((size_t)16 << 20)), (size_t)1 << 24);   // list slots are 24 bits
     if (batch > pt->paths_cap) {
         cudaFree(pt->d_paths); pt->d_paths = nullptr; pt->paths_cap = 0;
         CK(cudaMalloc(&pt->d_paths, batch * pt_path_bytes() + 64 * 256));

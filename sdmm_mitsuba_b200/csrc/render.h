@@ -53,10 +53,9 @@ struct PtPaths {
     uint64_t* rng;   // [2][n]
     int32_t* depth;  // rRec.depth, <= 0 : path finished
     int32_t* vcount; // stored vertices
-    int32_t* quad;   // quad of the pending hit
-    int32_t* mode;   // pending sampling decision: 0 BSDF only, 1 BSDF + MIS pdf query, 2 guided
-    uint32_t* slot;  // slot in list A or B
-    float* pend;     // [8][n]: hit p(3), b1, b2, npos(3)
+    uint32_t* pword; // pending hit and sampling decision: quad (6 bits) | mode (2: 0 BSDF only, 1 BSDF + MIS pdf query,
+                     // 2 guided) | slot in list A or B (24 bits: a batch holds at most 2^24 paths)
+    float* pend;     // [5][n]: hit p(3), b1, b2
     float* verts;    // [PT_MAX_VERTS][PT_VERT_FLOATS][n]
 };
 

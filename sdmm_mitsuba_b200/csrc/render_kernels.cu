@@ -226,13 +226,15 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
 
     if (!first) {
         // ---- finalise the sampling decision taken at the pending hit (sampleSurface, R: 383-507) ----
-        const PtQuad& Q = sc.quads[P.quad[i]];
+        // pending decision of the previous bounce, one word: quad (6 bits) | mode (2 bits) | list slot (24 bits)
+        const uint32_t pword = P.pword[i];
+        const PtQuad& Q = sc.quads[pword & 63u];
         const V3 nrm = ld3(Q.n), rho = ld3(Q.reflectance);
         const V3 p = v3(P.pend[i], P.pend[n + i], P.pend[2 * n + i]);
         const float b1 = P.pend[3 * n + i], b2 = P.pend[4 * n + i];
-        const V3 npos = v3(P.pend[5 * n + i], P.pend[6 * n + i], P.pend[7 * n + i]);
-        const int mode = P.mode[i];
-        const uint32_t slot = P.slot[i];
+        const V3 npos = (p - ld3(sc.aabb_min)) * sc.inv_spatial_norm;    // createCondition, recomputed (same bits)
+        const int mode = (int)((pword >> 6) & 3u);
+        const uint32_t slot = pword >> 8;
         V3 wo = v3(0.f, 0.f, 0.f), weight = v3(0.f, 0.f, 0.f);
         float misPdf = 0.f;
         bool use_bsdf = (mode != 2);
@@ -357,12 +359,9 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
                 }
             }
         }
-        P.quad[i] = hq;
-        P.mode[i] = mode;
-        P.slot[i] = slot;
+        P.pword[i] = (uint32_t)hq | ((uint32_t)mode << 6) | (slot << 8);
         P.pend[i] = p.x; P.pend[n + i] = p.y; P.pend[2 * n + i] = p.z;
         P.pend[3 * n + i] = b1; P.pend[4 * n + i] = b2;
-        P.pend[5 * n + i] = npos.x; P.pend[6 * n + i] = npos.y; P.pend[7 * n + i] = npos.z;
     }
     P.rng[i] = rng.state;
     if (first) P.rng[n + i] = rng.inc;
