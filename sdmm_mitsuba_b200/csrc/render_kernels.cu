@@ -183,6 +183,17 @@ __device__ __forceinline__ uint32_t find_leaf(const TreeNode* __restrict__ nodes
     return miss;
 }
 
+// A slot in one of the two query lists: the lanes of a warp that take this branch together reserve consecutive
+// slots with ONE atomic (the list counter is a single word; neighbours' records also end up next to each other).
+__device__ __forceinline__ uint32_t list_slot(uint32_t* counter) {
+    const unsigned m = __activemask();
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
@@ -346,13 +357,13 @@ __global__ void __launch_bounds__(128, 8) pt_bounce_kernel(const PtScene* __rest
                     s = s * rsqrtf(dot(s, s));
                     const V3 tt = v3(hn.y * s.z - hn.z * s.y, hn.z * s.x - hn.x * s.z, hn.x * s.y - hn.y * s.x);
                     const V3 wo = s * loc.x + tt * loc.y + hn * loc.z;
-                    slot = atomicAdd(&L.counters[1], 1u);
+                    slot = list_slot(&L.counters[1]);
                     float4* r = reinterpret_cast<float4*>(L.recB + (size_t)slot * 8);
                     r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
                     r[1] = make_float4(wo.x, wo.y, wo.z, __int_as_float(hq));
                 } else {
                     mode = 2;
-                    slot = atomicAdd(&L.counters[0], 1u);
+                    slot = list_slot(&L.counters[0]);
                     float4* r = reinterpret_cast<float4*>(L.recA + (size_t)slot * 8);
                     r[0] = make_float4(__uint_as_float(cell), npos.x, npos.y, npos.z);
                     r[1] = make_float4(g0, g1, g2, __int_as_float(hq));
