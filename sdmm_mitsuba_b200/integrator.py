@@ -35,6 +35,7 @@ class SDMMIntegrator:
         self.K, self.spi, self.max_depth = int(K), int(samples_per_iteration), int(max_depth)
         self.seed = int(seed)
         self.split_threshold = int(split_threshold)
+        assert max_cells <= 65536, "the (cell, pass, sequence) sort key of optimize() holds 16 bits of cell index"
         self.cells = SDMMCells(max_cells, K, device=device)
         self.cells.set_min_samples(1)
         # optimizeAsync (the reference's default, volpath_sdmm.cpp:65, 180-242): a fit's records and `initialized`
@@ -117,7 +118,7 @@ class SDMMIntegrator:
         new = (self.pool_count, int(st.pool_count))
         self.pool_count = int(st.pool_count)
         if collect and new[1] > new[0]:
-            self.pool[13, new[0]:new[1]] += 2.0 * (self.iteration & 0xFF)   # plane 13 = is_main + 2 * pass number
+            self.pool[13, new[0]:new[1]] += 2.0 * (self.iteration & 0x7FFF)   # plane 13 = is_main + 2 * pass number (exact in float32)
         # the pool is filled in scheduling order; optimize() sorts the training samples of a cell by their push
         # sequence number (plane 14), the order a single-threaded reference would have pushed them in
         return st, new
@@ -262,7 +263,7 @@ class SDMMIntegrator:
         # planes the fit reads
         seq = self.pool[14, :n].view(torch.int32).to(torch.int64) & 0xFFFFFFFF
         passno = (self.pool[13, :n] * 0.5).to(torch.int64)
-        key = (cells_all << 40) | (passno << 32) | seq
+        key = (cells_all << 47) | (passno << 32) | seq                   # cell < 2^16, pass < 2^15, seq < 2^32
         if all_train:
             sel = None
             idx = torch.sort(key)[1]
