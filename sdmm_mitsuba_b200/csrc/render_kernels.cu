@@ -405,31 +405,47 @@ __global__ void pt_pack_lists_kernel(const PtScene* __restrict__ scp, PtLists L,
     }
 }
 
-// One push site of the collection, executed by the WHOLE warp: the lanes that push reserve consecutive pool
-// slots with one atomic per warp (the pool counter is a single word: per-lane atomics on it serialise across the
-// GPU) and write them coalesced.  "Data full." (R: sdmm/include/sdmm/opt/data.h:60-66) is counted per sample.
-__device__ __forceinline__ void pool_push_warp(bool pred, const PtLists& L, const PtFrame& F, const float* vp, size_t n,
-                                               float w, V3 key, float is_main, uint32_t seq) {
-    const unsigned m = __ballot_sync(0xffffffffu, pred);
-    if (m == 0u) return;
+// The pushes of one vertex step -- the main sample and up to two jittered copies per lane -- executed by the WHOLE
+// warp: the lanes reserve consecutive pool slots with one atomic per warp (the pool counter is a single word: per-lane
+// atomics on it serialise across the GPU), the vertex record is read once, and the writes of neighbouring lanes are
+// adjacent.  "Data full." (R: sdmm/include/sdmm/opt/data.h:60-66) is counted per sample.
+__device__ __forceinline__ void pool_push_warp(const bool f[3], const V3 key[3], const uint32_t seq[3], const PtLists& L,
+                                               const PtFrame& F, const float* vp, size_t n, float w) {
+    const int cnt = (f[0] ? 1 : 0) + (f[1] ? 1 : 0) + (f[2] ? 1 : 0);
+    if (!__any_sync(0xffffffffu, cnt > 0)) return;
     const int lane = threadIdx.x & 31;
-    const int leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&L.counters[2], (uint32_t)__popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (!pred) return;
-    const uint32_t idx = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
-    if (idx >= F.pool_cap) {
-        atomicAdd(&L.counters[3], 1u);
-        return;
+    int incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += up;
     }
-    float* o = F.pool + idx;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(&L.counters[2], (uint32_t)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (cnt == 0) return;
+    uint32_t idx = base + (uint32_t)(incl - cnt);
+    float v9[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) v9[c] = vp[c * n];   // point6 | normal3
     const size_t S = F.pool_cap;
-    for (int c = 0; c < 9; ++c) o[c * S] = vp[c * n];   // point6 | normal3
-    o[9 * S] = w;
-    o[10 * S] = key.x; o[11 * S] = key.y; o[12 * S] = key.z;
-    o[13 * S] = is_main;
-    o[14 * S] = __uint_as_float(seq);   // order a single-threaded reference would push in: path, vertex, jitter
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        if (!f[r]) continue;
+        if (idx >= F.pool_cap) {
+            atomicAdd(&L.counters[3], 1u);
+        } else {
+            float* o = F.pool + idx;
+#pragma unroll
+            for (int c = 0; c < 9; ++c) o[c * S] = v9[c];
+            o[9 * S] = w;
+            o[10 * S] = key[r].x; o[11 * S] = key[r].y; o[12 * S] = key[r].z;
+            o[13 * S] = r == 0 ? 1.f : 0.f;   // only the main push feeds the cell's SpatialStats
+            o[14 * S] = __uint_as_float(seq[r]);   // order a single-threaded reference would push in: path, vertex, jitter
+        }
+        ++idx;
+    }
 }
 
 // end of every path: film accumulation + the sample collection of Li's tail (R: 862-965).  The vertex loop is
@@ -510,9 +526,12 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
             }
         }
         const uint32_t seq0 = ((uint32_t)(F.path_base + i) << 5) | ((uint32_t)(depth - 1 - dv) << 2);
-        pool_push_warp(act && cell_ok && valid, L, F, vp, n, w, pos, 1.f, seq0);
+        bool pf[3] = {act && cell_ok && valid, false, false};
+        V3 pkey[3] = {pos, pos, pos};
+        uint32_t pseq[3] = {seq0, seq0, seq0};
         uint32_t pushed = 0;
         int attempts = 0;
+#pragma unroll
         for (int j = 0; j < 2; ++j) {
             bool want = act && cell_ok && j < n_jitters, got = false;
             V3 key = pos;
@@ -532,8 +551,11 @@ __global__ void __launch_bounds__(256, 4) pt_finish_kernel(const PtScene* __rest
             }
             const bool push = got && valid;
             if (push) ++pushed;
-            pool_push_warp(push, L, F, vp, n, w, key, 0.f, seq0 + pushed);
+            pf[1 + j] = push;
+            pkey[1 + j] = key;
+            pseq[1 + j] = seq0 + pushed;
         }
+        pool_push_warp(pf, pkey, pseq, L, F, vp, n, w);
     }
 }
 
