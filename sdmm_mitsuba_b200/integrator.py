@@ -272,9 +272,15 @@ class SDMMIntegrator:
             base = torch.nonzero(sel).squeeze(1)
             idx = base[torch.sort(key[base])[1]]
         del key, seq, passno
-        train = self.pool[0:10, :n].index_select(1, idx)                 # sorted by cell
+        fresh = np.nonzero(can & ~self.has_mixture)[0]                   # cells sdmm::initialize will seed below
         off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
-        point6, normal3, weight = train[0:6], train[6:9], train[9]
+        if fresh.size:          # the normals are only read by sdmm::initialize
+            train = self.pool[0:10, :n].index_select(1, idx)             # sorted by cell
+            point6, normal3, weight = train[0:6], train[6:9], train[9]
+        else:
+            point6 = self.pool[0:6, :n].index_select(1, idx)
+            weight = self.pool[9, :n].index_select(0, idx)
+            train, normal3 = point6, None
         # async schedule: the fit runs on its own stream, ordered after everything queued so far, and is joined in
         # publish_pending() after the next pass; the training copies must outlive it
         if self.optimize_async:
@@ -282,7 +288,6 @@ class SDMMIntegrator:
             self._pending_keep = (train, point6, normal3, weight)
         with (torch.cuda.stream(self._em_stream) if self.optimize_async else contextlib.nullcontext()):
             # sdmm::initialize for cells without a mixture (volpath_sdmm.cpp:292-294)
-            fresh = np.nonzero(can & ~self.has_mixture)[0]
             if fresh.size:
                 runs = np.split(fresh, np.nonzero(np.diff(fresh) != 1)[0] + 1)
                 for run in runs:
