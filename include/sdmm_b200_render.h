@@ -85,7 +85,9 @@ int sdmmb_pt_render(sdmmb_pt* pt, int spp, uint64_t seed, int guided, int collec
  * samples [0, n) of d_pool [15][pool_capacity]: d_out_cell[i] = device slot of STree::find(key_i) (-1: none), and
  * d_out_stats [8][max_cells] doubles (zeroed by the call) = per cell: number, sum p, sum p^2 of the MAIN pushes with
  * index >= new_begin (the SpatialStats the renderer's push feeds, sdmm_proc.cpp:893-895; planes 0, 1-3, 4-6) and
- * the number of all pooled samples (Data::size of canBeOptimized; plane 7).  One kernel, asynchronous on `stream`. */
+ * the number of all pooled samples (Data::size of canBeOptimized; plane 7).  One kernel, asynchronous on `stream`.
+ * Plane 13 is read as an integer whose bit 0 is is_main: a caller may add 2 * (pass number) to the values
+ * sdmmb_pt_render wrote (integrator.py does, to keep older passes in front when it orders a cell's samples). */
 int sdmmb_pt_pool_stats(sdmmb_ctx* ctx, const float* d_pool, size_t pool_capacity, size_t n, size_t new_begin,
                         int32_t* d_out_cell, double* d_out_stats, void* stream);
 
