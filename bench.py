@@ -88,6 +88,7 @@ def run_b200(args, cfg):
     render = refbench = None
     if S.rank == 0 and S.world == 1 and not args.no_render:
         from benchlegs.render_leg import run_render
+        S.torch.cuda.empty_cache()       # the cfg5 leg's blocks go back to the driver before the tracer allocates its own
         render = run_render(S.torch, cpu=not args.no_cpu_baseline)
     if S.rank == 0 and S.world == 1 and not args.no_cpu_baseline:
         from benchlegs import refbench_leg
