@@ -425,8 +425,12 @@ em_mstep_kernel(MStepArgs a) {
             for (int i = 0; i < 25; ++i) snc[i] = rcp_weight_sum * st_cov[i];
             // update_model                                             R: opt/em.h:353-488
             const int it = iterations_run < 30 ? iterations_run : 30;
-            const float weight_prior_decay = (float)(1.0 / pow(3.0, (double)it));
-            const float cov_prior_strength_decay = (float)(1.0 / pow(2.0, (double)it));
+            // 3^it and 2^it, it <= 30, are exact in double (3^30 < 2^53): a product loop gives what std::pow gives the
+            // reference, without the several hundred instructions of a general double pow per thread
+            double p3 = 1.0;
+            for (int e = 0; e < it; ++e) p3 *= 3.0;
+            const float weight_prior_decay = (float)(1.0 / p3);
+            const float cov_prior_strength_decay = (float)(1.0 / (double)(1u << it));
             const float weight_prior_decayed = weight_prior * weight_prior_decay;
             const float cps_decayed = cov_prior_strength * cov_prior_strength_decay;
             const float rcp_weight = 1.f / snw;
